@@ -1,0 +1,111 @@
+"""Pins the CPU oracle (oracle/bphot_oracle.c) to the golden vectors produced by the
+UNMODIFIED reference (tests/golden/gen_golden.py).  CPU only."""
+import numpy as np
+import pytest
+
+from oracle import oracle
+from tests.conftest import assert_close, load_golden
+from tests.golden.cases import APER_CASES
+
+
+def test_pixwt_docstring_value():
+    # pixwt.py:25-30: Pixwt(3.23,4.22,3.44,5,7) ==> 0.6502
+    w = oracle.Pixwt(3.23, 4.22, 3.44, [5.0], [7.0])
+    assert abs(w[0] - 0.6502) < 5e-5
+
+
+def test_pixwt_golden():
+    g = load_golden("golden_pixwt.npz")
+    for i in range(g["xc"].size):
+        m = g["pid"] == i
+        w = oracle.Pixwt(g["xc"][i], g["yc"][i], g["r"][i], g["x"][m], g["y"][m])
+        assert_close(w, g["w"][m], rtol=1e-12, atol=1e-13, what="pixwt case %d" % i)
+    w = oracle.Pixwt(3.5, 3.5, 2.0, g["half_x"], g["half_y"])
+    assert_close(w, g["half_w"], rtol=1e-12, atol=1e-13, what="pixwt half-integer centre")
+    assert_close(oracle.Pixwt(3.23, 4.22, 3.44, [5.0], [7.0]), g["doc"], rtol=1e-13)
+
+
+def test_mmm_golden():
+    g = load_golden("golden_mmm.npz")
+    off = 0
+    for n, out in zip(g["lens"], g["out"]):
+        v = g["vec"][off:off + n]
+        off += n
+        got = oracle.mmm(v, readnoise=out[3], minsky=int(out[4]))
+        assert_close(got, out[:3], rtol=1e-12, atol=1e-12, what="mmm n=%d" % n)
+
+
+def test_psfmodel_golden():
+    g = load_golden("golden_psfmodel.npz")
+    f, pder = oracle.daoerf(g["xx"], g["yy"], g["gauss"])
+    assert_close(f, g["f"], rtol=1e-12, atol=1e-300, what="daoerf f")
+    assert_close(pder, g["pder"], rtol=1e-11, atol=1e-12, what="daoerf pder")
+    half = (g["psf"].shape[0] - 1) / 2.0
+    z, dx, dy = oracle.rinter(g["psf"], 2 * g["xx"] + half, 2 * g["yy"] + half)
+    assert_close(z, g["z"], rtol=1e-12, atol=1e-12, what="rinter z")
+    assert_close(dx, g["dfdx"], rtol=1e-12, atol=1e-12, what="rinter dfdx")
+    assert_close(dy, g["dfdy"], rtol=1e-12, atol=1e-12, what="rinter dfdy")
+    v, dvx, dvy = oracle.dao_value(g["xx"], g["yy"], g["gauss"], g["psf"])
+    assert_close(v, g["v"], rtol=1e-12, atol=1e-12, what="dao_value")
+    assert_close(dvx, g["dvx"], rtol=1e-11, atol=1e-11, what="dao_value dvdx")
+    assert_close(dvy, g["dvy"], rtol=1e-11, atol=1e-11, what="dao_value dvdy")
+    ve, _, _ = oracle.dao_value(g["xe"], g["yy"][:10], g["gauss"], g["psf"])
+    assert np.all(ve == 0.0) and np.all(g["ve"] == 0.0)
+
+
+@pytest.mark.parametrize("mode", ["py3", "py2"])
+@pytest.mark.parametrize("cname", [c[0] for c in APER_CASES])
+def test_aper_golden(mode, cname):
+    g = load_golden("golden_aper.npz")
+    kw = dict(dict(APER_CASES)[cname])
+    if mode == "py2" and not kw.get("exact"):
+        pytest.skip("py2 == py3 for exact=False")
+    r = oracle.aper(g["image"], g["x"], g["y"], phpadu=float(g["phpadu"]), zeropoint=25.0, compat=mode, **kw)
+    names = ("mag", "magerr", "flux", "fluxerr", "sky", "skyerr", "badflag")
+    for nm, a in zip(names, r):
+        want = g["%s__%s__%s" % (mode, cname, nm)]
+        if nm == "badflag":
+            assert np.array_equal(a, want), "badflag %s" % cname
+        else:
+            # flux is a difference of ~1e4-scale sums: allow 1e-9 of the summed magnitude via atol
+            assert_close(a, want, rtol=1e-9, atol=1e-7 if nm in ("flux", "fluxerr") else 1e-10,
+                         what="%s %s %s" % (mode, cname, nm))
+
+
+PK_COLS = {"norecent": ("errmag", "chi", "sharp", "niter", "scale", "chi2"),
+           "noise": ("errmag", "chi", "sharp", "niter", "scale", "x", "y"),
+           "pkfit_rec": ("errmag", "chi", "sharp", "niter", "scale", "x", "y"),
+           "pkfit_norec": ("errmag", "chi", "sharp", "niter", "scale", "x", "y")}
+
+
+@pytest.mark.parametrize("radius", [3.0, 5.0])
+@pytest.mark.parametrize("kind", list(PK_COLS))
+def test_pkfit_golden(kind, radius):
+    g = load_golden("golden_pkfit.npz")
+    want = g["%s__r%d" % (kind, radius)]
+    variant = {"norecent": oracle.PKFIT_NORECENT, "noise": oracle.PKFIT_NOISE,
+               "pkfit_rec": oracle.PKFIT, "pkfit_norec": oracle.PKFIT}[kind]
+    o = oracle.pkfit(variant, g["image"], g["gauss"], g["psf"], float(g["ronois"]), float(g["phpadu"]),
+                     g["noise"], g["mask"], g["scale0"], g["x"], g["y"], g["sky"], radius,
+                     recenter=(kind != "pkfit_norec"))
+    cols = PK_COLS[kind]
+    assert np.array_equal(o["niter"], want[:, 3].astype(np.int32)), \
+        "niter differs at %s" % np.nonzero(o["niter"] != want[:, 3])[0][:8]
+    for j, nm in enumerate(cols):
+        if nm == "niter":
+            continue
+        w = want[:, j]
+        got = o[nm]
+        if nm in ("x", "y", "chi2"):
+            # early-return tuples of the reference drop these columns (padded NaN in the golden file)
+            keep = ~np.isnan(w)
+            got, w = got[keep], w[keep]
+        if nm == "sharp":
+            # Off-frame stars see only the far Gaussian tail, where Phi(u2)-Phi(u1) cancels to ~1e-7 of an
+            # erf ulp: scipy's erf (reference) and libm's erf (oracle) then differ by ~1e-9 relative in the
+            # model itself.  Third-party ulp-level arithmetic, so those stars get 1e-6.
+            ny_, nx_ = g["image"].shape
+            off = ~((g["x"] >= 0) & (g["x"] <= nx_ - 1) & (g["y"] >= 0) & (g["y"] <= ny_ - 1))
+            assert_close(got[off], w[off], rtol=1e-6, atol=1e-12, what="%s r=%g sharp(off-frame)" % (kind, radius))
+            got, w = got[~off], w[~off]
+        assert_close(got, w, rtol=1e-9, atol=1e-12, what="%s r=%g %s" % (kind, radius, nm))
