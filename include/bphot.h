@@ -1,0 +1,153 @@
+/*
+ * bphot.h -- C ABI of libbphot.so, the B200 (sm_100a) batched stellar-photometry library.
+ *
+ * The reference (djones1040/PythonPhot @ 7992eb6) is pure Python and has no FFI of its own; the
+ * boundary replaced here is its per-star Python API.  Each entry point
+ * below names the reference callable whose per-star loop it executes for a whole star list.
+ * Plain pointers and sizes only.  Two flavours per operation:
+ *
+ *   *_device  every array argument is a DEVICE pointer (e.g. torch.Tensor.data_ptr()); the work
+ *             is enqueued on `stream` (a cudaStream_t, NULL = default stream) and the call
+ *             returns without synchronising.  Small parameter vectors (apr, setskyval, gauss)
+ *             are HOST pointers, copied at call time.
+ *   *_host    every array argument is a HOST pointer; the call uploads, runs, downloads and
+ *             synchronises on CUDA device `device`.
+ *
+ * Conventions shared with the reference:
+ *   - images are [nrow, ncol] row-major, x = column, y = row; `pitch` = elements between rows;
+ *   - per-star failures are reported in band (NaN outputs, sigma = -1, badflag = 1, niter
+ *     sentinels) exactly as the reference reports them; the int return value is only about the
+ *     call itself: 0 = ok, negative = BPHOT_ERR_*; bphot_last_error() has the message.
+ *   - the library never retains or frees caller memory.
+ */
+#ifndef BPHOT_H
+#define BPHOT_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BPHOT_VERSION 100 /* 0.1.0 */
+
+#define BPHOT_F32 0
+#define BPHOT_F64 1
+
+#define BPHOT_PKFIT 0          /* PythonPhot/pkfit.py:132            pkfit_class.pkfit */
+#define BPHOT_PKFIT_NOISE 1    /* PythonPhot/pkfit_noise.py:131      pkfit_class.pkfit_noise */
+#define BPHOT_PKFIT_NORECENT 2 /* PythonPhot/pkfit_norecent_noise.py:132 pkfit_class.pkfit_norecent_noise */
+
+#define BPHOT_MAX_APERTURES 16
+
+#define BPHOT_OK 0
+#define BPHOT_ERR_ARG (-1)      /* bad argument (NULL pointer, naper out of range, ...) */
+#define BPHOT_ERR_CUDA (-2)     /* CUDA runtime error, see bphot_last_error() */
+#define BPHOT_ERR_CAPACITY (-3) /* sky annulus / fitting box larger than one CTA's shared memory */
+#define BPHOT_ERR_NODEVICE (-4) /* no CUDA device: there is no CPU fallback */
+
+int bphot_version(void);
+const char* bphot_last_error(void);
+int bphot_device_count(void);
+/* number of kernels this library has launched in this process (bench.py's gpu_launches) */
+long long bphot_launch_count(void);
+
+/*
+ * aper.aper(image, xc, yc, phpadu, apr, zeropoint, skyrad, badpix, setskyval, minsky,
+ *           skyalgorithm='mmm', exact, readnoise)            PythonPhot/aper.py:26-433
+ * with its callees mmm.mmm (mmm.py:7) and pixwt.Pixwt (pixwt.py:8).
+ *   apr[naper]        aperture radii (host)
+ *   skyrad_in/out     skyrad[0], skyrad[1]
+ *   badlo, badhi      badpix[0], badpix[1] (equal = no bad-pixel test, aper.py:260)
+ *   use_setsky        1 = setskyval given; setsky[3] = (sky, sigma, nsky) (aper.py:156-160, 302-308)
+ *   minsky            20 when the reference default [] is used (aper.py:148)
+ *   exact             1 = pixwt exact overlap (aper.py:313-333), 0 = polygon approximation
+ *   compat_py2        0 = Python-3 semantics of aper.py:246-248 (yy = row + col/nx), 1 = Python-2
+ *                     integer row (what the reference was written for); only matters when exact=1
+ * Outputs (fp64 unless noted): mag, magerr, flux, fluxerr [nstars*naper]; sky, skyerr [nstars];
+ * badflag uint8 [nstars*naper]; nsky int32 [nstars] (annulus pixels handed to mmm, aper.py:267);
+ * mmm_iter int32 [nstars] (clipping iterations mmm ran).
+ */
+int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, long long pitch,
+                      const double* d_xc, const double* d_yc, int nstars,
+                      double phpadu, const double* apr, int naper, double zeropoint,
+                      double skyrad_in, double skyrad_out, double badlo, double badhi,
+                      int use_setsky, const double* setsky, int minsky, int exact,
+                      double readnoise, int compat_py2,
+                      double* d_mag, double* d_magerr, double* d_flux, double* d_fluxerr,
+                      double* d_sky, double* d_skyerr, unsigned char* d_badflag,
+                      int* d_nsky, int* d_mmm_iter, void* stream);
+
+int bphot_aper_host(const void* image, int image_dtype, int nrow, int ncol,
+                    const double* xc, const double* yc, int nstars,
+                    double phpadu, const double* apr, int naper, double zeropoint,
+                    double skyrad_in, double skyrad_out, double badlo, double badhi,
+                    int use_setsky, const double* setsky, int minsky, int exact,
+                    double readnoise, int compat_py2,
+                    double* mag, double* magerr, double* flux, double* fluxerr,
+                    double* sky, double* skyerr, unsigned char* badflag,
+                    int* nsky, int* mmm_iter, int device);
+
+/*
+ * pkfit_class(image, gauss, psf, ronois, phpadu[, noise, mask]).{pkfit, pkfit_noise,
+ * pkfit_norecent_noise}(scale, x, y, sky, radius, maxiter)  for a list of stars.
+ *   PythonPhot/pkfit.py:119-458, pkfit_noise.py:118-462, pkfit_norecent_noise.py:119-531,
+ *   with dao_value.dao_value (dao_value.py:9), daoerf.daoerf (daoerf.py:9), rinter.rinter (rinter.py:8).
+ *   variant           BPHOT_PKFIT / BPHOT_PKFIT_NOISE / BPHOT_PKFIT_NORECENT
+ *   noise, mask       ignored (may be NULL) for BPHOT_PKFIT; mask is uint8, nonzero = masked
+ *   gauss[5]          (height, x0, y0, sigx, sigy) (host)
+ *   psf[npsf*npsf]    residual look-up table, fp64
+ *   recenter          pkfit.py's `recenter` keyword (BPHOT_PKFIT only)
+ * Outputs [nstars]: errmag, chi, sharp, scale, x, y, chi2 (fp64), niter (int32).  x, y are the
+ * fitted (or unchanged) positions (`xyout=True`); chi2 is pkfit_norecent_noise's `returnchi2`
+ * value, NaN for the other variants.
+ */
+int bphot_pkfit_device(int variant, const void* d_image, int image_dtype,
+                       const void* d_noise, int noise_dtype, const unsigned char* d_mask,
+                       int nrow, int ncol, long long pitch, long long noise_pitch, long long mask_pitch,
+                       const double* gauss, const double* d_psf, int npsf,
+                       double ronois, double phpadu,
+                       const double* d_scale, const double* d_x, const double* d_y, const double* d_sky,
+                       double radius, int maxiter, int recenter, int nstars,
+                       double* d_errmag, double* d_chi, double* d_sharp, int* d_niter,
+                       double* d_scale_out, double* d_x_out, double* d_y_out, double* d_chi2,
+                       void* stream);
+
+int bphot_pkfit_host(int variant, const void* image, int image_dtype,
+                     const void* noise, int noise_dtype, const unsigned char* mask,
+                     int nrow, int ncol,
+                     const double* gauss, const double* psf, int npsf,
+                     double ronois, double phpadu,
+                     const double* scale, const double* x, const double* y, const double* sky,
+                     double radius, int maxiter, int recenter, int nstars,
+                     double* errmag, double* chi, double* sharp, int* niter,
+                     double* scale_out, double* x_out, double* y_out, double* chi2,
+                     int device);
+
+/*
+ * mmm.mmm(sky_vector, readnoise, minsky, mxiter) for nvec vectors packed back to back
+ * (PythonPhot/mmm.py:7-314).  offs[nvec+1] = element offsets; max_len = longest vector.
+ * out3[nvec*3] = (skymod, sigma, skew) per vector; iters[nvec] = clipping iterations.
+ */
+int bphot_mmm_device(const void* d_vec, int dtype, const long long* d_offs, int nvec, int max_len,
+                     double readnoise, int minsky, int mxiter,
+                     double* d_out3, int* d_iters, void* stream);
+
+/* pixwt.Pixwt(xc, yc, r, x[n], y[n]) -> out[n]            PythonPhot/pixwt.py:8-48 */
+int bphot_pixwt_device(double xc, double yc, double r, const double* d_x, const double* d_y,
+                       long long n, double* d_out, void* stream);
+
+/*
+ * Per-point PSF model pieces (dao_value.py:95-107, daoerf.py:49-74, rinter.py:98-195).
+ * out[12*n], structure-of-arrays rows: value, dvdx, dvdy, daoerf f, pder0..pder4, rinter z, dfdx, dfdy.
+ * Points whose table coordinates fall outside [1, npsf-2] get zeros in the table-dependent rows;
+ * dao_value's all-or-nothing guard (dao_value.py:70-84) is the caller's to apply.
+ * table_coords != 0: xx, yy are already look-up-table coordinates (rinter.rinter's own x, y); only the
+ * rinter rows (z, dfdx, dfdy) are meaningful then.
+ */
+int bphot_psfmodel_device(const double* d_xx, const double* d_yy, long long n,
+                          const double* d_gauss, const double* d_psf, int npsf, int table_coords,
+                          double* d_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BPHOT_H */

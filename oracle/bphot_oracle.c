@@ -267,7 +267,11 @@ int bo_mmm(const double *v, int n_in, double readnoise, int minsky, int mxiter,
 /* ------------------------------------------------------------------- aper */
 /* aper.py:26-433 with skyalgorithm='mmm' or setskyval.  Outputs are [nstars*naper]
  * (mag, magerr, flux, fluxerr, badflag) and [nstars] (sky, skyerr, nsky, mmm_iter).
- * compat_py2 selects the Python-2 integer row for yy at aper.py:248. */
+ * compat_py2 selects the Python-2 integer row for yy at aper.py:248.
+ * fragile[nstars*naper] (may be NULL): 1 when the reference's own badflag / flux for that aperture hinges on
+ * rounding noise -- a non-finite or out-of-range pixel sits where Pixwt returns |w| < 1e-9 (outside the
+ * circle but inside the bigrad box), so whether it is "in" the aperture (aper.py:329-330, w > 0) depends on
+ * the last bits of eight atan() values.  Tests exclude those apertures from bit-exact comparison. */
 int bo_aper(const void *img, int img_dt, int nrow, int ncol,
             const double *xc, const double *yc, int nstars,
             double phpadu, const double *apr, int naper, double zeropoint,
@@ -276,7 +280,7 @@ int bo_aper(const void *img, int img_dt, int nrow, int ncol,
             double readnoise, int compat_py2,
             double *mag, double *magerr, double *flux, double *fluxerr,
             double *sky, double *skyerr, double *badflag, int *nsky_o, int *mmm_iter_o,
-            int nthreads) {
+            unsigned char *fragile, int nthreads) {
     if (use_setsky) { skyrad_in = 0.; skyrad_out = apr[0]; for (int k = 1; k < naper; k++) if (apr[k] > skyrad_out) skyrad_out = apr[k]; skyrad_out += 1; } /* aper.py:156-160 */
     double rinsq = skyrad_in * skyrad_in, routsq = skyrad_out * skyrad_out;
 #ifdef _OPENMP
@@ -291,7 +295,7 @@ int bo_aper(const void *img, int img_dt, int nrow, int ncol,
             double *o_mag = mag + (size_t)i * naper, *o_magerr = magerr + (size_t)i * naper;
             double *o_flux = flux + (size_t)i * naper, *o_fluxerr = fluxerr + (size_t)i * naper;
             double *o_bad = badflag + (size_t)i * naper;
-            for (int k = 0; k < naper; k++) { o_mag[k] = o_magerr[k] = o_flux[k] = o_fluxerr[k] = NAN; o_bad[k] = 1; }
+            for (int k = 0; k < naper; k++) { o_mag[k] = o_magerr[k] = o_flux[k] = o_fluxerr[k] = NAN; o_bad[k] = 1; if (fragile) fragile[(size_t)i * naper + k] = 0; }
             double skymod = 0., skysig = 0., skyskw = 0., skyvar = 0., sigsq = 0.;
             sky[i] = 0.; skyerr[i] = 0.; nsky_o[i] = 0; mmm_iter_o[i] = 0;
             double x = xc[i], y = yc[i];
@@ -362,7 +366,15 @@ int bo_aper(const void *img, int img_dt, int nrow, int ncol,
                             double w;
                             if (x1 > bigrad || y1 > bigrad) continue; /* aper.py:319-320 */
                             if (x1 < smallrad && y1 < smallrad) w = 1.0; /* aper.py:316-318 */
-                            else { w = bo_pixwt(dx, dy, ap, xxp, yyp); if (w < 0.0) w = 0.0; } /* aper.py:328-329 */
+                            else {
+                                w = bo_pixwt(dx, dy, ap, xxp, yyp); /* aper.py:328-329 */
+                                if (fragile && fabs(w) < 1e-9) {
+                                    double pv = ld(img, img_dt, (size_t)(ly + r) * ncol + (lx + c));
+                                    if (!isfinite(pv) || (badlo < badhi && (pv <= badlo || pv >= badhi)))
+                                        fragile[(size_t)i * naper + k] = 1;
+                                }
+                                if (w < 0.0) w = 0.0;
+                            }
                             if (!(w > 0.0)) continue; /* aper.py:330 */
                             skybuf[nw] = ld(img, img_dt, (size_t)(ly + r) * ncol + (lx + c));
                             wv[nw] = w; nw++;

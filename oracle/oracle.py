@@ -85,6 +85,7 @@ def aper(image, xc, yc, phpadu=1, apr=5, zeropoint=25, skyrad=(40, 50), badpix=(
     bad = np.empty((n, na))
     sky, skyerr = np.empty(n), np.empty(n)
     nsky, mit = np.empty(n, np.int32), np.empty(n, np.int32)
+    fragile = np.zeros((n, na), np.uint8)
     if setskyval is not None:
         ssv = np.atleast_1d(np.asarray(setskyval, dtype=np.float64))
         if ssv.size == 1:
@@ -100,10 +101,10 @@ def aper(image, xc, yc, phpadu=1, apr=5, zeropoint=25, skyrad=(40, 50), badpix=(
                   C.c_int(use), _p(ssv), C.c_int(int(minsky)), C.c_int(int(bool(exact))), C.c_double(float(readnoise or 0)),
                   C.c_int(1 if compat == "py2" else 0),
                   _p(outs[0]), _p(outs[1]), _p(outs[2]), _p(outs[3]), _p(sky), _p(skyerr), _p(bad), _p(nsky), _p(mit),
-                  C.c_int(nthreads))
+                  _p(fragile), C.c_int(nthreads))
     res = (outs[0], outs[1], outs[2], outs[3], sky, skyerr, bad)
     if return_extra:
-        return res + (nsky, mit)
+        return res + (nsky, mit, fragile.astype(bool))
     return res
 
 

@@ -1,0 +1,174 @@
+"""ctypes binding of libbphot.so (C ABI declared in include/bphot.h).
+
+The CUDA library is the only execution path of this package: if it is missing, or no CUDA device
+is visible, the entry points raise -- there is no CPU fallback.
+PyTorch is used for device buffers, streams and copies only.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(_HERE, "csrc")
+SO_PATH = os.path.join(CSRC, "libbphot.so")
+F32, F64 = 0, 1
+PKFIT, PKFIT_NOISE, PKFIT_NORECENT = 0, 1, 2
+MAX_APERTURES = 16
+
+_lib = None
+
+_vp, _i, _d, _ll = C.c_void_p, C.c_int, C.c_double, C.c_longlong
+
+_SIGNATURES = {
+    "bphot_version": (C.c_int, []),
+    "bphot_last_error": (C.c_char_p, []),
+    "bphot_device_count": (C.c_int, []),
+    "bphot_launch_count": (C.c_longlong, []),
+    "bphot_aper_device": (C.c_int, [_vp, _i, _i, _i, _ll, _vp, _vp, _i, _d, _vp, _i, _d, _d, _d, _d, _d, _i, _vp, _i, _i,
+                                    _d, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "bphot_aper_host": (C.c_int, [_vp, _i, _i, _i, _vp, _vp, _i, _d, _vp, _i, _d, _d, _d, _d, _d, _i, _vp, _i, _i,
+                                  _d, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i]),
+    "bphot_pkfit_device": (C.c_int, [_i, _vp, _i, _vp, _i, _vp, _i, _i, _ll, _ll, _ll, _vp, _vp, _i, _d, _d,
+                                     _vp, _vp, _vp, _vp, _d, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "bphot_pkfit_host": (C.c_int, [_i, _vp, _i, _vp, _i, _vp, _i, _i, _vp, _vp, _i, _d, _d,
+                                   _vp, _vp, _vp, _vp, _d, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i]),
+    "bphot_mmm_device": (C.c_int, [_vp, _i, _vp, _i, _i, _d, _i, _i, _vp, _vp, _vp]),
+    "bphot_pixwt_device": (C.c_int, [_d, _d, _d, _vp, _vp, _ll, _vp, _vp]),
+    "bphot_psfmodel_device": (C.c_int, [_vp, _vp, _ll, _vp, _vp, _i, _i, _vp, _vp]),
+}
+EXPORTS = tuple(_SIGNATURES)
+
+
+class BphotError(RuntimeError):
+    pass
+
+
+def build(force=False, extra=""):
+    """Compile libbphot.so in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    if force and os.path.exists(SO_PATH):
+        os.remove(SO_PATH)
+    cmd = ["make", "-s", "-C", CSRC, "libbphot.so"]
+    if extra:
+        cmd.append("EXTRA=" + extra)
+    subprocess.check_call(cmd)
+    return SO_PATH
+
+
+def lib():
+    """Load libbphot.so; raise loudly if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise BphotError("%s not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                             "(or `make -C pythonphot_b200/csrc`). This package has no CPU fallback." % SO_PATH)
+        handle = C.CDLL(SO_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise BphotError("libbphot error %d: %s" % (rc, lib().bphot_last_error().decode("utf-8", "replace")))
+
+
+def launch_count():
+    return int(lib().bphot_launch_count())
+
+
+def torch_cuda():
+    """Return the torch module after checking that a CUDA device is usable."""
+    import torch
+    if not torch.cuda.is_available():
+        raise BphotError("no CUDA device is visible: pythonphot_b200 runs on the GPU only (no CPU fallback)")
+    return torch
+
+
+def device_of(device=None):
+    torch = torch_cuda()
+    if device is None:
+        return torch.device("cuda", torch.cuda.current_device())
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        raise BphotError("device must be a CUDA device, got %r" % (device,))
+    if dev.index is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+    return dev
+
+
+def dtype_code(t):
+    """BPHOT_F32/F64 for a torch tensor or numpy array of floats."""
+    name = str(t.dtype)
+    if name.endswith("float32"):
+        return F32
+    if name.endswith("float64"):
+        return F64
+    raise BphotError("unsupported pixel dtype %s (float32 or float64)" % name)
+
+
+def to_device_image(a, device, allow=("float32", "float64")):
+    """numpy array / torch tensor -> contiguous 2-D CUDA tensor (fp32 stays fp32; other dtypes -> fp64).
+
+    A float32 image is widened pixel by pixel inside the kernels, which is bit-equivalent to the
+    reference called with image.astype(float64)."""
+    torch = torch_cuda()
+    if isinstance(a, torch.Tensor):
+        t = a
+        if t.dtype not in (torch.float32, torch.float64):
+            t = t.to(torch.float64)
+        t = t.to(device, non_blocking=True)
+    else:
+        a = np.asarray(a)
+        if a.dtype != np.float32:
+            a = a.astype(np.float64, copy=False)
+        t = torch.from_numpy(np.ascontiguousarray(a)).to(device, non_blocking=True)
+    if t.dim() != 2:
+        raise BphotError("image must be 2-D, got shape %s" % (tuple(t.shape),))
+    return t.contiguous()
+
+
+def to_device_mask(a, device):
+    """mask image -> uint8 CUDA tensor, nonzero = masked (pkfit_noise.py:206-208 tests mask == 0)."""
+    torch = torch_cuda()
+    if isinstance(a, torch.Tensor):
+        t = (a != 0).to(torch.uint8).to(device, non_blocking=True)
+    else:
+        t = torch.from_numpy(np.ascontiguousarray(np.asarray(a) != 0).view(np.uint8)).to(device, non_blocking=True)
+    return t.contiguous()
+
+
+def to_device_f64(a, device, n=None):
+    """star-list column -> contiguous fp64 CUDA vector (scalars broadcast to n)."""
+    torch = torch_cuda()
+    if isinstance(a, torch.Tensor):
+        t = a.to(device=device, dtype=torch.float64, non_blocking=True).reshape(-1)
+    else:
+        t = torch.from_numpy(np.ascontiguousarray(np.atleast_1d(np.asarray(a, dtype=np.float64)).reshape(-1))).to(
+            device, non_blocking=True)
+    if n is not None and t.numel() != n:
+        if t.numel() != 1:
+            raise BphotError("star-list column has %d entries, expected %d" % (t.numel(), n))
+        t = t.expand(n)
+    return t.contiguous()
+
+
+def host_f64(a):
+    return np.ascontiguousarray(np.atleast_1d(np.asarray(a, dtype=np.float64)).reshape(-1))
+
+
+def ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def nptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def stream_ptr(device):
+    torch = torch_cuda()
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)

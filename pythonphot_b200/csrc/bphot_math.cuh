@@ -1,0 +1,437 @@
+// bphot_math.cuh -- scalar fp64 building blocks of the photometry kernels.
+//
+// Every function here is the per-pixel / per-star arithmetic of one reference routine
+// (djones1040/PythonPhot @ 7992eb6), written in the reference's own order of operations so
+// that discrete decisions (pixel membership, clipping brackets, convergence) agree with it.
+// The translation unit is compiled with --fmad=false: no a*b+c contraction, each operation
+// rounds once like numpy does.  Transcendentals (erf, exp, atan, log10, sqrt) are CUDA libm.
+//
+//   pixwt()        PythonPhot/pixwt.py:8-235   (vector branch, the one aper.py:328 calls)
+//   daoerf()       PythonPhot/daoerf.py:49-90
+//   rinter()       PythonPhot/rinter.py:98-195 (deriv=True)
+//   psf_value()    PythonPhot/dao_value.py:95-107 (per point; the edge guard is the caller's)
+//   inv3()         scipy.linalg.inv on the 3x3 normal matrix (pkfit*.py) -- potrf/potri when
+//                  symmetric positive definite, getrf/getri otherwise
+//   mmm_*          bracket searches of PythonPhot/mmm.py:199-248 on a sorted vector
+#pragma once
+#include <math.h>
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define BP_HD __host__ __device__ __forceinline__
+#define BP_D __device__ __forceinline__
+#else
+#define BP_HD static inline
+#endif
+
+namespace bphot {
+
+// ------------------------------------------------------------------ pixwt
+// pixwt.py:50-62.  Plain division: x == 0 gives +-inf and atan(+-inf) = +-pi/2 (IEEE), as numpy.
+BP_HD double pw_arc(double x, double y0, double y1, double r) {
+    return 0.5 * r * r * (atan(y1 / x) - atan(y0 / x));
+}
+// pixwt.py:64-72
+BP_HD double pw_chord(double x, double y0, double y1) { return 0.5 * x * (y1 - y0); }
+
+// pixwt.py:112-213: area between the line X = x and the circle, from y0 to y1.
+BP_HD double pw_oneside(double x, double y0, double y1, double r) {
+    if (fabs(x) >= r) return pw_arc(x, y0, y1, r);
+    const double yh = sqrt(r * r - x * x);
+    // three zones for y0 (<= -yh, inside, >= yh) x three zones for y1 (<= -yh, <= yh, above)
+    const int z0 = (y0 <= -yh) ? 0 : ((y0 < yh) ? 1 : 2);
+    const int z1 = (y1 <= -yh) ? 0 : ((y1 <= yh) ? 1 : 2);
+    switch (z0 * 3 + z1) {
+        case 0: return pw_arc(x, y0, y1, r);
+        case 1: return pw_arc(x, y0, -yh, r) + pw_chord(x, -yh, y1);
+        case 2: return pw_arc(x, y0, -yh, r) + pw_chord(x, -yh, yh) + pw_arc(x, yh, y1, r);
+        case 3: return pw_chord(x, y0, -yh) + pw_arc(x, -yh, y1, r);
+        case 4: return pw_chord(x, y0, y1);
+        case 5: return pw_chord(x, y0, yh) + pw_arc(x, yh, y1, r);
+        case 6: return pw_arc(x, y0, yh, r) + pw_chord(x, yh, -yh) + pw_arc(x, -yh, y1, r);
+        case 7: return pw_arc(x, y0, yh, r) + pw_chord(x, yh, y1);
+        default: return pw_arc(x, y0, y1, r);
+    }
+}
+
+// pixwt.py:8-48 + Intarea pixwt.py:215-235: area of the unit pixel centred (x,y) inside the
+// circle of radius r centred (xc,yc).
+BP_HD double pixwt(double xc, double yc, double r, double x, double y) {
+    const double x0 = (x - 0.5) - xc, y0 = (y - 0.5) - yc;
+    const double x1 = (x + 0.5) - xc, y1 = (y + 0.5) - yc;
+    return pw_oneside(x1, y0, y1, r) + pw_oneside(y1, -x1, -x0, r) +
+           pw_oneside(-x0, -y1, -y0, r) + pw_oneside(-y0, x0, x1, r);
+}
+
+// -------------------------------------------------------------- PSF model
+// daoerf.py:76-90
+BP_HD double gauss_cdf(double t) { return 0.5 + 0.5 * erf(t * (1. / sqrt(2.))); }
+
+// daoerf.py:49-74.  a = (height, x0, y0, sigx, sigy).  Returns f; pder[0..4] when non-null.
+BP_HD double daoerf(double x, double y, const double* a, double* pder) {
+    const double norm = 2.506628275;  // the reference's truncated sqrt(2 pi), daoerf.py:49
+    const double u2 = (x - a[1] + 0.5) / a[3], u1 = (x - a[1] - 0.5) / a[3];
+    const double v2 = (y - a[2] + 0.5) / a[4], v1 = (y - a[2] - 0.5) / a[4];
+    const double fx = norm * a[3] * (gauss_cdf(u2) - gauss_cdf(u1));
+    const double fy = norm * a[4] * (gauss_cdf(v2) - gauss_cdf(v1));
+    if (pder) {
+        const double up = exp(-0.5 * (u2 * u2)), um = exp(-0.5 * (u1 * u1));
+        const double vp = exp(-0.5 * (v2 * v2)), vm = exp(-0.5 * (v1 * v1));
+        pder[0] = fx * fy;
+        pder[1] = a[0] * fy * (-up + um);
+        pder[2] = a[0] * fx * (-vp + vm);
+        pder[3] = a[0] * fy * (fx / a[3] + u1 * um - u2 * up);
+        pder[4] = a[0] * fx * (fy / a[4] + v1 * vm - v2 * vp);
+    }
+    return a[0] * fx * fy;
+}
+
+// Only what the fit needs from daoerf: f, df/dx0, df/dy0 (pder[1], pder[2]).
+BP_HD double daoerf_xy(double x, double y, const double* a, double* p1, double* p2) {
+    const double norm = 2.506628275;
+    const double u2 = (x - a[1] + 0.5) / a[3], u1 = (x - a[1] - 0.5) / a[3];
+    const double v2 = (y - a[2] + 0.5) / a[4], v1 = (y - a[2] - 0.5) / a[4];
+    const double fx = norm * a[3] * (gauss_cdf(u2) - gauss_cdf(u1));
+    const double fy = norm * a[4] * (gauss_cdf(v2) - gauss_cdf(v1));
+    const double up = exp(-0.5 * (u2 * u2)), um = exp(-0.5 * (u1 * u1));
+    const double vp = exp(-0.5 * (v2 * v2)), vm = exp(-0.5 * (v1 * v1));
+    *p1 = a[0] * fy * (-up + um);
+    *p2 = a[0] * fx * (-vp + vm);
+    return a[0] * fx * fy;
+}
+
+// One row of rinter.py:161-184: cubic through the flat neighbours k-1..k+2 of the table.
+// Flat indices past the end read the last element (rinter.py:117-135 pads the table with it).
+BP_HD void rinter_row(const double* p, long plen, long k, double xd, double* val, double* der) {
+    const long last = plen - 1;
+    const double pm = p[(k - 1) < plen ? (k - 1) : last];
+    const double p0 = p[k < plen ? k : last];
+    const double p1 = p[(k + 1) < plen ? (k + 1) : last];
+    const double p2 = p[(k + 2) < plen ? (k + 2) : last];
+    const double c1 = 0.5 * (p1 - pm);
+    const double c2 = 2. * p1 + pm - 0.5 * (5. * p0 + p2);
+    const double c3 = 0.5 * (3. * (p0 - p1) + p2 - pm);
+    *val = xd * (xd * (xd * c3 + c2) + c1) + p0;
+    *der = xd * (xd * c3 * 3. + 2. * c2) + c1;
+}
+
+// rinter.py:98-195 for one point of an [nr, nc] table (row-major, x = column).
+BP_HD double rinter(const double* p, int nr, int nc, double x, double y, double* dfdx, double* dfdy) {
+    const long plen = (long)nr * nc;
+    const long i = (long)x, j = (long)y;  // rinter.py:98 (truncation)
+    const double xd = x - (double)i, yd = y - (double)j;
+    const long km = (long)nc * (j - 1) + i;  // rinter.py:101-104
+    double ym, y0, y1, y2, gm, g0, g1, g2;
+    rinter_row(p, plen, km, xd, &ym, &gm);
+    rinter_row(p, plen, km + nc, xd, &y0, &g0);
+    rinter_row(p, plen, km + 2L * nc, xd, &y1, &g1);
+    rinter_row(p, plen, km + 3L * nc, xd, &y2, &g2);
+    {  // rinter.py:185-188: the y-cubic of the four row derivatives
+        const double d1 = 0.5 * (g1 - gm);
+        const double d2 = 2. * g1 + gm - 0.5 * (5. * g0 + g2);
+        const double d3 = 0.5 * (3. * (g0 - g1) + g2 - gm);
+        *dfdx = yd * (yd * (yd * d3 + d2) + d1) + g0;
+    }
+    const double d1 = 0.5 * (y1 - ym);  // rinter.py:190-195
+    const double d2 = 2. * y1 + ym - 0.5 * (5. * y0 + y2);
+    const double d3 = 0.5 * (3. * (y0 - y1) + y2 - ym);
+    *dfdy = yd * (yd * d3 * 3. + 2. * d2) + d1;
+    return yd * (yd * (yd * d3 + d2) + d1) + y0;
+}
+
+// dao_value.py:95-107 for one point that already passed the edge guard.
+BP_HD double psf_value(double xx, double yy, const double* gauss, const double* psf, int npsf,
+                       double* dvdx, double* dvdy) {
+    const double half = (double)(npsf - 1) / 2.;
+    double p1, p2, dfdx, dfdy;
+    const double e = daoerf_xy(xx, yy, gauss, &p1, &p2);
+    const double v = rinter(psf, npsf, npsf, 2. * xx + half, 2. * yy + half, &dfdx, &dfdy);
+    *dvdx = 2. * dfdx - p1;
+    *dvdy = 2. * dfdy - p2;
+    return e + v;
+}
+
+// ------------------------------------------------------------ 3x3 inverse
+// What scipy.linalg.inv does to the normal matrix: Cholesky (potrf + potri) when the matrix is
+// symmetric and positive definite, LU with partial pivoting (getrf + getri) otherwise.
+// Returns 0 on success, 1 when singular (scipy raises LinAlgError -> the fit returns NaN).
+BP_HD int inv3(double c[3][3]) {
+    bool sym = (c[0][1] == c[1][0]) && (c[0][2] == c[2][0]) && (c[1][2] == c[2][1]);
+    if (sym) {
+        double l00, l10, l20, l11, l21, l22;
+        double s = c[0][0];
+        if (s > 0.0) {
+            l00 = sqrt(s);
+            l10 = c[1][0] / l00;
+            l20 = c[2][0] / l00;
+            s = c[1][1] - l10 * l10;
+            if (s > 0.0) {
+                l11 = sqrt(s);
+                l21 = (c[2][1] - l20 * l10) / l11;
+                s = c[2][2] - l20 * l20;
+                s = s - l21 * l21;
+                if (s > 0.0) {
+                    l22 = sqrt(s);
+                    // M = inv(L), lower triangular; inv(A) = M^T M
+                    const double m00 = 1.0 / l00, m11 = 1.0 / l11, m22 = 1.0 / l22;
+                    const double m10 = -(l10 * m00) / l11;
+                    const double m21 = -(l21 * m11) / l22;
+                    double t = 0.0 + l20 * m00;
+                    t = t + l21 * m10;
+                    const double m20 = -t / l22;
+                    double a00 = 0.0 + m00 * m00; a00 = a00 + m10 * m10; a00 = a00 + m20 * m20;
+                    double a01 = 0.0 + m10 * m11; a01 = a01 + m20 * m21;
+                    const double a02 = 0.0 + m20 * m22;
+                    double a11 = 0.0 + m11 * m11; a11 = a11 + m21 * m21;
+                    const double a12 = 0.0 + m21 * m22;
+                    const double a22 = 0.0 + m22 * m22;
+                    c[0][0] = a00; c[0][1] = a01; c[0][2] = a02;
+                    c[1][0] = a01; c[1][1] = a11; c[1][2] = a12;
+                    c[2][0] = a02; c[2][1] = a12; c[2][2] = a22;
+                    return 0;
+                }
+            }
+        }
+    }
+    // LU with partial pivoting, then inv(U) and the getri back-substitution.
+    double a[3][3];
+    int piv[3];
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) a[i][j] = c[i][j];
+    for (int j = 0; j < 3; j++) {
+        int p = j;
+        double best = fabs(a[j][j]);
+        for (int i = j + 1; i < 3; i++)
+            if (fabs(a[i][j]) > best) { best = fabs(a[i][j]); p = i; }
+        piv[j] = p;
+        if (a[p][j] == 0.0) return 1;
+        if (p != j)
+            for (int k = 0; k < 3; k++) { const double t = a[j][k]; a[j][k] = a[p][k]; a[p][k] = t; }
+        for (int i = j + 1; i < 3; i++) a[i][j] = a[i][j] / a[j][j];
+        for (int i = j + 1; i < 3; i++)
+            for (int k = j + 1; k < 3; k++) a[i][k] = a[i][k] - a[i][j] * a[j][k];
+    }
+    for (int j = 0; j < 3; j++) {  // inv(U) in place (trti2)
+        a[j][j] = 1.0 / a[j][j];
+        const double ajj = -a[j][j];
+        for (int jj = 0; jj < j; jj++) {
+            const double t = a[jj][j];
+            for (int i = 0; i < jj; i++) a[i][j] = a[i][j] + t * a[i][jj];
+            a[jj][j] = t * a[jj][jj];
+        }
+        for (int i = 0; i < j; i++) a[i][j] = a[i][j] * ajj;
+    }
+    for (int j = 2; j >= 0; j--) {  // inv(A) L = inv(U) (getri)
+        double w[3] = {0., 0., 0.};
+        for (int i = j + 1; i < 3; i++) { w[i] = a[i][j]; a[i][j] = 0.0; }
+        for (int k = j + 1; k < 3; k++)
+            for (int i = 0; i < 3; i++) a[i][j] = a[i][j] - a[i][k] * w[k];
+    }
+    for (int j = 1; j >= 0; j--) {
+        const int p = piv[j];
+        if (p != j)
+            for (int i = 0; i < 3; i++) { const double t = a[i][j]; a[i][j] = a[i][p]; a[i][p] = t; }
+    }
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) c[i][j] = a[i][j];
+    return 0;
+}
+
+// ------------------------------------------------------------------- mmm
+// Sorted-vector searches.  `at(i)` widens element i to double.
+template <typename Get>
+BP_HD int lower_bound_ge(const Get& at, int n, double v) {  // first i with at(i) >= v (n if none)
+    int lo = 0, hi = n;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (at(mid) >= v) hi = mid; else lo = mid + 1;
+    }
+    return lo;
+}
+template <typename Get>
+BP_HD int upper_bound_gt(const Get& at, int n, double v) {  // first i with at(i) > v (n if none)
+    int lo = 0, hi = n;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (at(mid) > v) hi = mid; else lo = mid + 1;
+    }
+    return lo;
+}
+
+// mmm.py:199-215: where the one-index-at-a-time walk of the LOWER edge stops.  `minimm` is the
+// index just below the accepted set (may be -1).  Returns the new minimm; *moved = false when
+// the reference takes its "done" shortcut and leaves sum/sumsq untouched.
+// The walk stops at the first index i (stepping from minimm) with i == -1, i == nlast, or
+// at(i) <= cut1 <= at(i+1); in a sorted vector those i form [lb-1, ub-1].
+template <typename Get>
+BP_HD int mmm_walk_min(const Get& at, int nsky, int minimm, double cut1, bool* moved, bool* grew) {
+    const int nlast = nsky - 1;
+    const bool tst_min = at(minimm + 1) >= cut1;
+    *grew = tst_min;
+    bool done = (minimm == -1) && tst_min;
+    if (!done) {
+        const int k = minimm > 0 ? minimm : 0;
+        if (at(k) < cut1 && tst_min) done = true;
+    }
+    *moved = !done;
+    if (done) return minimm;
+    if (tst_min) {  // grow downward: first i <= minimm-1 inside the bracket set, else -1
+        const int b = upper_bound_gt(at, nsky, cut1) - 1;
+        int r = b < (minimm - 1) ? b : (minimm - 1);
+        return r < -1 ? -1 : r;
+    }
+    // shrink upward: first i >= minimm+1 inside the bracket set, else nlast
+    const int a = lower_bound_ge(at, nsky, cut1) - 1;
+    int r = a > (minimm + 1) ? a : (minimm + 1);
+    return r > nlast ? nlast : r;
+}
+
+// mmm.py:224-241: the UPPER edge.  `maximm` is the last accepted index.
+template <typename Get>
+BP_HD int mmm_walk_max(const Get& at, int nsky, int maximm, double cut2, bool* moved, bool* grew) {
+    const int nlast = nsky - 1;
+    const bool tst_max = at(maximm) <= cut2;
+    *grew = tst_max;
+    bool done = (maximm == nlast) && tst_max;
+    if (!done) {
+        const int k = (maximm + 1 < nlast) ? maximm + 1 : nlast;
+        if (tst_max && at(k) > cut2) done = true;
+    }
+    *moved = !done;
+    if (done) return maximm;
+    if (tst_max) {  // grow upward
+        const int a = lower_bound_ge(at, nsky, cut2) - 1;
+        int r = a > (maximm + 1) ? a : (maximm + 1);
+        return r > nlast ? nlast : r;
+    }
+    // shrink downward
+    const int b = upper_bound_gt(at, nsky, cut2) - 1;
+    int r = b < (maximm - 1) ? b : (maximm - 1);
+    return r < -1 ? -1 : r;
+}
+
+// mmm.py:106-314 on an already sorted, NaN-free vector of nsky elements.
+//   at(i)                         element i widened to double
+//   delta_sums(lo, hi, mid, &a, &q)  a = sum(at(i)-mid), q = sum((at(i)-mid)^2) over [lo, hi)
+//   plain_sum(lo, hi)             sum(at(i)) over [lo, hi)
+// The functors let a whole warp share the reductions on the device (every lane must receive the same
+// bits) and a plain loop stand in on the host (tests/hostcheck).  Failure modes keep the reference's
+// in-band codes (sigma = -1).
+struct MmmResult {
+    double skymod, sigma, skew;
+    int iters;
+};
+BP_HD double mmm_nan() { return (double)NAN; }
+
+template <typename Get, typename DSums, typename PSum>
+BP_HD MmmResult mmm_sorted(const Get& at, const DSums& delta_sums, const PSum& plain_sum, int nsky,
+                           double readnoise, int minsky, int mxiter) {
+    MmmResult R;
+    R.iters = 0;
+    R.skew = 0.0;
+    if (nsky < minsky) {  // mmm.py:109-112
+        R.skymod = mmm_nan(); R.sigma = -1.0;
+        return R;
+    }
+    const int nlast = nsky - 1;
+    const double skymid = 0.5 * at((nsky - 1) / 2) + 0.5 * at(nsky / 2);  // mmm.py:121
+    double cut1, cut2;
+    {
+        const double a = skymid - at(0), b = at(nlast) - skymid;  // mmm.py:123-127
+        const double c = a < b ? a : b;
+        cut2 = skymid + c;
+        cut1 = skymid - c;
+    }
+    const int gmin = lower_bound_ge(at, nsky, cut1);
+    const int gmax = upper_bound_gt(at, nsky, cut2) - 1;
+    if (gmin > gmax) {  // mmm.py:134-138
+        R.skymod = 0.0; R.sigma = -1.0;
+        return R;
+    }
+    double sum, sumsq;
+    delta_sums(gmin, gmax + 1, skymid, &sum, &sumsq);  // mmm.py:141-142
+    int maximm = gmax, minimm = gmin - 1;      // mmm.py:144-145
+    double skymed = 0.5 * at((int)((minimm + maximm + 1) / 2.0)) + 0.5 * at((int)((minimm + maximm) / 2.0 + 1));
+    double skymn = sum / (maximm - minimm);
+    double sigma = sqrt(sumsq / (maximm - minimm) - skymn * skymn);
+    skymn = skymn + skymid;
+    double skymod = (skymed < skymn) ? 3. * skymed - 2. * skymn : skymn;  // mmm.py:157-159
+
+    int niter = 0;
+    double clamp = 1.0, old = 0.0;
+    bool redo = true;
+    while (redo) {  // mmm.py:168-301
+        niter++;
+        if (niter > mxiter || (maximm - minimm) < minsky) {  // mmm.py:170-182
+            R.skymod = skymod; R.sigma = -1.0; R.iters = niter;
+            return R;
+        }
+        double r = log10((double)(maximm - minimm));  // mmm.py:186-187
+        const double r2 = (-0.1042 * r + 1.1695) * r + 0.8895;
+        r = 2. > r2 ? 2. : r2;
+        const double cut = r * sigma + 0.5 * fabs(skymn - skymod);  // mmm.py:191-193
+        cut1 = skymod - cut;
+        cut2 = skymod + cut;
+        redo = false;
+        bool moved, grew;
+        const int newmin = mmm_walk_min(at, nsky, minimm, cut1, &moved, &grew);  // mmm.py:199-222
+        if (moved) {
+            double s1, s2;
+            if (grew) {
+                delta_sums(newmin + 1, minimm + 1, skymid, &s1, &s2);
+                sum = sum + s1; sumsq = sumsq + s2;
+            } else {
+                delta_sums(minimm + 1, newmin + 1, skymid, &s1, &s2);
+                sum = sum - s1; sumsq = sumsq - s2;
+            }
+            redo = true;
+            minimm = newmin;
+        }
+        const int newmax = mmm_walk_max(at, nsky, maximm, cut2, &moved, &grew);  // mmm.py:224-248
+        if (moved) {
+            double s1, s2;
+            if (grew) {
+                delta_sums(maximm + 1, newmax + 1, skymid, &s1, &s2);
+                sum = sum + s1; sumsq = sumsq + s2;
+            } else {
+                delta_sums(newmax + 1, maximm + 1, skymid, &s1, &s2);
+                sum = sum - s1; sumsq = sumsq - s2;
+            }
+            redo = true;
+            maximm = newmax;
+        }
+        const int ns = maximm - minimm;  // mmm.py:253-257
+        if (ns < minsky) {
+            R.skymod = skymod; R.sigma = -1.0; R.iters = niter;
+            return R;
+        }
+        skymn = sum / ns;  // mmm.py:259-263
+        double var = sumsq / ns - skymn * skymn;
+        if (var < 0) var = 0;
+        sigma = sqrt(var);
+        skymn = skymn + skymid;
+        // robust median: mean of the central 20 % (mmm.py:271-289; np.round = half-to-even)
+        const double center = (minimm + 1 + maximm) / 2.;
+        const double side = rint(0.2 * (maximm - minimm)) / 2. + 0.25;
+        double j = rint(center - side), k = rint(center + side);
+        if (readnoise != 0.0) {  // mmm.py:280-287
+            const double L = rint(center - 0.25), M = rint(center + 0.25), Rn = 0.25 * readnoise;
+            while (j > 0 && k < ns - 1 && ((at((int)L) - at((int)j)) < Rn || (at((int)k) - at((int)M)) < Rn)) {
+                j -= 1; k += 1;
+            }
+        }
+        int ji = (int)j, ki = (int)k + 1;
+        if (ji < 0) ji = 0;
+        if (ki > nsky) ki = nsky;
+        skymed = plain_sum(ji, ki) / (k - j + 1);
+        const double dmod = (skymed < skymn) ? 3. * skymed - 2. * skymn - skymod : skymn - skymod;  // mmm.py:294-296
+        if (dmod * old < 0) clamp = 0.5 * clamp;  // mmm.py:299-301
+        skymod = skymod + clamp * dmod;
+        old = dmod;
+    }
+    R.skew = (skymn - skymod) / (sigma > 1. ? sigma : 1.);  // mmm.py:306
+    R.skymod = skymod; R.sigma = sigma; R.iters = niter;
+    return R;
+}
+
+}  // namespace bphot

@@ -1,0 +1,69 @@
+// bphot_params.h -- kernel argument blocks (plain data, passed by value to the kernels).
+#pragma once
+#include <stdint.h>
+
+#define BPHOT_MAX_APER 16
+
+namespace bphot {
+
+struct AperParams {
+    // image: [nrow, ncol] row-major, x = column; `pitch` = elements between rows
+    const void* img;
+    int nrow, ncol;
+    long long pitch;
+    // star list
+    const double* xc;
+    const double* yc;
+    int nstars;
+    // aper.py:26-29 keywords
+    double phpadu, zeropoint;
+    double apr[BPHOT_MAX_APER];
+    int naper;
+    double skyrad_in, skyrad_out;  // already [0, max(apr)+1] when use_setsky (aper.py:156-160)
+    double badlo, badhi;
+    int use_setsky;
+    double setsky[3];
+    int minsky, exact, compat_py2, mxiter;
+    double readnoise;
+    int sort_cap;  // power of two >= the largest possible annulus pixel count
+    // outputs
+    double* mag;      // [nstars, naper]
+    double* magerr;   // [nstars, naper]
+    double* flux;     // [nstars, naper]
+    double* fluxerr;  // [nstars, naper]
+    double* sky;      // [nstars]
+    double* skyerr;   // [nstars]
+    uint8_t* badflag; // [nstars, naper]
+    int* nsky;        // [nstars]  sky pixels handed to mmm (aper.py:267)
+    int* mmm_iter;    // [nstars]  mmm clipping iterations
+};
+
+struct PkfitParams {
+    int variant;  // 0 pkfit.py, 1 pkfit_noise.py, 2 pkfit_norecent_noise.py
+    const void* img;
+    const void* noise;
+    const uint8_t* mask;
+    int nrow, ncol;
+    long long pitch, npitch, mpitch;
+    double gauss[5];
+    const double* psf;  // [npsf, npsf] fp64, device
+    int npsf;
+    double ronois, phpadu, radius;
+    int maxiter, recenter;
+    const double* scale;
+    const double* x;
+    const double* y;
+    const double* sky;
+    int nstars;
+    int cap;  // per-star pixel-list capacity
+    double* errmag;
+    double* chi;
+    double* sharp;
+    int* niter;
+    double* scale_out;
+    double* x_out;
+    double* y_out;
+    double* chi2;
+};
+
+}  // namespace bphot

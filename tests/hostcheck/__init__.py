@@ -1,0 +1,55 @@
+"""ctypes front-end of tests/hostcheck/hostcheck.cpp (TEST INFRASTRUCTURE: the kernels' shared
+scalar header compiled for the host, so its arithmetic can be checked without a GPU)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libhostcheck.so")
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        src = os.path.join(_HERE, "hostcheck.cpp")
+        hdr = os.path.join(_HERE, "..", "..", "pythonphot_b200", "csrc", "bphot_math.cuh")
+        if (not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(src), os.path.getmtime(hdr))):
+            subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-x", "c++",
+                                   "-shared", "-o", _SO, src])
+        _lib = C.CDLL(_SO)
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def pixwt(xc, yc, r, x, y):
+    x = np.ascontiguousarray(x, np.float64); y = np.ascontiguousarray(y, np.float64)
+    out = np.empty_like(x)
+    lib().hc_pixwt(C.c_double(xc), C.c_double(yc), C.c_double(r), _p(x), _p(y), C.c_int(x.size), _p(out))
+    return out
+
+
+def psfmodel(xx, yy, gauss, psf):
+    xx = np.ascontiguousarray(xx, np.float64); yy = np.ascontiguousarray(yy, np.float64)
+    gauss = np.ascontiguousarray(gauss, np.float64); psf = np.ascontiguousarray(psf, np.float64)
+    out = np.empty((12, xx.size))
+    lib().hc_psfmodel(_p(xx), _p(yy), C.c_int(xx.size), _p(gauss), _p(psf), C.c_int(psf.shape[1]), _p(out))
+    return out
+
+
+def inv3(c):
+    c = np.array(c, dtype=np.float64, order="C")
+    st = lib().hc_inv3(_p(c))
+    return c, st
+
+
+def mmm(v, readnoise=0.0, minsky=20, mxiter=50):
+    v = np.ascontiguousarray(np.asarray(v).ravel(), np.float64)
+    out = np.empty(3)
+    it = lib().hc_mmm(_p(v), C.c_int(v.size), C.c_double(readnoise), C.c_int(minsky), C.c_int(mxiter), _p(out))
+    return out[0], out[1], out[2], it

@@ -1,0 +1,64 @@
+"""CPU-side checks of the boundary: the C-ABI library loads and exports every symbol include/bphot.h
+declares; the package fails loudly without a GPU (no CPU fallback).  No compute calls."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from pythonphot_b200 import _lib
+    _lib.build()
+    return _lib
+
+
+def test_exports_match_header(lib):
+    hdr = open(os.path.join(ROOT, "include", "bphot.h")).read()
+    declared = set(re.findall(r"^\s*(?:int|long long|const char\*)\s+(bphot_\w+)\s*\(", hdr, flags=re.M))
+    assert declared, "no declarations parsed from include/bphot.h"
+    handle = ctypes.CDLL(lib.SO_PATH)
+    for name in sorted(declared):
+        assert hasattr(handle, name), "libbphot.so does not export %s" % name
+    assert declared == set(lib.EXPORTS), "python binding table and header disagree: %s" % (declared ^ set(lib.EXPORTS))
+
+
+def test_version_and_constants(lib):
+    h = lib.lib()
+    hdr = open(os.path.join(ROOT, "include", "bphot.h")).read()
+    assert h.bphot_version() == int(re.search(r"#define BPHOT_VERSION (\d+)", hdr).group(1))
+    assert int(re.search(r"#define BPHOT_MAX_APERTURES (\d+)", hdr).group(1)) == lib.MAX_APERTURES
+    assert h.bphot_launch_count() == 0
+
+
+def test_no_cpu_fallback(lib):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    import pythonphot_b200 as pp
+    img = np.zeros((64, 64), np.float32)
+    with pytest.raises(lib.BphotError):
+        pp.aper.aper(img, [30.0], [30.0], verbose=False)
+    with pytest.raises(lib.BphotError):
+        pp.pkfit_class(img, np.ones(5), np.zeros((41, 41)), 1.0, 1.0)
+    with pytest.raises(lib.BphotError):
+        pp.mmm.mmm(np.arange(100.0))
+    # the host-buffer C entry point reports "no device" instead of computing anything
+    z = np.zeros(1)
+    rc = lib.lib().bphot_aper_host(lib.nptr(img), 0, 64, 64, lib.nptr(z), lib.nptr(z), 1, 1.0, lib.nptr(z), 1, 25.0, 40.0, 50.0,
+                                   0.0, 0.0, 0, None, 20, 1, 0.0, 0, lib.nptr(z), lib.nptr(z), lib.nptr(z), lib.nptr(z),
+                                   lib.nptr(z), lib.nptr(z), lib.nptr(z), None, None, 0)
+    assert rc == -4
+
+
+def test_product_package_does_not_import_oracle():
+    pkg = os.path.join(ROOT, "pythonphot_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, fn)).read()
+                assert "oracle" not in src.replace("# oracle", ""), "%s mentions the oracle" % fn

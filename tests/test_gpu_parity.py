@@ -1,0 +1,343 @@
+"""Parity of the CUDA path (through libbphot's C ABI) against the golden vectors of the unmodified
+reference and against the CPU oracle on seeded synthetic fields.  Needs a B200: `pytest -m gpu`.
+
+Tolerances (north_star): counts / flags / iteration numbers bit-exact; fp64 quantities 1e-9 relative.
+Aperture fluxes are differences of ~1e4..1e6-ADU sums, so they additionally get an absolute 1e-7 ADU
+(1e-11 of the summed counts)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from tests.conftest import assert_close, load_golden
+from tests.golden.cases import APER_CASES
+
+pytestmark = pytest.mark.gpu
+
+NAMES = ("mag", "magerr", "flux", "fluxerr", "sky", "skyerr", "badflag")
+
+
+@pytest.fixture(scope="module")
+def pp():
+    import pythonphot_b200
+    pythonphot_b200._lib.torch_cuda()
+    return pythonphot_b200
+
+
+@pytest.fixture(scope="module")
+def oracle():
+    from oracle import oracle as o
+    return o
+
+
+# ------------------------------------------------------------------ device math vs goldens
+def test_pixwt_golden(pp):
+    g = load_golden("golden_pixwt.npz")
+    for i in range(g["xc"].size):
+        m = g["pid"] == i
+        w = pp.pixwt.Pixwt(g["xc"][i], g["yc"][i], g["r"][i], g["x"][m], g["y"][m])
+        assert_close(w, g["w"][m], rtol=1e-12, atol=1e-12, what="pixwt %d" % i)
+    assert_close(pp.pixwt.Pixwt(3.5, 3.5, 2.0, g["half_x"], g["half_y"]), g["half_w"], rtol=1e-12, atol=1e-12)
+    assert abs(pp.pixwt.Pixwt(3.23, 4.22, 3.44, 5, 7) - 0.6502) < 5e-5  # pixwt.py:25-30
+
+
+def test_psfmodel_golden(pp):
+    g = load_golden("golden_psfmodel.npz")
+    f, pder = pp.daoerf.daoerf(g["xx"], g["yy"], g["gauss"])
+    assert_close(f, g["f"], rtol=1e-11, atol=1e-300, what="daoerf f")
+    assert_close(pder, g["pder"], rtol=1e-10, atol=1e-11, what="daoerf pder")
+    half = (g["psf"].shape[0] - 1) / 2.0
+    z, dx, dy = pp.rinter.rinter(g["psf"], 2 * g["xx"] + half, 2 * g["yy"] + half, deriv=True)
+    assert_close(z, g["z"], rtol=1e-12, atol=1e-12, what="rinter z")
+    assert_close(dx, g["dfdx"], rtol=1e-12, atol=1e-12, what="rinter dfdx")
+    assert_close(dy, g["dfdy"], rtol=1e-12, atol=1e-12, what="rinter dfdy")
+    v, dvx, dvy = pp.dao_value.dao_value(g["xx"], g["yy"], g["gauss"], g["psf"], deriv=True)
+    assert_close(v, g["v"], rtol=1e-11, atol=1e-11, what="dao_value")
+    assert_close(dvx, g["dvx"], rtol=1e-10, atol=1e-10, what="dvdx")
+    assert_close(dvy, g["dvy"], rtol=1e-10, atol=1e-10, what="dvdy")
+    ve = pp.dao_value.dao_value(g["xe"], g["yy"][:10], g["gauss"], g["psf"], deriv=False)
+    assert np.all(ve == 0.0)  # dao_value.py:70-84
+
+
+def test_mmm_golden(pp):
+    g = load_golden("golden_mmm.npz")
+    off = 0
+    for n, out in zip(g["lens"], g["out"]):
+        v = g["vec"][off:off + n]
+        off += n
+        got = pp.mmm.mmm(v, readnoise=out[3], minsky=int(out[4]))
+        assert_close(got, out[:3], rtol=1e-10, atol=1e-10, what="mmm n=%d" % n)
+
+
+def test_mmm_batch_vs_oracle_ties(pp, oracle):
+    rng = np.random.default_rng(77)
+    vecs = []
+    for t in range(400):
+        n = int(rng.integers(20, 3000))
+        v = np.round(rng.normal(300, rng.uniform(0.5, 8), n)) if t % 2 else rng.normal(300, 9, n)
+        v[rng.integers(0, n, n // 10 + 1)] += np.round(rng.exponential(300, n // 10 + 1))
+        vecs.append(v.astype(np.float32) if t % 3 == 0 else v)
+    vecs32 = [v.astype(np.float32) for v in vecs]
+    for batch in (vecs, vecs32):
+        got, iters = pp.mmm.mmm_batch(batch, return_iters=True)
+        for i, v in enumerate(batch):
+            want = oracle.mmm(v.astype(np.float64), return_info=True)
+            assert iters[i] == want[3], "mmm iterations differ for vector %d" % i
+            assert_close(got[i], want[:3], rtol=1e-10, atol=1e-10, what="mmm vec %d" % i)
+
+
+# ------------------------------------------------------------------ aper vs the reference's goldens
+def _check_aper(got, want, fragile, what, nsky=None, want_nsky=None):
+    """got/want: dicts of arrays.  badflag bit-exact except where the reference's own flag hinges on
+    rounding noise (`fragile`, see oracle/bphot_oracle.c); values compared where flags agree."""
+    gb, wb = got["badflag"].astype(bool), want["badflag"].astype(bool)
+    mism = gb != wb
+    assert not (mism & ~fragile).any(), "%s: badflag differs on %d robust apertures" % (what, (mism & ~fragile).sum())
+    ok = ~mism
+    for nm in ("flux", "fluxerr", "mag", "magerr"):
+        atol = 1e-7 if nm in ("flux", "fluxerr") else 1e-9
+        assert_close(got[nm][ok], want[nm][ok], rtol=1e-9, atol=atol, what="%s %s" % (what, nm))
+    assert_close(got["sky"], want["sky"], rtol=1e-9, atol=1e-9, what=what + " sky")
+    assert_close(got["skyerr"], want["skyerr"], rtol=1e-9, atol=1e-9, what=what + " skyerr")
+    if nsky is not None:
+        assert np.array_equal(nsky, want_nsky), what + ": nsky differs"
+    return int(mism.sum())
+
+
+@pytest.mark.parametrize("mode", ["py3", "py2"])
+@pytest.mark.parametrize("cname", [c[0] for c in APER_CASES])
+def test_aper_golden(pp, oracle, mode, cname):
+    g = load_golden("golden_aper.npz")
+    kw = dict(dict(APER_CASES)[cname])
+    if mode == "py2" and not kw.get("exact"):
+        pytest.skip("py2 == py3 for exact=False")
+    r = pp.aper.aper(g["image"], g["x"], g["y"], phpadu=float(g["phpadu"]), zeropoint=25.0, verbose=False,
+                     compat=mode, return_info=True, **kw)
+    got = dict(zip(NAMES, r[:7]))
+    n = g["x"].size
+    for k in ("mag", "magerr", "flux", "fluxerr", "badflag"):
+        got[k] = np.asarray(got[k]).reshape(n, -1)
+    want = {nm: g["%s__%s__%s" % (mode, cname, nm)] for nm in NAMES}
+    o = oracle.aper(g["image"], g["x"], g["y"], phpadu=float(g["phpadu"]), zeropoint=25.0, compat=mode,
+                    return_extra=True, **kw)
+    nm = _check_aper(got, want, o[-1], "%s/%s" % (mode, cname), r[8]["nsky"], o[7])
+    assert np.array_equal(r[8]["mmm_iter"], o[8]), "mmm iteration counts differ"
+    print("fragile apertures: %d, of which flag differs: %d" % (o[-1].sum(), nm))
+
+
+def test_aper_scalar_star_squeezes(pp):
+    g = load_golden("golden_aper.npz")
+    r = pp.aper.aper(g["image"], float(g["x"][3]), float(g["y"][3]), phpadu=float(g["phpadu"]), apr=5.0,
+                     skyrad=[40, 50], badpix=[-12000, 60000], exact=True, verbose=False)
+    assert np.shape(r[0]) == (1,) and np.shape(r[4]) == () and isinstance(r[7], str)  # aper.py:419-427
+
+
+# ------------------------------------------------------------------ aper vs the oracle, larger fields
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("exact,compat", [(True, "py3"), (True, "py2"), (False, "py3")])
+def test_aper_vs_oracle_field(pp, oracle, dtype, exact, compat):
+    from pythonphot_b200 import synth
+    f = synth.make_field(700, 900, 3000, seed=31, dtype=dtype, with_noise=False, edge_frac=0.03)
+    kw = dict(phpadu=f["phpadu"], apr=np.array([3., 5., 8.]), zeropoint=25.0, skyrad=[40, 50],
+              badpix=[-12000, 60000], exact=exact)
+    r = pp.aper.aper(f["image"], f["x"], f["y"], verbose=False, compat=compat, return_info=True, **kw)
+    got = dict(zip(NAMES, r[:7]))
+    o = oracle.aper(f["image"], f["x"], f["y"], compat=compat, nthreads=0, return_extra=True, **kw)
+    want = dict(zip(NAMES, o[:7]))
+    nm = _check_aper(got, want, o[-1], "field %s exact=%s %s" % (np.dtype(dtype).name, exact, compat), r[8]["nsky"], o[7])
+    assert np.array_equal(r[8]["mmm_iter"], o[8])
+    print("fragile: %d mismatching: %d of %d" % (o[-1].sum(), nm, o[-1].size))
+
+
+def test_aper_edge_matrix(pp, oracle):
+    """Branches of aper.py: off-frame, edge < apr, nsky < minsky, NaN in annulus / aperture, all-NaN."""
+    rng = np.random.default_rng(3)
+    img = rng.normal(100, 5, (160, 180))
+    img[60:70, 60:70] = np.nan           # NaNs inside an aperture
+    img[100:104, 20:90] = 70000.0        # saturated streak through annuli
+    img[:, 150:] = np.nan                # a whole region of NaN: nsky after NaN drop < minsky
+    x = np.array([-5.0, 0.4, 0.6, 2.0, 90.0, 65.0, 64.2, 30.0, 178.6, 179.0, 165.0, 90.0, 12.5, np.nan])
+    y = np.array([50.0, 50.0, 50.0, 3.0, 80.0, 65.0, 60.1, 102.0, 80.0, 80.0, 80.0, 158.9, 12.5, 20.0])
+    for kw in (dict(apr=np.array([2., 4., 7.]), skyrad=[10, 15], badpix=[-100, 60000], exact=True),
+               dict(apr=np.array([2., 4., 7.]), skyrad=[10, 15], badpix=[0, 0], exact=False),
+               dict(apr=np.array([3.]), skyrad=[3, 5], badpix=[-100, 60000], exact=True, minsky=60),
+               dict(apr=np.array([2., 3.]), skyrad=[10, 15], badpix=[-100, 60000], exact=True, setskyval=99.0)):
+        r = pp.aper.aper(img, x, y, phpadu=2.0, verbose=False, return_info=True, **kw)
+        o = oracle.aper(img, x, y, phpadu=2.0, return_extra=True, **kw)
+        _check_aper(dict(zip(NAMES, r[:7])), dict(zip(NAMES, o[:7])), o[-1], "edge %r" % (kw,), r[8]["nsky"], o[7])
+
+
+def test_aper_properties_full_size(pp):
+    """BASELINE config 3 shape (4096^2, 100k stars): power-of-two scaling is exact in fp64, a star-list
+    permutation permutes results bit-for-bit, and a constant image integrates to pi r^2 (Pixwt closure)."""
+    from pythonphot_b200 import synth
+    f = synth.make_field(4096, 4096, 100000, seed=1003, dtype=np.float32, with_noise=False)
+    kw = dict(phpadu=f["phpadu"], apr=np.array([3., 5., 8.]), skyrad=[40, 50], badpix=[-12000, 60000], exact=True,
+              verbose=False)
+    a = pp.aper.aper(f["image"], f["x"], f["y"], **kw)
+    kw2 = dict(kw, badpix=[-24000, 120000])
+    b = pp.aper.aper(f["image"] * np.float32(2), f["x"], f["y"], **kw2)
+    assert np.array_equal(np.nan_to_num(b[2], nan=-1.0), np.nan_to_num(2 * a[2], nan=-1.0)), "flux not linear"
+    assert np.array_equal(np.nan_to_num(b[4], nan=-1.0), np.nan_to_num(2 * a[4], nan=-1.0)), "sky not linear"
+    assert np.array_equal(a[6], b[6])
+    perm = np.random.default_rng(0).permutation(f["x"].size)
+    c = pp.aper.aper(f["image"], f["x"][perm], f["y"][perm], **kw)
+    for i in (0, 1, 2, 3, 4, 5, 6):
+        assert np.array_equal(np.nan_to_num(c[i], nan=-1.0), np.nan_to_num(a[i][perm], nan=-1.0)), "permutation changed output %d" % i
+    const = np.full((512, 512), 7.0, dtype=np.float32)
+    xs = np.random.default_rng(1).uniform(60, 450, 500)
+    ys = np.random.default_rng(2).uniform(60, 450, 500)
+    for compat in ("py3", "py2"):
+        d = pp.aper.aper(const, xs, ys, phpadu=1, apr=np.array([2., 3., 5., 8.]), skyrad=[40, 50], exact=True,
+                         setskyval=0.0, verbose=False, compat=compat)
+        area = np.pi * np.array([2., 3., 5., 8.]) ** 2
+        assert np.abs(d[2] / (7.0 * area) - 1).max() < 1e-9
+
+
+# ------------------------------------------------------------------ pkfit vs the reference's goldens
+PK_COLS = {"norecent": ("errmag", "chi", "sharp", "niter", "scale", "chi2"),
+           "noise": ("errmag", "chi", "sharp", "niter", "scale", "x", "y"),
+           "pkfit_rec": ("errmag", "chi", "sharp", "niter", "scale", "x", "y"),
+           "pkfit_norec": ("errmag", "chi", "sharp", "niter", "scale", "x", "y")}
+
+
+def _run_pk(pp, kind, g_or_f, scale, x, y, sky, radius, image, noise, mask):
+    gauss, psf, ron, ph = g_or_f["gauss"], g_or_f["psf"], float(g_or_f["ronois"]), float(g_or_f["phpadu"])
+    if kind == "norecent":
+        pk = pp.pkfit_norecent_noise.pkfit_class(image, gauss, psf, ron, ph, noise, mask)
+        r = pk.pkfit_norecent_noise(scale, x, y, sky, radius, returnchi2=True)
+        return dict(zip(PK_COLS[kind], r))
+    if kind == "noise":
+        pk = pp.pkfit_noise.pkfit_class(image, gauss, psf, ron, ph, noise, mask)
+        return dict(zip(PK_COLS[kind], pk.pkfit_noise(scale, x, y, sky, radius, xyout=True)))
+    pk = pp.pkfit.pkfit_class(image, gauss, psf, ron, ph)
+    return dict(zip(PK_COLS[kind], pk.pkfit(scale, x, y, sky, radius, xyout=True, recenter=(kind == "pkfit_rec"))))
+
+
+def _check_pk(got, want, cols, x, y, shape, what):
+    """want: dict of arrays (NaN = column dropped by a reference early return, only for x/y/chi2)."""
+    assert np.array_equal(got["niter"], want["niter"].astype(np.int32)), \
+        "%s: niter differs at %s" % (what, np.nonzero(got["niter"] != want["niter"])[0][:8])
+    ny_, nx_ = shape
+    off = ~((x >= 0) & (x <= nx_ - 1) & (y >= 0) & (y <= ny_ - 1))
+    for nm in cols:
+        if nm == "niter":
+            continue
+        a, w = got[nm], want[nm]
+        keep = np.ones(a.size, bool)
+        if nm in ("x", "y", "chi2"):
+            keep = ~np.isnan(w)
+        if nm == "sharp":
+            # off-frame stars see only the far Gaussian tail: erf implementations differ at ~1e-9 there
+            assert_close(a[keep & off], w[keep & off], rtol=1e-6, atol=1e-12, what=what + " sharp(off-frame)")
+            keep = keep & ~off
+        assert_close(a[keep], w[keep], rtol=1e-9, atol=1e-12, what="%s %s" % (what, nm))
+
+
+@pytest.mark.parametrize("radius", [3.0, 5.0])
+@pytest.mark.parametrize("kind", list(PK_COLS))
+def test_pkfit_golden(pp, kind, radius):
+    g = load_golden("golden_pkfit.npz")
+    want_rows = g["%s__r%d" % (kind, radius)]
+    want = {c: want_rows[:, j] for j, c in enumerate(PK_COLS[kind])}
+    got = _run_pk(pp, kind, g, g["scale0"], g["x"], g["y"], g["sky"], radius, g["image"], g["noise"], g["mask"])
+    _check_pk(got, want, PK_COLS[kind], g["x"], g["y"], g["image"].shape, "%s r=%g" % (kind, radius))
+
+
+def test_pkfit_scalar_call_returns_scalars(pp):
+    g = load_golden("golden_pkfit.npz")
+    pk = pp.pkfit_class(g["image"], g["gauss"], g["psf"], float(g["ronois"]), float(g["phpadu"]), g["noise"], g["mask"])
+    r = pk.pkfit_norecent_noise(float(g["scale0"][0]), float(g["x"][0]), float(g["y"][0]), float(g["sky"][0]), 3.0)
+    assert len(r) == 5 and isinstance(r[3], int) and isinstance(r[4], float)
+    want = g["norecent__r3"][0]
+    assert r[3] == int(want[3]) and abs(r[4] - want[4]) <= 1e-9 * abs(want[4])
+    r2 = pk.pkfit_noise(float(g["scale0"][0]), float(g["x"][0]), float(g["y"][0]), float(g["sky"][0]), 3.0, xyout=True)
+    assert len(r2) == 7
+    r3 = pk.pkfit(float(g["scale0"][0]), float(g["x"][0]), float(g["y"][0]), float(g["sky"][0]), 3.0)
+    assert len(r3) == 5
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("kind,radius", [("norecent", 5.0), ("noise", 5.0), ("pkfit_rec", 3.0), ("norecent", 2.2)])
+def test_pkfit_vs_oracle_field(pp, oracle, dtype, kind, radius):
+    from pythonphot_b200 import synth
+    f = synth.make_field(600, 800, 4000, seed=41, dtype=dtype, edge_frac=0.03, margin=10.0)
+    n = f["x"].size
+    scale0 = f["scale"] * np.where(np.arange(n) % 2 == 0, 1.0, 0.5)
+    sky = np.full(n, f["sky"])
+    x, y = f["xfit"].copy(), f["yfit"].copy()
+    x[7] = np.nan
+    got = _run_pk(pp, kind, f, scale0, x, y, sky, radius, f["image"], f["noise"], f["mask"])
+    variant = {"norecent": oracle.PKFIT_NORECENT, "noise": oracle.PKFIT_NOISE, "pkfit_rec": oracle.PKFIT}[kind]
+    want = oracle.pkfit(variant, f["image"], f["gauss"], f["psf"], f["ronois"], f["phpadu"], f["noise"], f["mask"],
+                        scale0, x, y, sky, radius, recenter=True, nthreads=0)
+    _check_pk(got, want, PK_COLS[kind], x, y, f["image"].shape, "field %s %s r=%g" % (np.dtype(dtype).name, kind, radius))
+
+
+def test_pkfit_properties_full_size(pp):
+    """BASELINE config 4 shape (8192^2, 1M stars, forced fits, radius 5): a permutation of the star list
+    permutes the results bit-for-bit; converged fits recover the planted scale; niter within [1, 25]."""
+    from pythonphot_b200 import synth
+    f = synth.make_field(8192, 8192, 1000000, seed=1004, dtype=np.float32)
+    n = f["x"].size
+    pk = pp.pkfit_class(f["image"], f["gauss"], f["psf"], f["ronois"], f["phpadu"], f["noise"], f["mask"])
+    sky = np.full(n, f["sky"])
+    one = np.ones(n)
+    a = pk.pkfit_norecent_noise(one, f["xfit"], f["yfit"], sky, 5.0)
+    perm = np.random.default_rng(0).permutation(n)
+    b = pk.pkfit_norecent_noise(one, f["xfit"][perm], f["yfit"][perm], sky, 5.0)
+    for i in range(5):
+        assert np.array_equal(np.nan_to_num(b[i], nan=-1.0), np.nan_to_num(a[i][perm], nan=-1.0))
+    niter = a[3]
+    assert niter.min() >= 0 and niter.max() <= 25
+    good = np.isfinite(a[4]) & (f["scale"] > 20) & (a[0] < 0.05)
+    rel = np.abs(a[4][good] / f["scale"][good] - 1)
+    assert good.sum() > 0.3 * n and np.median(rel) < 0.05
+
+
+# ------------------------------------------------------------------ the host-buffer C ABI entry points
+def test_c_abi_host_entry_points(pp, oracle):
+    from pythonphot_b200 import _lib, synth
+    f = synth.make_field(300, 320, 200, seed=5, dtype=np.float32, margin=55.0)
+    lib = _lib.lib()
+    n, apr = f["x"].size, np.array([3.0, 6.0])
+    na = apr.size
+    outs = [np.empty((n, na)) for _ in range(4)]
+    sky, skyerr = np.empty(n), np.empty(n)
+    bad = np.empty((n, na), np.uint8)
+    nsky, it = np.empty(n, np.int32), np.empty(n, np.int32)
+    img = np.ascontiguousarray(f["image"])
+    p = _lib.nptr
+    rc = lib.bphot_aper_host(p(img), _lib.F32, img.shape[0], img.shape[1], p(f["x"]), p(f["y"]), n, f["phpadu"], p(apr), na,
+                             25.0, 40.0, 50.0, -12000.0, 60000.0, 0, None, 20, 1, 0.0, 0,
+                             p(outs[0]), p(outs[1]), p(outs[2]), p(outs[3]), p(sky), p(skyerr), p(bad), p(nsky), p(it), 0)
+    _lib.check(rc)
+    o = oracle.aper(img, f["x"], f["y"], phpadu=f["phpadu"], apr=apr, skyrad=(40, 50), badpix=(-12000, 60000), exact=True,
+                    return_extra=True)
+    got = dict(mag=outs[0], magerr=outs[1], flux=outs[2], fluxerr=outs[3], sky=sky, skyerr=skyerr, badflag=bad)
+    _check_aper(got, dict(zip(NAMES, o[:7])), o[-1], "bphot_aper_host", nsky, o[7])
+
+    res = {k: np.empty(n) for k in ("errmag", "chi", "sharp", "scale", "x", "y", "chi2")}
+    niter = np.empty(n, np.int32)
+    nz, mk = np.ascontiguousarray(f["noise"]), np.ascontiguousarray(f["mask"])
+    sc, skyv = np.ones(n), np.full(n, f["sky"])
+    rc = lib.bphot_pkfit_host(_lib.PKFIT_NORECENT, p(img), _lib.F32, p(nz), _lib.F32, p(mk), img.shape[0], img.shape[1],
+                              p(f["gauss"]), p(f["psf"]), f["psf"].shape[1], f["ronois"], f["phpadu"],
+                              p(sc), p(f["xfit"]), p(f["yfit"]), p(skyv), 4.0, 25, 0, n,
+                              p(res["errmag"]), p(res["chi"]), p(res["sharp"]), p(niter), p(res["scale"]), p(res["x"]),
+                              p(res["y"]), p(res["chi2"]), 0)
+    _lib.check(rc)
+    res["niter"] = niter
+    want = oracle.pkfit(oracle.PKFIT_NORECENT, img, f["gauss"], f["psf"], f["ronois"], f["phpadu"], nz, mk, sc, f["xfit"],
+                        f["yfit"], skyv, 4.0)
+    _check_pk(res, want, PK_COLS["norecent"], f["xfit"], f["yfit"], img.shape, "bphot_pkfit_host")
+
+
+def test_c_abi_errors_are_reported(pp):
+    from pythonphot_b200 import _lib
+    lib = _lib.lib()
+    rc = lib.bphot_aper_device(None, 0, 10, 10, 10, None, None, 1, 1.0, None, 1, 25.0, 40.0, 50.0, 0.0, 0.0, 0, None,
+                               20, 1, 0.0, 0, None, None, None, None, None, None, None, None, None, None)
+    assert rc == -1 and b"null" in lib.bphot_last_error()
+    with pytest.raises(_lib.BphotError):  # annulus too large for one CTA's shared memory
+        pp.aper.aper(np.zeros((64, 64), np.float32), [30.0], [30.0], skyrad=[100, 400], verbose=False)

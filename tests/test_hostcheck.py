@@ -1,0 +1,79 @@
+"""The kernels' shared scalar header (bphot_math.cuh), compiled for the host, against the golden
+vectors of the unmodified reference and against the oracle on adversarial inputs.  CPU only."""
+import numpy as np
+import pytest
+
+from oracle import oracle
+from tests import hostcheck
+from tests.conftest import assert_close, load_golden
+
+
+def test_pixwt_golden():
+    g = load_golden("golden_pixwt.npz")
+    for i in range(g["xc"].size):
+        m = g["pid"] == i
+        w = hostcheck.pixwt(g["xc"][i], g["yc"][i], g["r"][i], g["x"][m], g["y"][m])
+        assert_close(w, g["w"][m], rtol=1e-12, atol=1e-13, what="pixwt %d" % i)
+    assert_close(hostcheck.pixwt(3.5, 3.5, 2.0, g["half_x"], g["half_y"]), g["half_w"], rtol=1e-12, atol=1e-13)
+
+
+def test_psfmodel_golden():
+    g = load_golden("golden_psfmodel.npz")
+    o = hostcheck.psfmodel(g["xx"], g["yy"], g["gauss"], g["psf"])
+    for row, key, tol in ((0, "v", 1e-12), (1, "dvx", 1e-11), (2, "dvy", 1e-11), (3, "f", 1e-12),
+                          (9, "z", 1e-12), (10, "dfdx", 1e-12), (11, "dfdy", 1e-12)):
+        assert_close(o[row], g[key], rtol=tol, atol=tol, what=key)
+    assert_close(o[4:9], g["pder"], rtol=1e-11, atol=1e-12, what="pder")
+
+
+def test_mmm_golden():
+    g = load_golden("golden_mmm.npz")
+    off = 0
+    for n, out in zip(g["lens"], g["out"]):
+        v = g["vec"][off:off + n]
+        off += n
+        got = hostcheck.mmm(v, readnoise=out[3], minsky=int(out[4]))
+        assert_close(got[:3], out[:3], rtol=1e-11, atol=1e-11, what="mmm n=%d" % n)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_mmm_bracket_search_equals_index_walk(seed):
+    """The binary-searched brackets (mmm_walk_min/max) against the oracle's literal one-index-at-a-time
+    walk, on data full of ties (integer-valued, few distinct levels, outliers on either side)."""
+    rng = np.random.default_rng(100 + seed)
+    for trial in range(300):
+        n = int(rng.integers(20, 400))
+        kind = trial % 5
+        if kind == 0:
+            v = np.round(rng.normal(300, rng.uniform(0.5, 6), n))
+        elif kind == 1:
+            v = rng.integers(0, 4, n).astype(float) * rng.uniform(1, 50)
+        elif kind == 2:
+            v = np.round(rng.normal(100, 3, n)); v[rng.integers(0, n, n // 6 + 1)] += np.round(rng.exponential(200, n // 6 + 1))
+        elif kind == 3:
+            v = np.round(rng.normal(100, 3, n)); v[rng.integers(0, n, n // 5 + 1)] -= np.round(rng.exponential(80, n // 5 + 1))
+        else:
+            v = rng.normal(50, 2, n)
+        rn = float(rng.choice([0.0, 0.0, 4.0]))
+        ms = int(rng.choice([20, 20, 35]))
+        want = oracle.mmm(v, readnoise=rn, minsky=ms, return_info=True)
+        got = hostcheck.mmm(v, readnoise=rn, minsky=ms)
+        assert got[3] == want[3], "iteration count differs (trial %d kind %d): %r vs %r" % (trial, kind, got, want)
+        assert_close(got[:3], want[:3], rtol=1e-10, atol=1e-10, what="mmm trial %d kind %d" % (trial, kind))
+
+
+def test_inv3_matches_oracle():
+    rng = np.random.default_rng(5)
+    for t in range(500):
+        a = rng.normal(size=(3, 3)) * 10.0 ** rng.integers(-3, 4, size=(1, 3))
+        c = a @ a.T if t % 2 == 0 else a  # SPD -> Cholesky route, general -> LU route
+        if t % 2 == 0:
+            c = (c + c.T) / 2
+        if t % 50 == 49:
+            c[2] = c[1] * 2.0  # singular
+            c[:, 2] = c[:, 1] * 2.0
+        got, st = hostcheck.inv3(c)
+        want, st2 = oracle.inv3(c)
+        assert st == st2
+        if st == 0:
+            assert np.array_equal(got, want), "inv3 differs from the oracle bit-for-bit at trial %d" % t
