@@ -93,7 +93,9 @@ def _check_aper(got, want, fragile, what, nsky=None, want_nsky=None):
     gb, wb = got["badflag"].astype(bool), want["badflag"].astype(bool)
     mism = gb != wb
     assert not (mism & ~fragile).any(), "%s: badflag differs on %d robust apertures" % (what, (mism & ~fragile).sum())
-    ok = ~mism
+    # a fragile aperture holds a NaN / out-of-range pixel whose pixwt weight is 0 +- 1e-9: whether the reference
+    # zeroes the whole aperture (aper.py:366) hinges on the last bit of atan(), so its VALUE is not comparable either
+    ok = ~mism & ~fragile
     for nm in ("flux", "fluxerr", "mag", "magerr"):
         atol = 1e-7 if nm in ("flux", "fluxerr") else 1e-9
         assert_close(got[nm][ok], want[nm][ok], rtol=1e-9, atol=atol, what="%s %s" % (what, nm))
