@@ -1,31 +1,125 @@
-// aper_kernel.cu -- concentric-aperture photometry + mmm sky, one CTA per star (sm_100a).
+// aper_kernel.cu -- concentric-aperture photometry + mmm sky, one 128-thread CTA per star (sm_100a).
 //
 // Replaces the per-star Python loop of PythonPhot/aper.py:217-417 and its callees
-// mmm.mmm (mmm.py:7-314) and pixwt.Pixwt (pixwt.py:8-235).  Per star, one 256-thread CTA
-//   P1  gathers the sky-annulus pixels of the (2*skyrad_out+1)^2 stamp into shared memory
-//       (row-wise, coalesced, candidate column span per row; aper.py:240-267),
-//   P2  sorts them in shared memory (bitonic network; np.sort at mmm.py:119),
-//   P3  warp 0 runs the mmm clipping loop on the sorted vector (binary-searched brackets in
-//       place of the index walk, fp64 range sums by warp shuffle) WHILE warps 1..7 accumulate
-//       the aperture sums (exact circle/pixel overlap weights or the polygon approximation),
+// mmm.mmm (mmm.py:7-314) and pixwt.Pixwt (pixwt.py:8-235).  Per star:
+//   P1  the four warps gather the sky-annulus pixels of the (2*skyrad_out+1)^2 stamp into shared
+//       memory, row by row, visiting only the two column spans of each row that can intersect
+//       the annulus (coalesced; aper.py:240-267);
+//   P2  the keys are sorted (np.sort at mmm.py:119) by a bitonic network that lives in REGISTERS:
+//       each thread holds K consecutive keys, compare-exchanges between a thread's own keys are
+//       FMNMX pairs, exchanges inside a warp are shuffles, and only the 3 (K=32) stages that cross
+//       warps go through shared memory;
+//   P3  warp 0 runs the mmm clipping loop on the sorted vector (32-way ballot searches in place of
+//       the reference's index walk, fp64 range sums by warp shuffle) WHILE warps 1..3 do the
+//       aperture sums: pixels are classified geometrically (inside / outside / crossed by the
+//       circle) and only crossed pixels go through pixwt, four lanes per pixel (one per side);
 //   P4  combines both into flux / error / magnitude (aper.py:383-403).
-// A persistent grid strides over the star list.
+// A persistent grid strides over the star list.  K = 0 selects the fallback for annuli of more
+// than 4096 pixels: the same phases with a shared-memory bitonic sort.
 #include "bphot_device.cuh"
 #include "bphot_params.h"
 
 namespace bphot {
 
-constexpr int APER_THREADS = 256;
-constexpr int APER_WARPS = APER_THREADS / 32;
-constexpr int APER_WORKERS = APER_WARPS - 1;  // warps that do aperture sums during mmm
+constexpr int AP_THREADS = 128;
+constexpr int AP_WARPS = AP_THREADS / 32;
+constexpr int AP_WORKERS = AP_WARPS - 1;  // warps that do aperture sums during mmm
+
+BP_D float kmin(float a, float b) { return fminf(a, b); }
+BP_D float kmax(float a, float b) { return fmaxf(a, b); }
+BP_D double kmin(double a, double b) { return fmin(a, b); }
+BP_D double kmax(double a, double b) { return fmax(a, b); }
 
 // ----------------------------------------------------------------- sort
-// Bitonic sorting network over m = 2^k keys in shared memory (ascending).
+// Element e of the 128*K-key vector lives in register e % K of thread e / K.  The network is the
+// all-ascending form of bitonic sort: phase k first pairs e with its mirror e ^ (k-1) inside each
+// k-block, then half-cleans with partners e ^ j, j = k/4 .. 1; the lower index keeps the minimum.
+template <typename T>
+BP_D void ce(T& a, T& b) {
+    const T lo = kmin(a, b), hi = kmax(a, b);
+    a = lo;
+    b = hi;
+}
+template <typename T, int K, int J>
+BP_D void half_clean(T (&r)[K]) {
+    if constexpr (J >= 1) {
+#pragma unroll
+        for (int q = 0; q < K; q++)
+            if ((q & J) == 0) ce(r[q], r[q ^ J]);
+        half_clean<T, K, J / 2>(r);
+    }
+}
+template <typename T, int K, int KK>
+BP_D void local_phases(T (&r)[K]) {  // phases k = KK .. K, entirely inside one thread
+    if constexpr (KK <= K) {
+#pragma unroll
+        for (int q = 0; q < K; q++)
+            if (q < (q ^ (KK - 1))) ce(r[q], r[q ^ (KK - 1)]);
+        half_clean<T, K, KK / 4>(r);
+        local_phases<T, K, KK * 2>(r);
+    }
+}
+// partner thread tid ^ m inside the warp; mirror stages pair register q with the partner's K-1-q
+template <typename T, int K>
+BP_D void shfl_stage(T (&r)[K], int m, bool keepmin) {
+#pragma unroll
+    for (int q = 0; q < K; q++) {
+        const T o = __shfl_xor_sync(FULL, r[q], m);
+        r[q] = keepmin ? kmin(r[q], o) : kmax(r[q], o);
+    }
+}
+template <typename T, int K>
+BP_D void shfl_mirror(T (&r)[K], int m, bool keepmin) {
+#pragma unroll
+    for (int q = 0; q < K / 2; q++) {
+        const T oa = __shfl_xor_sync(FULL, r[K - 1 - q], m);
+        const T ob = __shfl_xor_sync(FULL, r[q], m);
+        r[q] = keepmin ? kmin(r[q], oa) : kmax(r[q], oa);
+        r[K - 1 - q] = keepmin ? kmin(r[K - 1 - q], ob) : kmax(r[K - 1 - q], ob);
+    }
+}
+// partner thread in another warp: through shared memory, row stride K+1 keeps both the writes and
+// the partner reads conflict-free
+template <typename T, int K>
+BP_D void smem_stage(T (&r)[K], int m, bool mirror, bool keepmin, T* xbuf, int tid) {
+    T* mine = xbuf + tid * (K + 1);
+#pragma unroll
+    for (int q = 0; q < K; q++) mine[q] = r[q];
+    __syncthreads();
+    const T* theirs = xbuf + (tid ^ m) * (K + 1);
+#pragma unroll
+    for (int q = 0; q < K; q++) {
+        const T o = theirs[mirror ? K - 1 - q : q];
+        r[q] = keepmin ? kmin(r[q], o) : kmax(r[q], o);
+    }
+    __syncthreads();
+}
+template <typename T, int K>
+BP_D void cta_sort_regs(T (&r)[K], T* xbuf, int tid) {
+    local_phases<T, K, 2>(r);
+#pragma unroll 1
+    for (int k = 2 * K; k <= AP_THREADS * K; k <<= 1) {
+        const int m = k / K - 1;
+        const bool keepmin = (tid & (k / (2 * K))) == 0;
+        if (m < 32) shfl_mirror<T, K>(r, m, keepmin);
+        else smem_stage<T, K>(r, m, true, keepmin, xbuf, tid);
+#pragma unroll 1
+        for (int j = k >> 2; j >= K; j >>= 1) {
+            const int mm = j / K;
+            const bool km = (tid & mm) == 0;
+            if (mm < 32) shfl_stage<T, K>(r, mm, km);
+            else smem_stage<T, K>(r, mm, false, km, xbuf, tid);
+        }
+        half_clean<T, K, K / 2>(r);
+    }
+}
+
+// Fallback: bitonic sorting network over m = 2^k keys in shared memory (ascending).
 template <typename T>
 BP_D void cta_bitonic_sort(T* keys, int m, int tid) {
     for (int k = 2; k <= m; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int t = tid; t < (m >> 1); t += APER_THREADS) {
+            for (int t = tid; t < (m >> 1); t += AP_THREADS) {
                 const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));  // lower index of the pair
                 const int p = i | j;
                 const bool up = (i & k) == 0;
@@ -38,12 +132,42 @@ BP_D void cta_bitonic_sort(T* keys, int m, int tid) {
 }
 
 // ------------------------------------------------------------------ mmm
+// Sorted keys in shared memory; element i sits at i + (i >> shift) (row padding of the register
+// sort's write-back; shift = 31 means unpadded).
+template <typename T>
+struct SortedView {
+    const T* p;
+    int shift;
+    BP_D double operator()(int i) const { return (double)p[i + (i >> shift)]; }
+};
+
+// First index in [0, n) whose element satisfies the monotone predicate (n if none): 32 probes
+// per round instead of one, so 4096 keys take 3 dependent shared-memory reads, not 12.
+template <typename Pred>
+BP_D int warp_first_true(const Pred& pred, int n, int lane) {
+    int lo = 0, hi = n;
+    while (hi - lo > 32) {
+        const int step = (hi - lo + 31) >> 5;
+        int idx = lo + (lane + 1) * step - 1;
+        if (idx > hi - 1) idx = hi - 1;
+        const unsigned b = __ballot_sync(FULL, pred(idx));
+        if (b == 0u) return hi;
+        const int L = __ffs(b) - 1;
+        int nhi = lo + (L + 1) * step - 1;
+        if (nhi > hi - 1) nhi = hi - 1;
+        lo = lo + L * step;
+        hi = nhi;  // pred(hi) is known true
+    }
+    const int idx = lo + lane;
+    const unsigned b = __ballot_sync(FULL, idx < hi && pred(idx));
+    return b ? lo + __ffs(b) - 1 : hi;
+}
+
 // mmm.py:106-314 on an already sorted, NaN-free vector, executed by ONE warp: the control code is
 // mmm_sorted() of bphot_math.cuh (all lanes carry identical scalars); the range sums are
 // lane-strided fp64 partials combined by a butterfly, so every lane sees the same bits.
 template <typename T>
-BP_D MmmResult mmm_warp(const T* sky, int nsky, double readnoise, int minsky, int mxiter, int lane) {
-    auto at = [sky](int i) -> double { return (double)sky[i]; };
+BP_D MmmResult mmm_warp(const SortedView<T> at, int nsky, double readnoise, int minsky, int mxiter, int lane) {
     auto delta_sums = [&](int lo, int hi, double skymid, double* s1, double* s2) {
         double a = 0.0, q = 0.0;
         for (int i = lo + lane; i < hi; i += 32) {
@@ -59,7 +183,10 @@ BP_D MmmResult mmm_warp(const T* sky, int nsky, double readnoise, int minsky, in
         for (int i = lo + lane; i < hi; i += 32) a = a + at(i);
         return warp_sum(a);
     };
-    return mmm_sorted(at, delta_sums, plain_sum, nsky, readnoise, minsky, mxiter);
+    auto first = [&](double v, bool strict) -> int {
+        return warp_first_true([&](int i) { const double a = at(i); return strict ? a > v : a >= v; }, nsky, lane);
+    };
+    return mmm_sorted(at, delta_sums, plain_sum, first, nsky, readnoise, minsky, mxiter);
 }
 
 // ----------------------------------------------------------------- aper
@@ -70,13 +197,188 @@ struct ApPartial {  // one worker warp's share of one aperture
     int nfull, npart, flags;  // flags: bit0 non-finite pixel seen, bit1 bad-range pixel seen
 };
 
+struct StarGeom {  // aper.py:188-208
+    int nx, ny;
+    double dx, dy, edge;
+    size_t origin;  // element offset of the stamp's first pixel
+};
+
+BP_D StarGeom star_geom(const AperParams& P, double x, double y) {
+    long long lx = (long long)(x - P.skyrad_out), ly = (long long)(y - P.skyrad_out);  // int truncation, then clamp
+    long long ux = (long long)(x + P.skyrad_out), uy = (long long)(y + P.skyrad_out);
+    if (lx < 0) lx = 0;
+    if (ux > P.ncol - 1) ux = P.ncol - 1;
+    if (ly < 0) ly = 0;
+    if (uy > P.nrow - 1) uy = P.nrow - 1;
+    StarGeom g;
+    g.nx = (int)(ux - lx + 1);
+    g.ny = (int)(uy - ly + 1);
+    g.dx = x - (double)lx;
+    g.dy = y - (double)ly;
+    double edge = g.dx - 0.5;
+    if (g.nx + 0.5 - g.dx < edge) edge = g.nx + 0.5 - g.dx;
+    if (g.dy - 0.5 < edge) edge = g.dy - 0.5;
+    if (g.ny + 0.5 - g.dy < edge) edge = g.ny + 0.5 - g.dy;
+    g.edge = edge;
+    g.origin = (size_t)ly * P.pitch + lx;
+    return g;
+}
+
+// P1: one warp's rows of the annulus gather (aper.py:240-267).  Per row only the columns that
+// can lie in the annulus are visited: [a0, a1] minus the strictly-inside-the-inner-circle span
+// [b0, b1]; the exact fp64 membership test of the reference decides.  Returns this lane's copy
+// of the warp's count of selected pixels (NaNs included, as aper's nsky counts them).
 template <typename T>
-__global__ void __launch_bounds__(APER_THREADS) aper_kernel(const AperParams P) {
+BP_D int gather_rows(const AperParams& P, const T* __restrict__ stamp, const StarGeom& g, double rinsq, double routsq,
+                     T* keys, int* s_nvalid, int warp, int lane) {
+    int nsel = 0;
+    for (int r = warp; r < g.ny; r += AP_WARPS) {
+        const double dyv = (double)r - g.dy, dysq = dyv * dyv;
+        const double rem = routsq - dysq;
+        if (rem < 0.0) continue;  // rsq >= dysq > routsq for the whole row
+        const double hw = sqrt(rem) + 1.0;
+        int a0 = (int)floor(g.dx - hw), a1 = (int)ceil(g.dx + hw);
+        if (a0 < 0) a0 = 0;
+        if (a1 > g.nx - 1) a1 = g.nx - 1;
+        int b0 = a1 + 1, b1 = a1;  // empty exclusion span
+        const double remi = rinsq - dysq;
+        if (remi > 4.0) {  // columns with |c - dx| <= sqrt(remi) - 1 have rsq < rinsq
+            const double hwi = sqrt(remi) - 1.0;
+            int e0 = (int)ceil(g.dx - hwi), e1 = (int)floor(g.dx + hwi);
+            if (e0 < a0) e0 = a0;
+            if (e1 > a1) e1 = a1;
+            if (e0 <= e1) { b0 = e0; b1 = e1; }
+        }
+        const int nl = b0 - a0, tot = nl + (a1 - b1);
+        const T* __restrict__ row = stamp + (size_t)r * P.pitch;
+        for (int base = 0; base < tot; base += 32) {
+            const int t = base + lane;
+            bool sel = false, valid = false;
+            T val = T(0);
+            if (t < tot) {
+                const int c = t < nl ? a0 + t : b1 + 1 + (t - nl);
+                const double dxv = (double)c - g.dx;
+                const double rsq = dxv * dxv + dysq;
+                if (rsq >= rinsq && rsq <= routsq) {
+                    val = row[c];
+                    const double dv = (double)val;
+                    sel = !(P.badlo != P.badhi && (dv < P.badlo || dv > P.badhi));
+                    valid = sel && (val == val);  // mmm.py:106 drops NaNs; aper's nsky keeps them
+                }
+            }
+            const unsigned m_all = __ballot_sync(FULL, sel), m_val = __ballot_sync(FULL, valid);
+            nsel += __popc(m_all);
+            if (m_val == 0u) continue;
+            int base_idx = 0;
+            if (lane == 0) base_idx = atomicAdd(s_nvalid, __popc(m_val));
+            base_idx = __shfl_sync(FULL, base_idx, 0);
+            if (valid) {
+                const int idx = base_idx + __popc(m_val & ((1u << lane) - 1u));
+                if (idx < P.sort_cap) keys[idx] = val;
+            }
+        }
+    }
+    return nsel;
+}
+
+// P3 (worker warps): this warp's share of one aperture's pixel sums (aper.py:310-380).
+// `w` = worker index 0..AP_WORKERS-1; sx/sy/sw = 32 doubles of per-warp scratch each.
+template <typename T>
+BP_D ApPartial aperture_warp(const AperParams& P, const T* __restrict__ stamp, const StarGeom& g, double ap,
+                             int w, int lane, double* sx, double* sy, double* sw) {
+    ApPartial A;
+    A.sfull = 0.0; A.spart = 0.0; A.wpart = 0.0; A.nfull = 0; A.npart = 0; A.flags = 0;
+    const double bigrad = ap + 0.5, smallrad = ap / sqrt(2.) - 0.5;  // aper.py:179-181
+    // candidate box: every pixel the reference can give a positive weight lies inside it in either compat mode
+    // (py3: yy = row + col/nx shifts a pixel's y by < 1 row, aper.py:246-248)
+    int c0 = (int)floor(g.dx - bigrad) - 1, c1 = (int)ceil(g.dx + bigrad) + 1;
+    int r0 = (int)floor(g.dy - bigrad) - 2, r1 = (int)ceil(g.dy + bigrad) + 1;
+    if (c0 < 0) c0 = 0;
+    if (c1 > g.nx - 1) c1 = g.nx - 1;
+    if (r0 < 0) r0 = 0;
+    if (r1 > g.ny - 1) r1 = g.ny - 1;
+    const int bw = c1 - c0 + 1, bh = r1 - r0 + 1;
+    const int npx = (bw > 0 && bh > 0) ? bw * bh : 0;
+    const unsigned lt = (1u << lane) - 1u;
+    for (int base = w * 32; base < npx; base += 32 * AP_WORKERS) {
+        const int p = base + lane;
+        int r = 0, c = 0, cls = 0;
+        double xxp = 0., yyp = 0., wgt = 0.;
+        bool full = false;
+        if (p < npx) {
+            const int rr = p / bw;
+            r = r0 + rr;
+            c = c0 + (p - rr * bw);
+            if (P.exact) {  // aper.py:313-333
+                xxp = (double)c;
+                yyp = P.compat_py2 ? (double)r : (double)((long long)r * g.nx + c) / (double)g.nx;
+                const double x1 = fabs(xxp - g.dx), y1 = fabs(yyp - g.dy);
+                if (!(x1 > bigrad || y1 > bigrad)) cls = (x1 < smallrad && y1 < smallrad) ? 1 : pixel_class(x1, y1, ap);
+                if (cls == 1) wgt = 1.0;
+            } else {  // aper.py:336-349
+                const double dxv = (double)c - g.dx, dyv = (double)r - g.dy;
+                const double rad = sqrt(dxv * dxv + dyv * dyv) - 0.5;
+                if (rad < ap) {
+                    wgt = ap - rad;
+                    if (wgt > 1.) wgt = 1.;
+                    if (wgt < 0.) wgt = 0.;
+                    full = (wgt == 1.0);
+                    cls = 3;
+                }
+            }
+        }
+        const unsigned bmask = __ballot_sync(FULL, cls == 2);
+        if (bmask) {  // pixels the circle crosses: pixwt, one lane per pixel side
+            const int rank = __popc(bmask & lt), nb = __popc(bmask);
+            if (cls == 2) { sx[rank] = xxp; sy[rank] = yyp; }
+            __syncwarp();
+            for (int g0 = 0; g0 < nb; g0 += 8) {
+                const int j = g0 + (lane >> 2), side = lane & 3;
+                double s = 0.0;
+                if (j < nb) s = pixwt_side(g.dx, g.dy, ap, sx[j], sy[j], side);
+                const double s1 = __shfl_down_sync(FULL, s, 1), s2 = __shfl_down_sync(FULL, s, 2), s3 = __shfl_down_sync(FULL, s, 3);
+                if (side == 0 && j < nb) sw[j] = ((s + s1) + s2) + s3;  // Intarea's order of addition, pixwt.py:234-235
+            }
+            __syncwarp();
+            if (cls == 2) {
+                wgt = sw[rank];
+                if (wgt < 0.0) wgt = 0.0;  // aper.py:329
+            }
+            __syncwarp();
+        }
+        if (cls == 3 || (cls != 0 && wgt > 0.0)) {
+            double v = (double)stamp[(size_t)r * P.pitch + c];
+            if (!isfinite(v)) { A.flags |= 1; v = 0.0; }  // aper.py:359-366
+            if (P.badlo < P.badhi && (v <= P.badlo || v >= P.badhi)) { A.flags |= 2; v = 0.0; }  // aper.py:367-378
+            if (P.exact || full) {
+                A.sfull = A.sfull + v * wgt;
+                A.nfull += 1;
+            } else {
+                A.spart = A.spart + v * wgt;
+                A.wpart = A.wpart + wgt;
+                A.npart += 1;
+            }
+        }
+    }
+    A.sfull = warp_sum(A.sfull);
+    A.spart = warp_sum(A.spart);
+    A.wpart = warp_sum(A.wpart);
+    A.nfull = warp_sum_int(A.nfull);
+    A.npart = warp_sum_int(A.npart);
+    A.flags = __reduce_or_sync(FULL, (unsigned)A.flags);
+    return A;
+}
+
+// K > 0: register sort of 128*K keys (P.sort_cap == 128*K).  K == 0: shared-memory sort of P.sort_cap keys.
+template <typename T, int K>
+__global__ void __launch_bounds__(AP_THREADS) aper_kernel(const AperParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* keys = reinterpret_cast<T*>(smem_raw);
-    __shared__ int s_cnt[2];
-    __shared__ ApPartial s_part[BPHOT_MAX_APER][APER_WORKERS];
+    __shared__ int s_nvalid;
+    __shared__ int s_nsel[AP_WARPS];
+    __shared__ ApPartial s_part[BPHOT_MAX_APER][AP_WORKERS];
     __shared__ MmmResult s_mmm;
+    __shared__ double s_scr[AP_WORKERS][3][32];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const T* __restrict__ img = reinterpret_cast<const T*>(P.img);
@@ -88,7 +390,7 @@ __global__ void __launch_bounds__(APER_THREADS) aper_kernel(const AperParams P) 
         // aper.py:209-210 (a NaN position crashes the reference; it is flagged bad here)
         const bool badstar = !(x >= 0.5) || !(x <= P.ncol - 1.5) || !(y >= 0.5) || !(y <= P.nrow - 1.5);
         auto write_bad = [&](double skyv, double skyerrv, int nskyv, int iters) {
-            for (int k = tid; k < naper; k += APER_THREADS) {
+            for (int k = tid; k < naper; k += AP_THREADS) {
                 const size_t o = (size_t)s * naper + k;
                 P.mag[o] = nan64(); P.magerr[o] = nan64(); P.flux[o] = nan64(); P.fluxerr[o] = nan64();
                 P.badflag[o] = 1;
@@ -96,85 +398,55 @@ __global__ void __launch_bounds__(APER_THREADS) aper_kernel(const AperParams P) 
             if (tid == 0) { P.sky[s] = skyv; P.skyerr[s] = skyerrv; P.nsky[s] = nskyv; P.mmm_iter[s] = iters; }
         };
         if (badstar) { write_bad(0.0, 0.0, 0, 0); continue; }
-
-        // aper.py:188-208: stamp limits (int truncation, clamp to the frame), centre in stamp coords
-        long long lx = (long long)(x - P.skyrad_out), ly = (long long)(y - P.skyrad_out);
-        long long ux = (long long)(x + P.skyrad_out), uy = (long long)(y + P.skyrad_out);
-        if (lx < 0) lx = 0;
-        if (ux > P.ncol - 1) ux = P.ncol - 1;
-        if (ly < 0) ly = 0;
-        if (uy > P.nrow - 1) uy = P.nrow - 1;
-        const int nx = (int)(ux - lx + 1), ny = (int)(uy - ly + 1);
-        const double dx = x - (double)lx, dy = y - (double)ly;
-        double edge = dx - 0.5;
-        if (nx + 0.5 - dx < edge) edge = nx + 0.5 - dx;
-        if (dy - 0.5 < edge) edge = dy - 0.5;
-        if (ny + 0.5 - dy < edge) edge = ny + 0.5 - dy;
-        const T* __restrict__ stamp = img + (size_t)ly * P.pitch + lx;
+        const StarGeom g = star_geom(P, x, y);
+        const T* __restrict__ stamp = img + g.origin;
 
         int nsky_all = 0, nvalid = 0;
         if (!P.use_setsky) {
-            // ---- P1: gather the annulus (aper.py:240-267)
-            if (tid == 0) { s_cnt[0] = 0; s_cnt[1] = 0; }
+            // ---- P1: gather the annulus
+            if (tid == 0) s_nvalid = 0;
             __syncthreads();
-            for (int r = warp; r < ny; r += APER_WARPS) {
-                const double dyv = (double)r - dy, dysq = dyv * dyv;
-                const double rem = routsq - dysq;
-                if (rem < 0.0) continue;  // rsq >= dysq > routsq for the whole row
-                const double hw = sqrt(rem) + 1.0;
-                int c0 = (int)floor(dx - hw), c1 = (int)ceil(dx + hw);
-                if (c0 < 0) c0 = 0;
-                if (c1 > nx - 1) c1 = nx - 1;
-                const T* __restrict__ row = stamp + (size_t)r * P.pitch;
-                for (int cb = c0; cb <= c1; cb += 32) {
-                    const int c = cb + lane;
-                    bool sel = false, valid = false;
-                    T val = T(0);
-                    if (c <= c1) {
-                        const double dxv = (double)c - dx;
-                        const double rsq = dxv * dxv + dysq;
-                        if (rsq >= rinsq && rsq <= routsq) {
-                            val = row[c];
-                            const double dv = (double)val;
-                            sel = !(P.badlo != P.badhi && (dv < P.badlo || dv > P.badhi));
-                            valid = sel && (val == val);  // mmm.py:106 drops NaNs; aper's nsky keeps them
-                        }
-                    }
-                    const unsigned m_all = __ballot_sync(FULL, sel), m_val = __ballot_sync(FULL, valid);
-                    if (m_all == 0u) continue;
-                    int base = 0;
-                    if (lane == 0) {
-                        atomicAdd(&s_cnt[0], __popc(m_all));
-                        base = atomicAdd(&s_cnt[1], __popc(m_val));
-                    }
-                    base = __shfl_sync(FULL, base, 0);
-                    if (valid) {
-                        const int idx = base + __popc(m_val & ((1u << lane) - 1u));
-                        if (idx < P.sort_cap) keys[idx] = val;
-                    }
-                }
-            }
+            const int nsel = gather_rows<T>(P, stamp, g, rinsq, routsq, keys, &s_nvalid, warp, lane);
+            if (lane == 0) s_nsel[warp] = nsel;
             __syncthreads();
-            nsky_all = s_cnt[0];
-            nvalid = s_cnt[1] < P.sort_cap ? s_cnt[1] : P.sort_cap;
+#pragma unroll
+            for (int w = 0; w < AP_WARPS; w++) nsky_all += s_nsel[w];
+            nvalid = s_nvalid < P.sort_cap ? s_nvalid : P.sort_cap;
             if (nsky_all < P.minsky) {  // aper.py:269-272
                 write_bad(0.0, 0.0, nsky_all, 0);
-                __syncthreads();  // s_cnt is reset by the next star
+                __syncthreads();  // the counters are reset by the next star
                 continue;
             }
-
-            // ---- P2: sort (mmm.py:119); pad to a power of two with +inf
-            int m = 2;
-            while (m < nvalid) m <<= 1;
-            for (int i = nvalid + tid; i < m; i += APER_THREADS) keys[i] = KeyTraits<T>::inf();
+            // ---- P2: sort (mmm.py:119); the tail is padded with +inf
+            if constexpr (K > 0) {
+                T r[K];
+#pragma unroll
+                for (int q = 0; q < K; q++) {
+                    const int idx = q * AP_THREADS + tid;  // any bijection will do before sorting
+                    r[q] = idx < nvalid ? keys[idx] : KeyTraits<T>::inf();
+                }
+                __syncthreads();
+                cta_sort_regs<T, K>(r, keys, tid);
+#pragma unroll
+                for (int q = 0; q < K; q++) keys[tid * (K + 1) + q] = r[q];
+            } else {
+                int m = 2;
+                while (m < nvalid) m <<= 1;
+                for (int i = nvalid + tid; i < m; i += AP_THREADS) keys[i] = KeyTraits<T>::inf();
+                __syncthreads();
+                cta_bitonic_sort(keys, m, tid);
+            }
             __syncthreads();
-            cta_bitonic_sort(keys, m, tid);
         }
 
         // ---- P3: warp 0 -> mmm ; warps 1.. -> aperture sums
         if (warp == 0) {
             if (!P.use_setsky) {
-                MmmResult R = mmm_warp(keys, nvalid, P.readnoise, P.minsky, P.mxiter, lane);
+                SortedView<T> view;
+                view.p = keys;
+                view.shift = 31;
+                if constexpr (K > 0) view.shift = __ffs(K) - 1;
+                MmmResult R = mmm_warp<T>(view, nvalid, P.readnoise, P.minsky, P.mxiter, lane);
                 if (lane == 0) s_mmm = R;
             }
         } else {
@@ -183,60 +455,7 @@ __global__ void __launch_bounds__(APER_THREADS) aper_kernel(const AperParams P) 
                 const double ap = P.apr[k];
                 ApPartial A;
                 A.sfull = 0.0; A.spart = 0.0; A.wpart = 0.0; A.nfull = 0; A.npart = 0; A.flags = 0;
-                if (edge >= ap) {
-                    const double bigrad = ap + 0.5, smallrad = ap / sqrt(2.) - 0.5;  // aper.py:179-181
-                    int c0 = (int)floor(dx - bigrad) - 1, c1 = (int)ceil(dx + bigrad) + 1;
-                    int r0 = (int)floor(dy - bigrad) - 2, r1 = (int)ceil(dy + bigrad) + 1;
-                    if (c0 < 0) c0 = 0;
-                    if (c1 > nx - 1) c1 = nx - 1;
-                    if (r0 < 0) r0 = 0;
-                    if (r1 > ny - 1) r1 = ny - 1;
-                    for (int r = r0 + w; r <= r1; r += APER_WORKERS) {
-                        const T* __restrict__ row = stamp + (size_t)r * P.pitch;
-                        for (int c = c0 + lane; c <= c1; c += 32) {
-                            double wgt;
-                            bool full = false;
-                            if (P.exact) {  // aper.py:313-333
-                                const double xxp = (double)c;
-                                const double yyp = P.compat_py2 ? (double)r
-                                                                : (double)((long long)r * nx + c) / (double)nx;  // aper.py:246-248
-                                const double x1 = fabs(xxp - dx), y1 = fabs(yyp - dy);
-                                if (x1 > bigrad || y1 > bigrad) continue;
-                                if (x1 < smallrad && y1 < smallrad) wgt = 1.0;
-                                else {
-                                    wgt = pixwt(dx, dy, ap, xxp, yyp);
-                                    if (wgt < 0.0) wgt = 0.0;
-                                }
-                                if (!(wgt > 0.0)) continue;
-                            } else {  // aper.py:336-349
-                                const double dxv = (double)c - dx, dyv = (double)r - dy;
-                                const double rr = sqrt(dxv * dxv + dyv * dyv) - 0.5;
-                                if (!(rr < ap)) continue;
-                                wgt = ap - rr;
-                                if (wgt > 1.) wgt = 1.;
-                                if (wgt < 0.) wgt = 0.;
-                                full = (wgt == 1.0);
-                            }
-                            double v = (double)row[c];
-                            if (!isfinite(v)) { A.flags |= 1; v = 0.0; }  // aper.py:359-366
-                            if (P.badlo < P.badhi && (v <= P.badlo || v >= P.badhi)) { A.flags |= 2; v = 0.0; }  // aper.py:367-378
-                            if (P.exact || full) {
-                                A.sfull = A.sfull + v * wgt;
-                                A.nfull += 1;
-                            } else {
-                                A.spart = A.spart + v * wgt;
-                                A.wpart = A.wpart + wgt;
-                                A.npart += 1;
-                            }
-                        }
-                    }
-                    A.sfull = warp_sum(A.sfull);
-                    A.spart = warp_sum(A.spart);
-                    A.wpart = warp_sum(A.wpart);
-                    A.nfull = warp_sum_int(A.nfull);
-                    A.npart = warp_sum_int(A.npart);
-                    A.flags = __reduce_or_sync(FULL, (unsigned)A.flags);
-                }
+                if (g.edge >= ap) A = aperture_warp<T>(P, stamp, g, ap, w, lane, s_scr[w][0], s_scr[w][1], s_scr[w][2]);
                 if (lane == 0) s_part[k][w] = A;
             }
         }
@@ -266,14 +485,14 @@ __global__ void __launch_bounds__(APER_THREADS) aper_kernel(const AperParams P) 
             const int k = tid;
             const size_t o = (size_t)s * naper + k;
             const double ap = P.apr[k];
-            if (!(edge >= ap)) {  // aper.py:311, 350-353
+            if (!(g.edge >= ap)) {  // aper.py:311, 350-353
                 P.mag[o] = nan64(); P.magerr[o] = nan64(); P.flux[o] = nan64(); P.fluxerr[o] = nan64();
                 P.badflag[o] = 1;
             } else {
                 const double area = M_PI * ap * ap;
                 double sfull = 0.0, spart = 0.0, wpart = 0.0;
                 int nfull = 0, npart = 0, flags = 0;
-                for (int w = 0; w < APER_WORKERS; w++) {
+                for (int w = 0; w < AP_WORKERS; w++) {
                     const ApPartial& A = s_part[k][w];
                     sfull = sfull + A.sfull; spart = spart + A.spart; wpart = wpart + A.wpart;
                     nfull += A.nfull; npart += A.npart; flags |= A.flags;
@@ -300,14 +519,12 @@ __global__ void __launch_bounds__(APER_THREADS) aper_kernel(const AperParams P) 
     }
 }
 
-template __global__ void aper_kernel<float>(const AperParams);
-template __global__ void aper_kernel<double>(const AperParams);
-
 // ---------------------------------------------------- unit-test kernels
-// Batched mmm over CSR-packed vectors (row a4 of the scope table): one CTA per vector.
-template <typename T>
-__global__ void __launch_bounds__(APER_THREADS) mmm_kernel(const T* vec, const long long* offs, int nvec, double readnoise,
-                                                           int minsky, int mxiter, int sort_cap, double* out3, int* iters) {
+// Batched mmm over CSR-packed vectors (row a4 of the scope table): one CTA per vector, same sort
+// and clipping code as aper_kernel (K as there; sort_cap = 128*K when K > 0).
+template <typename T, int K>
+__global__ void __launch_bounds__(AP_THREADS) mmm_kernel(const T* vec, const long long* offs, int nvec, double readnoise,
+                                                         int minsky, int mxiter, int sort_cap, double* out3, int* iters) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* keys = reinterpret_cast<T*>(smem_raw);
     __shared__ int s_n;
@@ -316,7 +533,7 @@ __global__ void __launch_bounds__(APER_THREADS) mmm_kernel(const T* vec, const l
         const long long b = offs[v], e = offs[v + 1];
         if (tid == 0) s_n = 0;
         __syncthreads();
-        for (long long ib = b + (long long)warp * 32; ib < e; ib += APER_THREADS) {
+        for (long long ib = b + (long long)warp * 32; ib < e; ib += AP_THREADS) {
             const long long i = ib + lane;
             T val = T(0);
             bool ok = false;
@@ -332,13 +549,31 @@ __global__ void __launch_bounds__(APER_THREADS) mmm_kernel(const T* vec, const l
         }
         __syncthreads();
         const int n = s_n < sort_cap ? s_n : sort_cap;
-        int m = 2;
-        while (m < n) m <<= 1;
-        for (int i = n + tid; i < m; i += APER_THREADS) keys[i] = KeyTraits<T>::inf();
+        SortedView<T> view;
+        view.p = keys;
+        view.shift = 31;
+        if constexpr (K > 0) {
+            T r[K];
+#pragma unroll
+            for (int q = 0; q < K; q++) {
+                const int idx = q * AP_THREADS + tid;
+                r[q] = idx < n ? keys[idx] : KeyTraits<T>::inf();
+            }
+            __syncthreads();
+            cta_sort_regs<T, K>(r, keys, tid);
+#pragma unroll
+            for (int q = 0; q < K; q++) keys[tid * (K + 1) + q] = r[q];
+            view.shift = __ffs(K) - 1;
+        } else {
+            int m = 2;
+            while (m < n) m <<= 1;
+            for (int i = n + tid; i < m; i += AP_THREADS) keys[i] = KeyTraits<T>::inf();
+            __syncthreads();
+            cta_bitonic_sort(keys, m, tid);
+        }
         __syncthreads();
-        cta_bitonic_sort(keys, m, tid);
         if (warp == 0) {
-            MmmResult R = mmm_warp(keys, n, readnoise, minsky, mxiter, lane);
+            MmmResult R = mmm_warp<T>(view, n, readnoise, minsky, mxiter, lane);
             if (lane == 0) {
                 out3[3 * (size_t)v + 0] = R.skymod; out3[3 * (size_t)v + 1] = R.sigma; out3[3 * (size_t)v + 2] = R.skew;
                 iters[v] = R.iters;
@@ -347,8 +582,6 @@ __global__ void __launch_bounds__(APER_THREADS) mmm_kernel(const T* vec, const l
         __syncthreads();
     }
 }
-template __global__ void mmm_kernel<float>(const float*, const long long*, int, double, int, int, int, double*, int*);
-template __global__ void mmm_kernel<double>(const double*, const long long*, int, double, int, int, int, double*, int*);
 
 // Pixwt(xc, yc, r, x[], y[]) -- pixwt.py:8 (row a5).
 __global__ void pixwt_kernel(double xc, double yc, double r, const double* x, const double* y, long long n, double* out) {

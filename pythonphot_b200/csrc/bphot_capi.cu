@@ -132,10 +132,13 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     P.skyrad_in = skyrad_in; P.skyrad_out = skyrad_out; P.badlo = badlo; P.badhi = badhi;
     P.minsky = minsky; P.exact = exact ? 1 : 0; P.compat_py2 = compat_py2 ? 1 : 0; P.mxiter = 50;
     P.readnoise = readnoise;
-    P.sort_cap = use_setsky ? 2 : next_pow2(annulus_bound(skyrad_in, skyrad_out));
+    // register-sort variants hold 128*K keys; larger annuli fall back to the shared-memory sort (K = 0)
+    const int need = use_setsky ? 2 : next_pow2(annulus_bound(skyrad_in, skyrad_out));
+    const int K = need <= 1024 ? 8 : need <= 2048 ? 16 : need <= 4096 ? 32 : 0;
+    P.sort_cap = K ? AP_THREADS * K : need;
     P.mag = d_mag; P.magerr = d_magerr; P.flux = d_flux; P.fluxerr = d_fluxerr;
     P.sky = d_sky; P.skyerr = d_skyerr; P.badflag = d_badflag; P.nsky = d_nsky; P.mmm_iter = d_mmm_iter;
-    const size_t smem = (size_t)P.sort_cap * esize(image_dtype);
+    const size_t smem = (size_t)(K ? AP_THREADS * (K + 1) : need) * esize(image_dtype);
     DevInfo d;
     int rc = dev_info(&d);
     if (rc) return rc;
@@ -144,15 +147,23 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
                     skyrad_in, skyrad_out, smem, d.smem_optin);
     int grid = 0;
     cudaStream_t st = (cudaStream_t)stream;
-    if (image_dtype == BPHOT_F32) {
-        rc = persistent_grid(aper_kernel<float>, APER_THREADS, smem, nstars, &grid);
-        if (rc) return rc;
-        aper_kernel<float><<<grid, APER_THREADS, smem, st>>>(P);
-    } else {
-        rc = persistent_grid(aper_kernel<double>, APER_THREADS, smem, nstars, &grid);
-        if (rc) return rc;
-        aper_kernel<double><<<grid, APER_THREADS, smem, st>>>(P);
-    }
+#define BP_LAUNCH_APER(T, KK)                                                               \
+    do {                                                                                    \
+        rc = persistent_grid(aper_kernel<T, KK>, AP_THREADS, smem, nstars, &grid);          \
+        if (rc) return rc;                                                                  \
+        aper_kernel<T, KK><<<grid, AP_THREADS, smem, st>>>(P);                              \
+    } while (0)
+#define BP_LAUNCH_APER_K(T)                      \
+    do {                                         \
+        if (K == 8) BP_LAUNCH_APER(T, 8);        \
+        else if (K == 16) BP_LAUNCH_APER(T, 16); \
+        else if (K == 32) BP_LAUNCH_APER(T, 32); \
+        else BP_LAUNCH_APER(T, 0);               \
+    } while (0)
+    if (image_dtype == BPHOT_F32) BP_LAUNCH_APER_K(float);
+    else BP_LAUNCH_APER_K(double);
+#undef BP_LAUNCH_APER_K
+#undef BP_LAUNCH_APER
     g_launches++;
     CU_TRY(cudaGetLastError());
     return BPHOT_OK;
@@ -226,23 +237,34 @@ int bphot_mmm_device(const void* d_vec, int dtype, const long long* d_offs, int 
     if (!d_vec || !d_offs || !d_out3 || !d_iters || nvec < 0 || max_len < 0) return fail(BPHOT_ERR_ARG, "bphot_mmm: null pointer or negative size");
     if (dtype != BPHOT_F32 && dtype != BPHOT_F64) return fail(BPHOT_ERR_ARG, "bphot_mmm: dtype %d", dtype);
     if (nvec == 0) return BPHOT_OK;
-    const int cap = next_pow2(max_len);
-    const size_t smem = (size_t)cap * esize(dtype);
+    const int need = next_pow2(max_len);
+    const int K = need <= 1024 ? 8 : need <= 2048 ? 16 : need <= 4096 ? 32 : 0;
+    const int cap = K ? AP_THREADS * K : need;
+    const size_t smem = (size_t)(K ? AP_THREADS * (K + 1) : need) * esize(dtype);
     DevInfo d;
     int rc = dev_info(&d);
     if (rc) return rc;
     if (smem + 1024 > (size_t)d.smem_optin) return fail(BPHOT_ERR_CAPACITY, "bphot_mmm: vector of %d elements exceeds shared memory", max_len);
     int grid = 0;
     cudaStream_t st = (cudaStream_t)stream;
-    if (dtype == BPHOT_F32) {
-        rc = persistent_grid(mmm_kernel<float>, APER_THREADS, smem, nvec, &grid);
-        if (rc) return rc;
-        mmm_kernel<float><<<grid, APER_THREADS, smem, st>>>((const float*)d_vec, d_offs, nvec, readnoise, minsky, mxiter, cap, d_out3, d_iters);
-    } else {
-        rc = persistent_grid(mmm_kernel<double>, APER_THREADS, smem, nvec, &grid);
-        if (rc) return rc;
-        mmm_kernel<double><<<grid, APER_THREADS, smem, st>>>((const double*)d_vec, d_offs, nvec, readnoise, minsky, mxiter, cap, d_out3, d_iters);
-    }
+#define BP_LAUNCH_MMM(T, KK)                                                                                         \
+    do {                                                                                                             \
+        rc = persistent_grid(mmm_kernel<T, KK>, AP_THREADS, smem, nvec, &grid);                                      \
+        if (rc) return rc;                                                                                           \
+        mmm_kernel<T, KK><<<grid, AP_THREADS, smem, st>>>((const T*)d_vec, d_offs, nvec, readnoise, minsky, mxiter,  \
+                                                          cap, d_out3, d_iters);                                     \
+    } while (0)
+#define BP_LAUNCH_MMM_K(T)                      \
+    do {                                        \
+        if (K == 8) BP_LAUNCH_MMM(T, 8);        \
+        else if (K == 16) BP_LAUNCH_MMM(T, 16); \
+        else if (K == 32) BP_LAUNCH_MMM(T, 32); \
+        else BP_LAUNCH_MMM(T, 0);               \
+    } while (0)
+    if (dtype == BPHOT_F32) BP_LAUNCH_MMM_K(float);
+    else BP_LAUNCH_MMM_K(double);
+#undef BP_LAUNCH_MMM_K
+#undef BP_LAUNCH_MMM
     g_launches++;
     CU_TRY(cudaGetLastError());
     return BPHOT_OK;

@@ -35,23 +35,52 @@ BP_HD double pw_arc(double x, double y0, double y1, double r) {
 BP_HD double pw_chord(double x, double y0, double y1) { return 0.5 * x * (y1 - y0); }
 
 // pixwt.py:112-213: area between the line X = x and the circle, from y0 to y1.
+// The reference's 3 x 3 case table (zone of y0: <= -yh, inside, >= yh; zone of y1: <= -yh, <= yh,
+// above) always reduces to  [arc] + [chord] + [arc]  with the terms added left to right; the table
+// is folded into endpoint selects so that the device code has TWO arc call sites instead of
+// eleven (the inlined fp64 atan pairs of the case table overflowed the instruction cache).
 BP_HD double pw_oneside(double x, double y0, double y1, double r) {
-    if (fabs(x) >= r) return pw_arc(x, y0, y1, r);
-    const double yh = sqrt(r * r - x * x);
-    // three zones for y0 (<= -yh, inside, >= yh) x three zones for y1 (<= -yh, <= yh, above)
-    const int z0 = (y0 <= -yh) ? 0 : ((y0 < yh) ? 1 : 2);
-    const int z1 = (y1 <= -yh) ? 0 : ((y1 <= yh) ? 1 : 2);
-    switch (z0 * 3 + z1) {
-        case 0: return pw_arc(x, y0, y1, r);
-        case 1: return pw_arc(x, y0, -yh, r) + pw_chord(x, -yh, y1);
-        case 2: return pw_arc(x, y0, -yh, r) + pw_chord(x, -yh, yh) + pw_arc(x, yh, y1, r);
-        case 3: return pw_chord(x, y0, -yh) + pw_arc(x, -yh, y1, r);
-        case 4: return pw_chord(x, y0, y1);
-        case 5: return pw_chord(x, y0, yh) + pw_arc(x, yh, y1, r);
-        case 6: return pw_arc(x, y0, yh, r) + pw_chord(x, yh, -yh) + pw_arc(x, -yh, y1, r);
-        case 7: return pw_arc(x, y0, yh, r) + pw_chord(x, yh, y1);
-        default: return pw_arc(x, y0, y1, r);
+    const bool beyond = fabs(x) >= r;  // pixwt.py:93,129: the line misses the circle -> one arc y0..y1
+    const double yh = beyond ? 0.0 : sqrt(r * r - x * x);
+    const int z0 = beyond ? 0 : ((y0 <= -yh) ? 0 : ((y0 < yh) ? 1 : 2));
+    const int z1 = beyond ? 0 : ((y1 <= -yh) ? 0 : ((y1 <= yh) ? 1 : 2));
+    const bool has_a1 = (z0 != 1);                // leading arc starts at y0
+    const bool has_a2 = (z1 != 1) && (z1 != z0);  // trailing arc ends at y1
+    const bool has_c = !(z0 == z1 && z0 != 1);    // chord between them
+    double res = 0.0;
+    if (has_a1) res = pw_arc(x, y0, (z1 == z0) ? y1 : (z0 == 0 ? -yh : yh), r);
+    if (has_c) {
+        const double cs = (z0 == 1) ? y0 : (z0 == 0 ? -yh : yh);
+        const double ce = (z1 == 1) ? y1 : (z1 == 2 ? yh : -yh);
+        const double ch = pw_chord(x, cs, ce);
+        res = has_a1 ? res + ch : ch;
     }
+    if (has_a2) res = res + pw_arc(x, (z1 == 2) ? yh : -yh, y1, r);
+    return res;
+}
+
+// One of the four Intarea terms (pixwt.py:229-235) of the unit pixel centred (x, y):
+// side 0..3 in the reference's order of addition.
+BP_HD double pixwt_side(double xc, double yc, double r, double x, double y, int side) {
+    const double x0 = (x - 0.5) - xc, y0 = (y - 0.5) - yc;
+    const double x1 = (x + 0.5) - xc, y1 = (y + 0.5) - yc;
+    const double X = (side == 0) ? x1 : (side == 1) ? y1 : (side == 2) ? -x0 : -y0;
+    const double A = (side == 0) ? y0 : (side == 1) ? -x1 : (side == 2) ? -y1 : x0;
+    const double B = (side == 0) ? y1 : (side == 1) ? -x0 : (side == 2) ? -y0 : x1;
+    return pw_oneside(X, A, B, r);
+}
+
+// Geometric class of the unit pixel whose centre is (x1, y1) = |offset from the circle centre|:
+// 1 = every corner inside the circle (weight 1), 0 = no point of the pixel inside (weight 0),
+// 2 = the circle crosses the pixel (needs pixwt).  The 1e-9 px^2 guard band sends anything
+// within rounding distance of tangency to pixwt, so classes 0 and 1 are exact statements.
+BP_HD int pixel_class(double x1, double y1, double r) {
+    const double r2 = r * r;
+    const double fx = x1 + 0.5, fy = y1 + 0.5;
+    if (fx * fx + fy * fy <= r2 - 1e-9) return 1;
+    const double nx = x1 > 0.5 ? x1 - 0.5 : 0.0, ny = y1 > 0.5 ? y1 - 0.5 : 0.0;
+    if (nx * nx + ny * ny >= r2 + 1e-9) return 0;
+    return 2;
 }
 
 // pixwt.py:8-48 + Intarea pixwt.py:215-235: area of the unit pixel centred (x,y) inside the
@@ -262,9 +291,11 @@ BP_HD int upper_bound_gt(const Get& at, int n, double v) {  // first i with at(i
 // index just below the accepted set (may be -1).  Returns the new minimm; *moved = false when
 // the reference takes its "done" shortcut and leaves sum/sumsq untouched.
 // The walk stops at the first index i (stepping from minimm) with i == -1, i == nlast, or
-// at(i) <= cut1 <= at(i+1); in a sorted vector those i form [lb-1, ub-1].
-template <typename Get>
-BP_HD int mmm_walk_min(const Get& at, int nsky, int minimm, double cut1, bool* moved, bool* grew) {
+// at(i) <= cut1 <= at(i+1); in a sorted vector those i form [lb-1, ub-1], where
+// lb = first(cut1, false) and ub = first(cut1, true):
+//   first(v, strict) = index of the first element > v (strict) or >= v (not strict), nsky if none.
+template <typename Get, typename First>
+BP_HD int mmm_walk_min(const Get& at, const First& first, int nsky, int minimm, double cut1, bool* moved, bool* grew) {
     const int nlast = nsky - 1;
     const bool tst_min = at(minimm + 1) >= cut1;
     *grew = tst_min;
@@ -275,20 +306,19 @@ BP_HD int mmm_walk_min(const Get& at, int nsky, int minimm, double cut1, bool* m
     }
     *moved = !done;
     if (done) return minimm;
+    const int e = first(cut1, tst_min) - 1;
     if (tst_min) {  // grow downward: first i <= minimm-1 inside the bracket set, else -1
-        const int b = upper_bound_gt(at, nsky, cut1) - 1;
-        int r = b < (minimm - 1) ? b : (minimm - 1);
+        const int r = e < (minimm - 1) ? e : (minimm - 1);
         return r < -1 ? -1 : r;
     }
     // shrink upward: first i >= minimm+1 inside the bracket set, else nlast
-    const int a = lower_bound_ge(at, nsky, cut1) - 1;
-    int r = a > (minimm + 1) ? a : (minimm + 1);
+    const int r = e > (minimm + 1) ? e : (minimm + 1);
     return r > nlast ? nlast : r;
 }
 
 // mmm.py:224-241: the UPPER edge.  `maximm` is the last accepted index.
-template <typename Get>
-BP_HD int mmm_walk_max(const Get& at, int nsky, int maximm, double cut2, bool* moved, bool* grew) {
+template <typename Get, typename First>
+BP_HD int mmm_walk_max(const Get& at, const First& first, int nsky, int maximm, double cut2, bool* moved, bool* grew) {
     const int nlast = nsky - 1;
     const bool tst_max = at(maximm) <= cut2;
     *grew = tst_max;
@@ -299,14 +329,13 @@ BP_HD int mmm_walk_max(const Get& at, int nsky, int maximm, double cut2, bool* m
     }
     *moved = !done;
     if (done) return maximm;
+    const int e = first(cut2, !tst_max) - 1;
     if (tst_max) {  // grow upward
-        const int a = lower_bound_ge(at, nsky, cut2) - 1;
-        int r = a > (maximm + 1) ? a : (maximm + 1);
+        const int r = e > (maximm + 1) ? e : (maximm + 1);
         return r > nlast ? nlast : r;
     }
     // shrink downward
-    const int b = upper_bound_gt(at, nsky, cut2) - 1;
-    int r = b < (maximm - 1) ? b : (maximm - 1);
+    const int r = e < (maximm - 1) ? e : (maximm - 1);
     return r < -1 ? -1 : r;
 }
 
@@ -314,6 +343,7 @@ BP_HD int mmm_walk_max(const Get& at, int nsky, int maximm, double cut2, bool* m
 //   at(i)                         element i widened to double
 //   delta_sums(lo, hi, mid, &a, &q)  a = sum(at(i)-mid), q = sum((at(i)-mid)^2) over [lo, hi)
 //   plain_sum(lo, hi)             sum(at(i)) over [lo, hi)
+//   first(v, strict)              first index with at(i) > v (strict) / at(i) >= v (nsky if none)
 // The functors let a whole warp share the reductions on the device (every lane must receive the same
 // bits) and a plain loop stand in on the host (tests/hostcheck).  Failure modes keep the reference's
 // in-band codes (sigma = -1).
@@ -323,9 +353,9 @@ struct MmmResult {
 };
 BP_HD double mmm_nan() { return (double)NAN; }
 
-template <typename Get, typename DSums, typename PSum>
-BP_HD MmmResult mmm_sorted(const Get& at, const DSums& delta_sums, const PSum& plain_sum, int nsky,
-                           double readnoise, int minsky, int mxiter) {
+template <typename Get, typename DSums, typename PSum, typename First>
+BP_HD MmmResult mmm_sorted(const Get& at, const DSums& delta_sums, const PSum& plain_sum, const First& first,
+                           int nsky, double readnoise, int minsky, int mxiter) {
     MmmResult R;
     R.iters = 0;
     R.skew = 0.0;
@@ -342,8 +372,8 @@ BP_HD MmmResult mmm_sorted(const Get& at, const DSums& delta_sums, const PSum& p
         cut2 = skymid + c;
         cut1 = skymid - c;
     }
-    const int gmin = lower_bound_ge(at, nsky, cut1);
-    const int gmax = upper_bound_gt(at, nsky, cut2) - 1;
+    const int gmin = first(cut1, false);
+    const int gmax = first(cut2, true) - 1;
     if (gmin > gmax) {  // mmm.py:134-138
         R.skymod = 0.0; R.sigma = -1.0;
         return R;
@@ -374,32 +404,29 @@ BP_HD MmmResult mmm_sorted(const Get& at, const DSums& delta_sums, const PSum& p
         cut2 = skymod + cut;
         redo = false;
         bool moved, grew;
-        const int newmin = mmm_walk_min(at, nsky, minimm, cut1, &moved, &grew);  // mmm.py:199-222
-        if (moved) {
+        // mmm.py:199-248: both edges.  The upper walk reads only the vector, maximm and cut2, so it
+        // can be taken before the lower edge's sums are applied; the sums then share one call site.
+        bool moved1, grew1;
+        const int newmin = mmm_walk_min(at, first, nsky, minimm, cut1, &moved, &grew);
+        const int newmax = mmm_walk_max(at, first, nsky, maximm, cut2, &moved1, &grew1);
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+        for (int e = 0; e < 2; e++) {
+            const bool mv = e ? moved1 : moved, gr = e ? grew1 : grew;
+            if (!mv) continue;
+            // lower edge: grown range (newmin, minimm], shrunk range (minimm, newmin]
+            // upper edge: grown range (maximm, newmax], shrunk range (newmax, maximm]
+            const int from = e ? (gr ? maximm : newmax) : (gr ? newmin : minimm);
+            const int to = e ? (gr ? newmax : maximm) : (gr ? minimm : newmin);
             double s1, s2;
-            if (grew) {
-                delta_sums(newmin + 1, minimm + 1, skymid, &s1, &s2);
-                sum = sum + s1; sumsq = sumsq + s2;
-            } else {
-                delta_sums(minimm + 1, newmin + 1, skymid, &s1, &s2);
-                sum = sum - s1; sumsq = sumsq - s2;
-            }
+            delta_sums(from + 1, to + 1, skymid, &s1, &s2);
+            if (gr) { sum = sum + s1; sumsq = sumsq + s2; }
+            else { sum = sum - s1; sumsq = sumsq - s2; }
             redo = true;
-            minimm = newmin;
         }
-        const int newmax = mmm_walk_max(at, nsky, maximm, cut2, &moved, &grew);  // mmm.py:224-248
-        if (moved) {
-            double s1, s2;
-            if (grew) {
-                delta_sums(maximm + 1, newmax + 1, skymid, &s1, &s2);
-                sum = sum + s1; sumsq = sumsq + s2;
-            } else {
-                delta_sums(newmax + 1, maximm + 1, skymid, &s1, &s2);
-                sum = sum - s1; sumsq = sumsq - s2;
-            }
-            redo = true;
-            maximm = newmax;
-        }
+        minimm = newmin;
+        maximm = newmax;
         const int ns = maximm - minimm;  // mmm.py:253-257
         if (ns < minsky) {
             R.skymod = skymod; R.sigma = -1.0; R.iters = niter;

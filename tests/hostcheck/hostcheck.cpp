@@ -56,7 +56,11 @@ int hc_mmm(const double* v, int n, double readnoise, int minsky, int mxiter, dou
         for (int i = lo; i < hi; i++) sa = sa + p[i];
         return sa;
     };
-    bphot::MmmResult R = bphot::mmm_sorted(at, dsum, psum, (int)s.size(), readnoise, minsky, mxiter);
+    const int ns = (int)s.size();
+    auto first = [&](double v, bool strict) -> int {
+        return strict ? bphot::upper_bound_gt(at, ns, v) : bphot::lower_bound_ge(at, ns, v);
+    };
+    bphot::MmmResult R = bphot::mmm_sorted(at, dsum, psum, first, ns, readnoise, minsky, mxiter);
     out3[0] = R.skymod; out3[1] = R.sigma; out3[2] = R.skew;
     return R.iters;
 }
