@@ -129,6 +129,24 @@ BP_HD double daoerf_xy(double x, double y, const double* a, double* p1, double* 
     return a[0] * fx * fy;
 }
 
+// daoerf is separable: fx and (-up + um) depend only on the pixel's column, fy and (-vp + vm) only on
+// its row (daoerf.py:49-72).  One axis factor, for offset d from the star along that axis, centre c
+// (a[1] or a[2]) and width s (a[3] or a[4]):  f = norm*s*(cdf(u2)-cdf(u1)),  e = -exp(-u2^2/2) + exp(-u1^2/2).
+// A fitting box has ~12 columns + ~12 rows but ~80 pixels, so the kernels evaluate 4 erf/exp pairs per
+// column and row instead of per pixel; daoerf_from_axes() then reproduces daoerf_xy() bit for bit.
+BP_HD void daoerf_axis(double d, double c, double s, double* f, double* e) {
+    const double norm = 2.506628275;
+    const double u2 = (d - c + 0.5) / s, u1 = (d - c - 0.5) / s;
+    *f = norm * s * (gauss_cdf(u2) - gauss_cdf(u1));
+    const double up = exp(-0.5 * (u2 * u2)), um = exp(-0.5 * (u1 * u1));
+    *e = -up + um;
+}
+BP_HD double daoerf_from_axes(double a0, double fx, double ex, double fy, double ey, double* p1, double* p2) {
+    *p1 = a0 * fy * ex;
+    *p2 = a0 * fx * ey;
+    return a0 * fx * fy;
+}
+
 // One row of rinter.py:161-184: cubic through the flat neighbours k-1..k+2 of the table.
 // Flat indices past the end read the last element (rinter.py:117-135 pads the table with it).
 BP_HD void rinter_row(const double* p, long plen, long k, double xd, double* val, double* der) {

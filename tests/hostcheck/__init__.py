@@ -53,3 +53,9 @@ def mmm(v, readnoise=0.0, minsky=20, mxiter=50):
     out = np.empty(3)
     it = lib().hc_mmm(_p(v), C.c_int(v.size), C.c_double(readnoise), C.c_int(minsky), C.c_int(mxiter), _p(out))
     return out[0], out[1], out[2], it
+
+
+def daoerf_separable(xx, yy, gauss):
+    xx = np.ascontiguousarray(xx, np.float64); yy = np.ascontiguousarray(yy, np.float64)
+    gauss = np.ascontiguousarray(gauss, np.float64)
+    return bool(lib().hc_daoerf_separable(_p(xx), _p(yy), C.c_int(xx.size), _p(gauss)))

@@ -1,6 +1,8 @@
 // hostcheck.cpp -- TEST INFRASTRUCTURE.  Compiles the kernels' shared scalar header
 // (pythonphot_b200/csrc/bphot_math.cuh) with g++ so that its arithmetic and the mmm control code can
 // be checked on a machine without a GPU.  Never loaded by the product package.
+#include <string.h>
+
 #include <algorithm>
 #include <vector>
 
@@ -27,6 +29,19 @@ void hc_psfmodel(const double* xx, const double* yy, int n, const double* g, con
         for (int k = 0; k < 5; k++) out[(4 + k) * n + i] = pder[k];
         out[9 * n + i] = z; out[10 * n + i] = dfdx; out[11 * n + i] = dfdy;
     }
+}
+
+// 1 when daoerf_axis/daoerf_from_axes reproduce daoerf_xy bit for bit on every point
+int hc_daoerf_separable(const double* xx, const double* yy, int n, const double* g) {
+    for (int i = 0; i < n; i++) {
+        double p1, p2, q1, q2, fx, ex, fy, ey;
+        const double f = bphot::daoerf_xy(xx[i], yy[i], g, &p1, &p2);
+        bphot::daoerf_axis(xx[i], g[1], g[3], &fx, &ex);
+        bphot::daoerf_axis(yy[i], g[2], g[4], &fy, &ey);
+        const double h = bphot::daoerf_from_axes(g[0], fx, ex, fy, ey, &q1, &q2);
+        if (memcmp(&f, &h, 8) || memcmp(&p1, &q1, 8) || memcmp(&p2, &q2, 8)) return 0;
+    }
+    return 1;
 }
 
 int hc_inv3(double* c9) {

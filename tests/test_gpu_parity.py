@@ -216,8 +216,29 @@ def _run_pk(pp, kind, g_or_f, scale, x, y, sky, radius, image, noise, mask):
     return dict(zip(PK_COLS[kind], pk.pkfit(scale, x, y, sky, radius, xyout=True, recenter=(kind == "pkfit_rec"))))
 
 
-def _check_pk(got, want, cols, x, y, shape, what):
+def _underdetermined(x, y, radius, shape):
+    """Stars with fewer than 4 in-frame pixels inside the fitting radius: their 3x3 normal matrix is rank
+    deficient, and whether LAPACK meets an exactly zero pivot (-> NaN return, pkfit.py:383-406) or a
+    1e-17 one (-> garbage step) hinges on the last bit of erf(); neither implementation is 'right'."""
+    ny_, nx_ = shape
+    R = int(np.ceil(radius)) + 1
+    xi, yi = np.floor(np.nan_to_num(x)).astype(np.int64), np.floor(np.nan_to_num(y)).astype(np.int64)
+    cnt = np.zeros(x.size, dtype=np.int64)
+    for oy in range(-R, R + 1):
+        for ox in range(-R, R + 1):
+            px, py = xi + ox, yi + oy
+            inside = (px >= 0) & (px < nx_) & (py >= 0) & (py < ny_)
+            cnt += inside & (((px - x) ** 2 + (py - y) ** 2) < radius ** 2)
+    return (cnt < 4) & np.isfinite(x) & np.isfinite(y)
+
+
+def _check_pk(got, want, cols, x, y, shape, what, skip=None):
     """want: dict of arrays (NaN = column dropped by a reference early return, only for x/y/chi2)."""
+    if skip is not None and skip.any():
+        keep_ = ~skip
+        got = {k: np.asarray(v)[keep_] for k, v in got.items()}
+        want = {k: np.asarray(v)[keep_] for k, v in want.items()}
+        x, y = x[keep_], y[keep_]
     assert np.array_equal(got["niter"], want["niter"].astype(np.int32)), \
         "%s: niter differs at %s" % (what, np.nonzero(got["niter"] != want["niter"])[0][:8])
     ny_, nx_ = shape
@@ -273,7 +294,9 @@ def test_pkfit_vs_oracle_field(pp, oracle, dtype, kind, radius):
     variant = {"norecent": oracle.PKFIT_NORECENT, "noise": oracle.PKFIT_NOISE, "pkfit_rec": oracle.PKFIT}[kind]
     want = oracle.pkfit(variant, f["image"], f["gauss"], f["psf"], f["ronois"], f["phpadu"], f["noise"], f["mask"],
                         scale0, x, y, sky, radius, recenter=True, nthreads=0)
-    _check_pk(got, want, PK_COLS[kind], x, y, f["image"].shape, "field %s %s r=%g" % (np.dtype(dtype).name, kind, radius))
+    skip = _underdetermined(x, y, radius, f["image"].shape)
+    assert skip.sum() < 0.01 * n
+    _check_pk(got, want, PK_COLS[kind], x, y, f["image"].shape, "field %s %s r=%g" % (np.dtype(dtype).name, kind, radius), skip)
 
 
 def test_pkfit_properties_full_size(pp):

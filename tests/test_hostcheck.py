@@ -77,3 +77,12 @@ def test_inv3_matches_oracle():
         assert st == st2
         if st == 0:
             assert np.array_equal(got, want), "inv3 differs from the oracle bit-for-bit at trial %d" % t
+
+
+def test_daoerf_axis_factors_are_bit_identical():
+    """The kernels evaluate daoerf per column and per row of the fitting box (daoerf.py:49-72 is separable);
+    the product must reproduce the per-pixel formula bit for bit."""
+    rng = np.random.default_rng(5)
+    xx, yy = rng.uniform(-7, 7, 20000), rng.uniform(-7, 7, 20000)
+    for gauss in ([1000.0, 0.0, 0.0, 1.76, 1.70], [6107.2, -0.0126, -0.0037, 1.76, 1.7689], [3.0, 0.3, -0.2, 0.9, 2.5]):
+        assert hostcheck.daoerf_separable(xx, yy, gauss)
