@@ -205,7 +205,9 @@ int bphot_pkfit_device(int variant, const void* d_image, int image_dtype,
     }
     P.errmag = d_errmag; P.chi = d_chi; P.sharp = d_sharp; P.niter = d_niter;
     P.scale_out = d_scale_out; P.x_out = d_x_out; P.y_out = d_y_out; P.chi2 = d_chi2;
-    const size_t smem = (size_t)npsf * npsf * 8 + (size_t)PK_WARPS * P.cap * (PK_NARR * 8 + 4);
+    P.acap = 2 * (int)ceil(radius) + 4;  // int(x+r)+1 - int(x-r) + 1 <= 2r + 3
+    const int narr = (variant == BPHOT_PKFIT_NORECENT) ? PK_NARR_FORCED : PK_NARR_FIT;
+    const size_t smem = (size_t)npsf * npsf * 8 + (size_t)PK_WARPS * ((size_t)P.cap * (narr * 8 + 4) + (size_t)P.acap * 32);
     DevInfo d;
     int rc = dev_info(&d);
     if (rc) return rc;
@@ -215,16 +217,25 @@ int bphot_pkfit_device(int variant, const void* d_image, int image_dtype,
     int grid = 0;
     cudaStream_t st = (cudaStream_t)stream;
     const int nd = (variant == BPHOT_PKFIT) ? image_dtype : noise_dtype;
-#define BP_LAUNCH(TI, TN)                                                              \
-    do {                                                                               \
-        rc = persistent_grid(pkfit_kernel<TI, TN>, PK_THREADS, smem, nblocks, &grid);  \
-        if (rc) return rc;                                                             \
-        pkfit_kernel<TI, TN><<<grid, PK_THREADS, smem, st>>>(P);                       \
+#define BP_LAUNCH(V, TI, TN)                                                              \
+    do {                                                                                  \
+        rc = persistent_grid(pkfit_kernel<V, TI, TN>, PK_THREADS, smem, nblocks, &grid);  \
+        if (rc) return rc;                                                                \
+        pkfit_kernel<V, TI, TN><<<grid, PK_THREADS, smem, st>>>(P);                       \
     } while (0)
-    if (image_dtype == BPHOT_F32 && nd == BPHOT_F32) BP_LAUNCH(float, float);
-    else if (image_dtype == BPHOT_F32) BP_LAUNCH(float, double);
-    else if (nd == BPHOT_F32) BP_LAUNCH(double, float);
-    else BP_LAUNCH(double, double);
+#define BP_LAUNCH_T(V)                                                           \
+    do {                                                                         \
+        if (image_dtype == BPHOT_F32 && nd == BPHOT_F32) BP_LAUNCH(V, float, float);   \
+        else if (image_dtype == BPHOT_F32) BP_LAUNCH(V, float, double);          \
+        else if (nd == BPHOT_F32) BP_LAUNCH(V, double, float);                   \
+        else BP_LAUNCH(V, double, double);                                       \
+    } while (0)
+    if (variant == BPHOT_PKFIT) {  // no noise image: TN is unused
+        if (image_dtype == BPHOT_F32) BP_LAUNCH(0, float, float);
+        else BP_LAUNCH(0, double, double);
+    } else if (variant == BPHOT_PKFIT_NOISE) BP_LAUNCH_T(1);
+    else BP_LAUNCH_T(2);
+#undef BP_LAUNCH_T
 #undef BP_LAUNCH
     g_launches++;
     CU_TRY(cudaGetLastError());

@@ -55,7 +55,8 @@ struct PkfitParams {
     const double* y;
     const double* sky;
     int nstars;
-    int cap;  // per-star pixel-list capacity
+    int cap;   // per-star pixel-list capacity
+    int acap;  // columns / rows of the fitting box (capacity of the per-axis Gaussian factors)
     double* errmag;
     double* chi;
     double* sharp;

@@ -8,10 +8,16 @@
 //
 // Per star, one warp runs the damped Gauss-Newton loop.  Pixels of the fitting box are
 // enumerated in row-major order (ballot-ranked, so the pixel lists are ordered exactly like the
-// reference's np.where output); each lane evaluates the PSF model (integrated Gaussian +
-// bicubic residual look-up, table staged in shared memory) for its pixels; the 3-vector and
-// 3x3 normal matrix are fp64 butterfly reductions (every lane ends with identical bits, so
-// the convergence logic is warp-uniform); the 3x3 solve runs redundantly in registers.
+// reference's np.where output).  The PSF model is the integrated Gaussian, evaluated once per
+// COLUMN and once per ROW of the box (daoerf is separable; bphot_math.cuh daoerf_axis), plus the
+// bicubic residual look-up per pixel (table staged in shared memory).  The 3-vector and 3x3
+// normal matrix are fp64 butterfly reductions (every lane ends with identical bits, so the
+// convergence logic is warp-uniform); the 3x3 solve runs redundantly in registers.
+//
+// The forced fit (variant 2) never moves x, y, so everything that depends only on the pixel --
+// the good-pixel list, model value and derivatives, radial weight, sharpness kernel -- is
+// computed ONCE per star; an iteration is then ~10 fp64 operations per pixel plus the reductions.
+// The reference recomputes all of it every iteration from the same inputs, so the bits agree.
 #include "bphot_device.cuh"
 #include "bphot_params.h"
 
@@ -19,17 +25,310 @@ namespace bphot {
 
 constexpr int PK_WARPS = 4;
 constexpr int PK_THREADS = PK_WARPS * 32;
-constexpr int PK_NARR = 10;  // per-warp scratch arrays of `cap` doubles
+constexpr int PK_NARR_FIT = 10;     // per-warp scratch arrays of `cap` doubles, recentring variants
+constexpr int PK_NARR_FORCED = 7;   // forced variant
 
 struct FitOut {
     double errmag, chi, sharp, scale, x, y, chi2;
     int niter;
 };
 
+struct FitBox {  // pkfit.py:168-177: fitting box, int truncation then clamp
+    long long ixlo, iylo;
+    int ixx, iyy, npix;
+};
+BP_D FitBox fit_box(const PkfitParams& P, double x, double y) {
+    FitBox b;
+    long long ixlo = (long long)(x - P.radius); if (ixlo < 0) ixlo = 0;
+    long long iylo = (long long)(y - P.radius); if (iylo < 0) iylo = 0;
+    long long ixhi = (long long)(x + P.radius) + 1; if (ixhi > P.ncol - 1) ixhi = P.ncol - 1;
+    long long iyhi = (long long)(y + P.radius) + 1; if (iyhi > P.nrow - 1) iyhi = P.nrow - 1;
+    const long long ixx = ixhi - ixlo + 1, iyy = iyhi - iylo + 1;
+    const bool ok = ixx > 0 && iyy > 0 && ixx < 32768 && iyy < 32768 && ixx * iyy < (1LL << 30);
+    b.ixlo = ixlo; b.iylo = iylo;
+    b.ixx = ok ? (int)ixx : 0; b.iyy = ok ? (int)iyy : 0;
+    b.npix = b.ixx * b.iyy;
+    return b;
+}
+
+// Column and row factors of the integrated Gaussian for the whole box (daoerf.py:49-72): lanes
+// 0..ixx-1 take the columns, the next iyy lanes the rows.  AX = [FX | EX | FY | EY], each `acap` long.
+BP_D void fill_axes(const FitBox& b, double x, double y, const double* gauss, double* AX, int acap, int lane) {
+    const int nitem = b.ixx + b.iyy;
+    for (int i = lane; i < nitem; i += 32) {
+        const bool col = i < b.ixx;
+        const int k = col ? i : i - b.ixx;
+        if (k >= acap) continue;
+        const double d = col ? (double)(k + b.ixlo) - x : (double)(k + b.iylo) - y;
+        double f, e;
+        daoerf_axis(d, col ? gauss[1] : gauss[2], col ? gauss[3] : gauss[4], &f, &e);
+        double* dst = AX + (col ? 0 : 2 * acap);
+        dst[k] = f;
+        dst[acap + k] = e;
+    }
+}
+
+// dao_value.py:95-107 for the pixel in column c, row r of the box (offsets dxv, dyv from the star).
+BP_D double model_at(const double* AX, int acap, int c, int r, double dxv, double dyv, const double* gauss,
+                     const double* psf, int npsf, double half, double* dvx, double* dvy) {
+    double p1, p2, dfdx, dfdy;
+    const double e = daoerf_from_axes(gauss[0], AX[c], AX[acap + c], AX[2 * acap + r], AX[3 * acap + r], &p1, &p2);
+    const double v = rinter(psf, npsf, npsf, 2. * dxv + half, 2. * dyv + half, &dfdx, &dfdy);
+    *dvx = 2. * dfdx - p1;
+    *dvy = 2. * dfdy - p2;
+    return e + v;
+}
+
+struct FitState {
+    double clamp0, clamp1, clamp2, dtold0, dtold1, dtold2;
+    double chiold, chi, sharp, errmag, chi2, scale, x, y;
+    int niter;
+};
+BP_D FitState fit_init(double scale, double x, double y) {
+    FitState S;
+    S.clamp0 = S.clamp1 = S.clamp2 = 1.;
+    S.dtold0 = S.dtold1 = S.dtold2 = 0.;
+    S.chiold = 1.;
+    S.chi = S.sharp = S.errmag = S.chi2 = nan64();
+    S.scale = scale; S.x = x; S.y = y;
+    S.niter = 0;
+    return S;
+}
+BP_D FitOut fit_out(const FitState& S) {
+    FitOut o;
+    o.errmag = S.errmag; o.chi = S.chi; o.sharp = S.sharp; o.scale = S.scale; o.x = S.x; o.y = S.y;
+    o.chi2 = S.chi2; o.niter = S.niter;
+    return o;
+}
+// the reference's NaN returns: scale and errmag always NaN; chi / sharp keep their last value in some branches
+BP_D FitOut fit_nan(FitState& S, bool keep_chi, bool keep_sharp) {
+    S.scale = nan64(); S.errmag = nan64();
+    if (!keep_chi) S.chi = nan64();
+    if (!keep_sharp) S.sharp = nan64();
+    return fit_out(S);
+}
+
+// Everything after the normal-equation sums (pkfit.py:379-455 and the same lines of the other two
+// variants).  Returns false when the reference bails out with NaNs; otherwise updates S and sets *loop.
+template <int V>
+BP_D bool fit_tail(const PkfitParams& P, const double* gauss, FitState& S, double* v, double (*c)[3], double numer,
+                   double denom, double schi, double sumwt, bool* loop) {
+    S.chi = schi;
+    if (sumwt > 3.0) {  // pkfit.py:379-381
+        S.chi = 1.2533 * S.chi * sqrt(1. / (sumwt * (sumwt - 3.)));
+        S.chiold = ((sumwt - 3.) * S.chi + 3.) / sumwt;
+    }
+    double csum = 0.;
+    for (int a = 0; a < 3; a++)
+        for (int b = 0; b < 3; b++) csum = csum + c[a][b];
+    bool skip_inv = false;
+    if (V == 1) {  // pkfit_noise.py:399-410: NaN -> inversion skipped; inf -> inv raises -> NaN return
+        if (isnan(csum)) skip_inv = true;
+        else if (isinf(csum)) return false;
+    } else if (isnan(csum) || isinf(csum)) return false;  // pkfit.py:383-406
+    if (!skip_inv && inv3(c)) return false;
+    const double dt0 = v[0] * c[0][0] + v[1] * c[1][0] + v[2] * c[2][0];  // pkfit.py:408-409
+    const double dt1 = v[0] * c[0][1] + v[1] * c[1][1] + v[2] * c[2][1];
+    const double dt2 = v[0] * c[0][2] + v[1] * c[1][2] + v[2] * c[2][2];
+    if (V == 2 && isinf(c[0][0])) return false;  // pkfit_norecent_noise.py:474-483
+    if (S.dtold0 * dt0 < -1.e-38) S.clamp0 = S.clamp0 / 2.;  // pkfit.py:421-423
+    if (S.dtold1 * dt1 < -1.e-38) S.clamp1 = S.clamp1 / 2.;
+    if (S.dtold2 * dt2 < -1.e-38) S.clamp2 = S.clamp2 / 2.;
+    S.dtold0 = dt0; S.dtold1 = dt1; S.dtold2 = dt2;
+    const double adt0 = fabs(dt0), adt1 = fabs(dt1), adt2 = fabs(dt2);
+    double denom2 = dt0 / (5.25 * S.scale);  // pkfit.py:427-429
+    if (denom2 < (-1 * dt0 / (0.84 * S.scale))) denom2 = (-1 * dt0 / (0.84 * S.scale));
+    S.scale = S.scale + dt0 / (1 + denom2 / S.clamp0);
+    if (V == 1 || (V == 0 && P.recenter)) {  // pkfit.py:430-432
+        S.x = S.x + dt1 / (1. + adt1 / (0.5 * S.clamp1));
+        S.y = S.y + dt2 / (1. + adt2 / (0.5 * S.clamp2));
+    }
+    bool redo = false;
+    S.sharp = 2. * gauss[3] * gauss[4] * numer / (gauss[0] * S.scale * denom);  // pkfit.py:440
+    S.errmag = S.chiold * sqrt(c[0][0]);
+    if (V == 0) {  // pkfit.py:442
+        const double a = 0.05 * S.errmag, b = 0.001 * S.scale;
+        const double mx = (b > a) ? b : a;
+        if (adt0 > mx) redo = true;
+    } else if (adt0 > 0.05 * S.errmag || adt0 > 0.001 * S.scale) redo = true;  // pkfit_noise.py:445
+    if (adt1 > 0.01 || adt2 > 0.01) redo = true;
+    *loop = false;
+    if (S.niter < 3) *loop = true;
+    if (redo && S.errmag <= 1.9995 && S.niter < P.maxiter) *loop = true;
+    return true;
+}
+
+// ------------------------------------------------------------ variant 2
+// pkfit_norecent_noise.py:132-531.  W = PK_NARR_FORCED arrays of `cap` doubles, AX = 4 x acap doubles.
 template <typename TI, typename TN>
-BP_D FitOut pkfit_warp(const PkfitParams& P, const double* __restrict__ psf, double* W, int* GIDX,
-                       double scale, double x, double y, const double sky, const int lane) {
-    const int cap = P.cap, variant = P.variant, npsf = P.npsf;
+BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ psf, double* W, double* AX,
+                              double scale, const double x, const double y, const double sky, const int lane) {
+    const int cap = P.cap, acap = P.acap, npsf = P.npsf;
+    double* MV = W;                // model value per good pixel (t[0])
+    double* DVX = W + cap;         // d model / dx, dy  (t[1], t[2] = -scale * these)
+    double* DVY = W + 2 * cap;
+    double* FSUB = W + 3 * cap;    // pixel value
+    double* SIG = W + 4 * cap;     // noise-image value
+    double* W0 = W + 5 * cap;      // radial weight 5/(5 + rsq/(1-rsq)), pkfit_norecent_noise.py:375
+    double* DFS = W + 6 * cap;     // sharpness kernel exp(-rho/2)(rho/2 - 1) where rho <= 36, else NaN (:377-390)
+    const TI* __restrict__ img = reinterpret_cast<const TI*>(P.img);
+    const TN* __restrict__ noise = reinterpret_cast<const TN*>(P.noise);
+    const uint8_t* __restrict__ mask = P.mask;
+    const double gauss[5] = {P.gauss[0], P.gauss[1], P.gauss[2], P.gauss[3], P.gauss[4]};
+    const double radsq = P.radius * P.radius;
+    const double gx2 = gauss[3] * gauss[3], gy2 = gauss[4] * gauss[4];
+    const double half = (double)(npsf - 1) / 2.;
+    const unsigned lt = (1u << lane) - 1u;
+
+    FitState S = fit_init(scale, x, y);
+    // pkfit_norecent_noise.py:156-164 tests NaN before the loop (niter stays 0).  A non-finite position
+    // cannot be truncated to a pixel index (the reference raises); treated as NaN.
+    if (!isfinite(x) || !isfinite(y)) return fit_nan(S, false, false);
+
+    // ---- once per star (the reference redoes this every iteration from identical inputs, :170-240)
+    S.niter = 1;
+    const FitBox b = fit_box(P, x, y);
+    fill_axes(b, x, y, gauss, AX, acap, lane);
+    int ngood = 0;
+    double xmin = KeyTraits<double>::inf(), xmax = -KeyTraits<double>::inf(), ymin = xmin, ymax = xmax;
+    for (int base = 0; base < b.npix; base += 32) {
+        const int p = base + lane;
+        bool ok = false;
+        int r = 0, c = 0;
+        double dxv = 0., dyv = 0., rsq = 0., nz = 0.;
+        if (p < b.npix) {
+            r = p / b.ixx;
+            c = p - r * b.ixx;
+            dyv = (double)(r + b.iylo) - y;
+            dxv = (double)(c + b.ixlo) - x;
+            rsq = (dxv * dxv + dyv * dyv) / radsq;
+            if (rsq < 1.) {  // :212-219
+                const size_t row = (size_t)(b.iylo + r), col = (size_t)(b.ixlo + c);
+                nz = (double)noise[row * P.npitch + col];
+                ok = (nz > 0) && (mask[row * P.mpitch + col] == 0);
+            }
+        }
+        const unsigned mk = __ballot_sync(FULL, ok);
+        if (ok) {
+            const int q = ngood + __popc(mk & lt);
+            if (q < cap) {
+                const size_t row = (size_t)(b.iylo + r), col = (size_t)(b.ixlo + c);
+                FSUB[q] = (double)img[row * P.pitch + col];
+                SIG[q] = nz;
+                W0[q] = 5. / (5. + rsq / (1. - rsq));
+                const double rho = dxv * dxv / gx2 + dyv * dyv / gy2;  // :338
+                const double rh = 0.5 * rho;
+                DFS[q] = (rho <= 36.) ? exp(-rh) * (rh - 1.) : nan64();
+                // model inputs, consumed below once the dao_value guard is known
+                MV[q] = dxv; DVX[q] = dyv; DVY[q] = __longlong_as_double((long long)(r * 65536 + c));
+                xmin = fmin(xmin, dxv); xmax = fmax(xmax, dxv);
+                ymin = fmin(ymin, dyv); ymax = fmax(ymax, dyv);
+            }
+        }
+        ngood += __popc(mk);
+    }
+    if (ngood > cap) ngood = cap;
+    if (ngood == 0) return fit_nan(S, false, false);  // :225-236
+    __syncwarp();
+    // dao_value.py:60-84: any point off the look-up table zeroes the model for ALL points
+    xmin = 2. * warp_min(xmin) + half; xmax = 2. * warp_max(xmax) + half;
+    ymin = 2. * warp_min(ymin) + half; ymax = 2. * warp_max(ymax) + half;
+    const bool guard = (xmin < 1.) || (xmax > npsf - 2.) || (ymin < 1.) || (ymax > npsf - 2.);
+    for (int q = lane; q < ngood; q += 32) {
+        double mval = 0., dvx = 0., dvy = 0.;
+        if (!guard) {
+            const long long rc = __double_as_longlong(DVY[q]);
+            mval = model_at(AX, acap, (int)(rc & 65535), (int)(rc >> 16), MV[q], DVX[q], gauss, psf, npsf, half, &dvx, &dvy);
+        }
+        MV[q] = mval; DVX[q] = dvx; DVY[q] = dvy;
+    }
+    __syncwarp();
+
+    bool loop = true;
+    S.niter = 0;
+    while (loop) {
+        S.niter++;
+        const double chiold = S.chiold;
+        const bool later = S.niter >= 2;
+        double numer = 0., denom = 0., s3 = 0., schi = 0., sumwt = 0.;
+        double v0 = 0., v1 = 0., v2 = 0., c00 = 0., c01 = 0., c02 = 0., c11 = 0., c12 = 0., c22 = 0.;
+        double wmin = KeyTraits<double>::inf();
+        bool wfirst_nan = false, seen = false;
+        int nkept = 0, nl = 0;
+        for (int base = 0; base < ngood; base += 32) {
+            const int q = base + lane;
+            bool keep = false, lil = false;
+            double df = 0., rel = 0., sigsq = 1., wt = 0., t0 = 0., t1 = 0., t2 = 0., dfs = 0.;
+            if (q < ngood) {
+                t0 = MV[q];
+                const double sg = SIG[q];
+                df = FSUB[q] - S.scale * t0 - sky;  // :278
+                rel = df / sg;                       // :327
+                keep = !(later && fabs(rel / chiold) >= 10.);  // :341-373 (rejection restarts from the full list)
+                sigsq = sg * sg;
+                dfs = DFS[q];
+                lil = keep && (dfs == dfs);
+            }
+            const unsigned mk = __ballot_sync(FULL, keep);
+            if (lil) {  // :377-410
+                numer = numer + dfs * df / sigsq;
+                denom = denom + dfs * dfs / sigsq;
+                s3 = s3 + df * df / sigsq;
+                nl++;
+            }
+            if (keep) {
+                wt = W0[q];
+                schi = schi + wt * fabs(rel);  // :411
+                sumwt = sumwt + wt;
+                wt = wt / sigsq;               // :414
+                wmin = fmin(wmin, wt);
+                if (!seen && (mk & lt) == 0u) wfirst_nan = (wt != wt);
+                if (later) {                   // :426-427
+                    const double e = 0.4 * rel / chiold;
+                    const double e2 = e * e, e4 = e2 * e2;
+                    wt = wt / (1. + e4 * e4);
+                }
+                t1 = -S.scale * DVX[q];
+                t2 = -S.scale * DVY[q];
+                v0 = v0 + df * t0 * wt; v1 = v1 + df * t1 * wt; v2 = v2 + df * t2 * wt;
+                c00 = c00 + t0 * t0 * wt; c01 = c01 + t0 * t1 * wt; c02 = c02 + t0 * t2 * wt;
+                c11 = c11 + t1 * t1 * wt; c12 = c12 + t1 * t2 * wt; c22 = c22 + t2 * t2 * wt;
+                nkept++;
+            }
+            if (mk) seen = true;
+        }
+        nkept = warp_sum_int(nkept);
+        if (nkept == 0) return fit_nan(S, false, true);  // :347-356 (every pixel rejected)
+        nl = warp_sum_int(nl);
+        if (nl == 0) return fit_nan(S, false, false);    // :391-401
+        numer = warp_sum(numer); denom = warp_sum(denom);
+        S.chi2 = warp_sum(s3) / (double)(nl - 1);          // :409-410
+        schi = warp_sum(schi);
+        S.chi = schi;
+        sumwt = warp_sum(sumwt);
+        {   // :416-424; python min(): a NaN first element wins
+            wmin = warp_min(wmin);
+            const bool fn = __any_sync(FULL, wfirst_nan);
+            if (!fn && wmin > 100000) return fit_nan(S, false, false);
+        }
+        double v[3], c[3][3];
+        v[0] = warp_sum(v0); v[1] = warp_sum(v1); v[2] = warp_sum(v2);
+        c[0][0] = warp_sum(c00); c[1][1] = warp_sum(c11); c[2][2] = warp_sum(c22);
+        c[0][1] = c[1][0] = warp_sum(c01);
+        c[0][2] = c[2][0] = warp_sum(c02);
+        c[1][2] = c[2][1] = warp_sum(c12);
+        if (!fit_tail<2>(P, gauss, S, v, c, numer, denom, schi, sumwt, &loop)) return fit_nan(S, false, false);
+    }
+    return fit_out(S);
+}
+
+// ------------------------------------------------------- variants 0 and 1
+// pkfit.py:132-458 (V = 0) and pkfit_noise.py:131-462 (V = 1): x, y move, so the pixel list and the model
+// are rebuilt every iteration.  W = PK_NARR_FIT arrays of `cap` doubles, GIDX = cap ints, AX = 4 x acap doubles.
+template <int V, typename TI, typename TN>
+BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__ psf, double* W, int* GIDX, double* AX,
+                                double scale, double x, double y, const double sky, const int lane) {
+    const int cap = P.cap, acap = P.acap, npsf = P.npsf;
     double* DX = W;              // pass A -> B
     double* DY = W + cap;
     double* DF = DX;             // pass B onwards (same slots, same owner lane)
@@ -46,65 +345,41 @@ BP_D FitOut pkfit_warp(const PkfitParams& P, const double* __restrict__ psf, dou
     const TN* __restrict__ noise = reinterpret_cast<const TN*>(P.noise);
     const uint8_t* __restrict__ mask = P.mask;
     const double gauss[5] = {P.gauss[0], P.gauss[1], P.gauss[2], P.gauss[3], P.gauss[4]};
-    const double radius = P.radius, radsq = radius * radius;
+    const double radsq = P.radius * P.radius;
     const double gx2 = gauss[3] * gauss[3], gy2 = gauss[4] * gauss[4];
     const double pkerr = 0.027 / ((gauss[3] * gauss[4]) * (gauss[3] * gauss[4]));  // pkfit.py:146
     const double half = (double)(npsf - 1) / 2.;
     const unsigned lt = (1u << lane) - 1u;
 
-    double clamp0 = 1., clamp1 = 1., clamp2 = 1., dtold0 = 0., dtold1 = 0., dtold2 = 0.;
-    double chiold = 1., chi = nan64(), sharp = nan64(), errmag = nan64(), chi2 = nan64();
-    int niter = 0;
-
-#define PK_RETURN()                                                                              \
-    do {                                                                                         \
-        FitOut o_;                                                                               \
-        o_.errmag = errmag; o_.chi = chi; o_.sharp = sharp; o_.scale = scale; o_.x = x; o_.y = y; \
-        o_.chi2 = chi2; o_.niter = niter;                                                        \
-        return o_;                                                                               \
-    } while (0)
-#define PK_RETURN_NAN(keep_chi, keep_sharp)      \
-    do {                                         \
-        scale = nan64(); errmag = nan64();       \
-        if (!(keep_chi)) chi = nan64();          \
-        if (!(keep_sharp)) sharp = nan64();      \
-        PK_RETURN();                             \
-    } while (0)
-
-    // pkfit_norecent_noise.py:156-164 tests NaN before the loop (niter stays 0); the others inside it.
-    // A non-finite position cannot be truncated to a pixel index (the reference raises); treated as NaN.
-    const bool badpos = !isfinite(x) || !isfinite(y);
-    if (variant == 2 && badpos) PK_RETURN_NAN(0, 0);
-
+    FitState S = fit_init(scale, x, y);
     bool loop = true;
     while (loop) {
-        niter++;
-        if (badpos) PK_RETURN_NAN(0, 0);  // pkfit.py:158-166
-        // pkfit.py:168-177: fitting box, int truncation then clamp
-        long long ixlo = (long long)(x - radius); if (ixlo < 0) ixlo = 0;
-        long long iylo = (long long)(y - radius); if (iylo < 0) iylo = 0;
-        long long ixhi = (long long)(x + radius) + 1; if (ixhi > P.ncol - 1) ixhi = P.ncol - 1;
-        long long iyhi = (long long)(y + radius) + 1; if (iyhi > P.nrow - 1) iyhi = P.nrow - 1;
-        const long long ixx = ixhi - ixlo + 1, iyy = iyhi - iylo + 1;
-        const int npix = (ixx > 0 && iyy > 0 && ixx * iyy < (1LL << 30)) ? (int)(ixx * iyy) : 0;
+        S.niter++;
+        // pkfit.py:158-166.  A non-finite position cannot be truncated to a pixel index (the reference raises); treated as NaN.
+        if (!isfinite(S.x) || !isfinite(S.y)) return fit_nan(S, false, false);
+        const double scl = S.scale, chiold = S.chiold;
+        const FitBox b = fit_box(P, S.x, S.y);
+        fill_axes(b, S.x, S.y, gauss, AX, acap, lane);
 
         // ---- pass A: ordered list of good pixels (pkfit.py:184-219, pkfit_noise.py:206-208)
         int ngood = 0;
         double xmin = KeyTraits<double>::inf(), xmax = -KeyTraits<double>::inf(), ymin = xmin, ymax = xmax;
-        for (int base = 0; base < npix; base += 32) {
+        for (int base = 0; base < b.npix; base += 32) {
             const int p = base + lane;
             bool ok = false;
+            int r = 0, c = 0;
             double dxv = 0., dyv = 0., rsq = 0., rho = 0., fv = 0., nz = 0.;
-            if (p < npix) {
-                const int r = p / (int)ixx, c = p - r * (int)ixx;
-                dyv = (double)(r + iylo) - y;
-                dxv = (double)(c + ixlo) - x;
+            if (p < b.npix) {
+                r = p / b.ixx;
+                c = p - r * b.ixx;
+                dyv = (double)(r + b.iylo) - S.y;
+                dxv = (double)(c + b.ixlo) - S.x;
                 const double dysq = dyv * dyv, dxsq = dxv * dxv;
                 rsq = (dxsq + dysq) / radsq;
                 ok = rsq < 1.;
                 if (ok) {
-                    const size_t row = (size_t)(iylo + r), col = (size_t)(ixlo + c);
-                    if (variant != 0) {
+                    const size_t row = (size_t)(b.iylo + r), col = (size_t)(b.ixlo + c);
+                    if (V != 0) {
                         nz = (double)noise[row * P.npitch + col];
                         ok = (nz > 0) && (mask[row * P.mpitch + col] == 0);
                     }
@@ -119,7 +394,8 @@ BP_D FitOut pkfit_warp(const PkfitParams& P, const double* __restrict__ psf, dou
                 const int q = ngood + __popc(mk & lt);
                 if (q < cap) {
                     DX[q] = dxv; DY[q] = dyv; RSQ[q] = rsq; RHO[q] = rho; FSUB[q] = fv;
-                    if (variant != 0) { SIG[q] = nz; SIGSQ[q] = nz * nz; }
+                    GIDX[q] = r * 65536 + c;
+                    if (V != 0) { SIG[q] = nz; SIGSQ[q] = nz * nz; }
                     xmin = fmin(xmin, dxv); xmax = fmax(xmax, dxv);
                     ymin = fmin(ymin, dyv); ymax = fmax(ymax, dyv);
                 }
@@ -127,7 +403,7 @@ BP_D FitOut pkfit_warp(const PkfitParams& P, const double* __restrict__ psf, dou
             ngood += __popc(mk);
         }
         if (ngood > cap) ngood = cap;
-        if (ngood == 0) PK_RETURN_NAN(0, 0);  // pkfit.py:211-219
+        if (ngood == 0) return fit_nan(S, false, false);  // pkfit.py:211-219
         __syncwarp();
         // dao_value.py:60-84: any point off the look-up table zeroes the model for ALL points
         xmin = 2. * warp_min(xmin) + half; xmax = 2. * warp_max(xmax) + half;
@@ -137,13 +413,16 @@ BP_D FitOut pkfit_warp(const PkfitParams& P, const double* __restrict__ psf, dou
         // ---- pass B: model, residuals (pkfit.py:224-283)
         for (int q = lane; q < ngood; q += 32) {
             double mval = 0., dvx = 0., dvy = 0.;
-            if (!guard) mval = psf_value(DX[q], DY[q], gauss, psf, npsf, &dvx, &dvy);
+            if (!guard) {
+                const int rc = GIDX[q];
+                mval = model_at(AX, acap, rc & 65535, rc >> 16, DX[q], DY[q], gauss, psf, npsf, half, &dvx, &dvy);
+            }
             T0[q] = mval;
-            T1[q] = -scale * dvx;
-            T2[q] = -scale * dvy;
+            T1[q] = -scl * dvx;
+            T2[q] = -scl * dvy;
             const double fsub = FSUB[q];
-            const double df = fsub - scale * mval - sky;
-            if (variant == 0) {  // pkfit.py:277-282 (ronois enters un-squared, as in the reference)
+            const double df = fsub - scl * mval - sky;
+            if (V == 0) {  // pkfit.py:277-282 (ronois enters un-squared, as in the reference)
                 double fpos = fsub - df;
                 if (fpos < 0.) fpos = 0.;
                 const double s2 = fpos / P.phpadu + P.ronois + (0.0075 * fpos) * (0.0075 * fpos) +
@@ -159,15 +438,12 @@ BP_D FitOut pkfit_warp(const PkfitParams& P, const double* __restrict__ psf, dou
         // ---- 10-sigma rejection from the second iteration on (pkfit.py:296-321), ordered compaction
         int m = ngood;
         bool compacted = false;
-        if (niter >= 2) {
+        if (S.niter >= 2) {
             int nbad = 0;
             for (int q = lane; q < ngood; q += 32)
                 if (fabs(REL[q] / chiold) >= 10.) nbad++;
             nbad = warp_sum_int(nbad);
-            if (nbad == ngood) {
-                if (variant == 2) PK_RETURN_NAN(0, 1);  // pkfit_norecent_noise.py:347-356
-                PK_RETURN_NAN(1, 1);                    // pkfit.py:303-309
-            }
+            if (nbad == ngood) return fit_nan(S, true, true);  // pkfit.py:303-309
             if (nbad > 0) {
                 compacted = true;
                 m = 0;
@@ -193,14 +469,12 @@ BP_D FitOut pkfit_warp(const PkfitParams& P, const double* __restrict__ psf, dou
             }
         }
         // pkfit.py keeps t un-compacted and slices t[:, 0:lenwt] (pkfit.py:369-372): the k-th surviving
-        // pixel is paired with the k-th ORIGINAL pixel's t.  The noise variants index t by goodind.
-        const bool direct = !compacted || variant == 0;
+        // pixel is paired with the k-th ORIGINAL pixel's t.  pkfit_noise indexes t by goodind.
+        const bool direct = !compacted || V == 0;
 
         // ---- weights and sums (pkfit.py:323-372)
-        double numer = 0., denom = 0., s3 = 0., schi = 0., sumwt = 0.;
+        double numer = 0., denom = 0., schi = 0., sumwt = 0.;
         double v0 = 0., v1 = 0., v2 = 0., c00 = 0., c01 = 0., c02 = 0., c11 = 0., c12 = 0., c22 = 0.;
-        double wmin = KeyTraits<double>::inf();
-        bool wfirst_nan = false;
         int nl = 0;
         for (int base = 0; base < m; base += 32) {
             const int q = base + lane;
@@ -212,7 +486,7 @@ BP_D FitOut pkfit_warp(const PkfitParams& P, const double* __restrict__ psf, dou
                 const double rh = 0.5 * rho;
                 const double dfdsig = exp(-rh) * (rh - 1.);  // pkfit.py:336
                 double s;
-                if (variant == 0) {  // pkfit.py:341-346
+                if (V == 0) {  // pkfit.py:341-346
                     double fpos = FSUB[q];
                     if (fpos - sky < 0.) fpos = sky;
                     s = fpos / P.phpadu + P.ronois + (0.0075 * fpos) * (0.0075 * fpos) +
@@ -222,10 +496,9 @@ BP_D FitOut pkfit_warp(const PkfitParams& P, const double* __restrict__ psf, dou
                     s = sg * sg;  // pkfit_noise.py:361
                 }
                 // pkfit.py:350 pairs dfdsig with df[0:len(lilrho)] (the FIRST nl residuals)
-                const double dfv = (variant == 0) ? DF[nl + __popc(mk & lt)] : DF[q];
+                const double dfv = (V == 0) ? DF[nl + __popc(mk & lt)] : DF[q];
                 numer = numer + dfdsig * dfv / s;
                 denom = denom + dfdsig * dfdsig / s;
-                s3 = s3 + dfv * dfv / s;
             }
             nl += __popc(mk);
             if (in) {
@@ -234,9 +507,7 @@ BP_D FitOut pkfit_warp(const PkfitParams& P, const double* __restrict__ psf, dou
                 schi = schi + wt * fabs(rel);               // pkfit.py:359
                 sumwt = sumwt + wt;
                 wt = wt / SIGSQ[q];                          // pkfit.py:362
-                if (q == 0) wfirst_nan = (wt != wt);
-                wmin = fmin(wmin, wt);
-                if (niter >= 2) {  // pkfit.py:364
+                if (S.niter >= 2) {  // pkfit.py:364
                     const double e = 0.4 * rel / chiold;
                     const double e2 = e * e, e4 = e2 * e2;
                     wt = wt / (1. + e4 * e4);
@@ -248,82 +519,41 @@ BP_D FitOut pkfit_warp(const PkfitParams& P, const double* __restrict__ psf, dou
                 c11 = c11 + t1 * t1 * wt; c12 = c12 + t1 * t2 * wt; c22 = c22 + t2 * t2 * wt;
             }
         }
-        if (nl == 0) PK_RETURN_NAN(0, 0);  // pkfit.py:325-333
+        if (nl == 0) return fit_nan(S, false, false);  // pkfit.py:325-333
         numer = warp_sum(numer); denom = warp_sum(denom);
-        if (variant == 2) chi2 = warp_sum(s3) / (double)(nl - 1);  // pkfit_norecent_noise.py:409-410
-        chi = warp_sum(schi);
+        schi = warp_sum(schi);
+        S.chi = schi;
         sumwt = warp_sum(sumwt);
-        if (variant == 2) {  // pkfit_norecent_noise.py:416-424; python min(): a NaN first element wins
-            wmin = warp_min(wmin);
-            const bool fn = __any_sync(FULL, wfirst_nan);
-            if (!fn && wmin > 100000) PK_RETURN_NAN(0, 0);
-        }
         double v[3], c[3][3];
         v[0] = warp_sum(v0); v[1] = warp_sum(v1); v[2] = warp_sum(v2);
         c[0][0] = warp_sum(c00); c[1][1] = warp_sum(c11); c[2][2] = warp_sum(c22);
         c[0][1] = c[1][0] = warp_sum(c01);
         c[0][2] = c[2][0] = warp_sum(c02);
         c[1][2] = c[2][1] = warp_sum(c12);
-        if (sumwt > 3.0) {  // pkfit.py:379-381
-            chi = 1.2533 * chi * sqrt(1. / (sumwt * (sumwt - 3.)));
-            chiold = ((sumwt - 3.) * chi + 3.) / sumwt;
-        }
-        double csum = 0.;
-        for (int a = 0; a < 3; a++)
-            for (int b = 0; b < 3; b++) csum = csum + c[a][b];
-        bool skip_inv = false;
-        if (variant == 1) {  // pkfit_noise.py:399-410: NaN -> inversion skipped; inf -> inv raises -> NaN return
-            if (isnan(csum)) skip_inv = true;
-            else if (isinf(csum)) PK_RETURN_NAN(0, 0);
-        } else if (isnan(csum) || isinf(csum)) PK_RETURN_NAN(0, 0);  // pkfit.py:383-406
-        if (!skip_inv && inv3(c)) PK_RETURN_NAN(0, 0);
-        double dt0 = v[0] * c[0][0] + v[1] * c[1][0] + v[2] * c[2][0];  // pkfit.py:408-409
-        double dt1 = v[0] * c[0][1] + v[1] * c[1][1] + v[2] * c[2][1];
-        double dt2 = v[0] * c[0][2] + v[1] * c[1][2] + v[2] * c[2][2];
-        if (variant == 2 && isinf(c[0][0])) PK_RETURN_NAN(0, 0);  // pkfit_norecent_noise.py:474-483
-        if (dtold0 * dt0 < -1.e-38) clamp0 = clamp0 / 2.;  // pkfit.py:421-423
-        if (dtold1 * dt1 < -1.e-38) clamp1 = clamp1 / 2.;
-        if (dtold2 * dt2 < -1.e-38) clamp2 = clamp2 / 2.;
-        dtold0 = dt0; dtold1 = dt1; dtold2 = dt2;
-        const double adt0 = fabs(dt0), adt1 = fabs(dt1), adt2 = fabs(dt2);
-        double denom2 = dt0 / (5.25 * scale);  // pkfit.py:427-429
-        if (denom2 < (-1 * dt0 / (0.84 * scale))) denom2 = (-1 * dt0 / (0.84 * scale));
-        scale = scale + dt0 / (1 + denom2 / clamp0);
-        if (variant == 1 || (variant == 0 && P.recenter)) {  // pkfit.py:430-432
-            x = x + dt1 / (1. + adt1 / (0.5 * clamp1));
-            y = y + dt2 / (1. + adt2 / (0.5 * clamp2));
-        }
-        bool redo = false;
-        sharp = 2. * gauss[3] * gauss[4] * numer / (gauss[0] * scale * denom);  // pkfit.py:440
-        errmag = chiold * sqrt(c[0][0]);
-        if (variant == 0) {  // pkfit.py:442
-            const double a = 0.05 * errmag, b = 0.001 * scale;
-            const double mx = (b > a) ? b : a;
-            if (adt0 > mx) redo = true;
-        } else if (adt0 > 0.05 * errmag || adt0 > 0.001 * scale) redo = true;  // pkfit_noise.py:445
-        if (adt1 > 0.01 || adt2 > 0.01) redo = true;
-        if (niter >= 3) loop = false;
-        if (redo && errmag <= 1.9995 && niter < P.maxiter) loop = true;
+        if (!fit_tail<V>(P, gauss, S, v, c, numer, denom, schi, sumwt, &loop)) return fit_nan(S, false, false);
         __syncwarp();
     }
-    PK_RETURN();
-#undef PK_RETURN
-#undef PK_RETURN_NAN
+    return fit_out(S);
 }
 
-template <typename TI, typename TN>
+// Shared memory: [psf table | per-warp W arrays | per-warp AX | per-warp GIDX (variants 0, 1)].
+template <int V, typename TI, typename TN>
 __global__ void __launch_bounds__(PK_THREADS) pkfit_kernel(const PkfitParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int NARR = (V == 2) ? PK_NARR_FORCED : PK_NARR_FIT;
     double* psf = reinterpret_cast<double*>(smem_raw);
     const int ntab = P.npsf * P.npsf;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    double* W = psf + ntab + (size_t)warp * PK_NARR * P.cap;
-    int* GIDX = reinterpret_cast<int*>(psf + ntab + (size_t)PK_WARPS * PK_NARR * P.cap) + (size_t)warp * P.cap;
+    double* W = psf + ntab + (size_t)warp * NARR * P.cap;
+    double* AX = psf + ntab + (size_t)PK_WARPS * NARR * P.cap + (size_t)warp * 4 * P.acap;
+    int* GIDX = reinterpret_cast<int*>(psf + ntab + (size_t)PK_WARPS * (NARR * P.cap + 4 * P.acap)) + (size_t)warp * P.cap;
     for (int i = threadIdx.x; i < ntab; i += PK_THREADS) psf[i] = P.psf[i];
     __syncthreads();
     const int wstride = gridDim.x * PK_WARPS;
     for (int s = blockIdx.x * PK_WARPS + warp; s < P.nstars; s += wstride) {
-        FitOut o = pkfit_warp<TI, TN>(P, psf, W, GIDX, P.scale[s], P.x[s], P.y[s], P.sky[s], lane);
+        FitOut o;
+        if constexpr (V == 2) o = pkfit_forced_warp<TI, TN>(P, psf, W, AX, P.scale[s], P.x[s], P.y[s], P.sky[s], lane);
+        else o = pkfit_recenter_warp<V, TI, TN>(P, psf, W, GIDX, AX, P.scale[s], P.x[s], P.y[s], P.sky[s], lane);
         if (lane == 0) {
             P.errmag[s] = o.errmag; P.chi[s] = o.chi; P.sharp[s] = o.sharp; P.niter[s] = o.niter;
             P.scale_out[s] = o.scale; P.x_out[s] = o.x; P.y_out[s] = o.y; P.chi2[s] = o.chi2;
@@ -331,11 +561,6 @@ __global__ void __launch_bounds__(PK_THREADS) pkfit_kernel(const PkfitParams P) 
         __syncwarp();
     }
 }
-
-template __global__ void pkfit_kernel<float, float>(const PkfitParams);
-template __global__ void pkfit_kernel<float, double>(const PkfitParams);
-template __global__ void pkfit_kernel<double, float>(const PkfitParams);
-template __global__ void pkfit_kernel<double, double>(const PkfitParams);
 
 // ---------------------------------------------------- unit-test kernel
 // dao_value.dao_value(xx, yy, gauss, psf, deriv=True) for n points, plus the pieces it is made of
