@@ -1,21 +1,21 @@
-// aper_kernel.cu -- concentric-aperture photometry + mmm sky, one 128-thread CTA per star (sm_100a).
+// aper_kernel.cu -- concentric-aperture photometry + mmm sky (sm_100a).
 //
 // Replaces the per-star Python loop of PythonPhot/aper.py:217-417 and its callees
-// mmm.mmm (mmm.py:7-314) and pixwt.Pixwt (pixwt.py:8-235).  Per star:
+// mmm.mmm (mmm.py:7-314) and pixwt.Pixwt (pixwt.py:8-235), in two launches per batch of stars.
+// Stage 1, one 128-thread CTA per star:
 //   P1  the four warps gather the sky-annulus pixels of the (2*skyrad_out+1)^2 stamp into shared
 //       memory, row by row, visiting only the two column spans of each row that can intersect
 //       the annulus (coalesced; aper.py:240-267);
 //   P2  the keys are sorted (np.sort at mmm.py:119) by a bitonic network that lives in REGISTERS:
 //       each thread holds K consecutive keys, compare-exchanges between a thread's own keys are
 //       FMNMX pairs, exchanges inside a warp are shuffles, and only the 3 (K=32) stages that cross
-//       warps go through shared memory;
-//   P3  warp 0 runs the mmm clipping loop on the sorted vector (32-way ballot searches in place of
-//       the reference's index walk, fp64 range sums by warp shuffle) WHILE warps 1..3 do the
-//       aperture sums: pixels are classified geometrically (inside / outside / crossed by the
-//       circle) and only crossed pixels go through pixwt, four lanes per pixel (one per side);
-//   P4  combines both into flux / error / magnitude (aper.py:383-403).
-// A persistent grid strides over the star list.  K = 0 selects the fallback for annuli of more
-// than 4096 pixels: the same phases with a shared-memory bitonic sort.
+//       warps go through shared memory; the sorted vector goes to a global scratch row;
+//   P3  aperture sums: pixels are classified geometrically (inside / outside / crossed by the
+//       circle) and only crossed pixels go through pixwt, four lanes per pixel (one per side).
+// Stage 2, one WARP per star: the mmm clipping loop on the sorted row (32-way ballot searches in
+// place of the reference's index walk, fp64 range sums by warp shuffle), then flux / error /
+// magnitude (aper.py:383-403).
+// K = 0 selects the fallback for annuli of more than 4096 pixels: shared-memory bitonic sort.
 #include "bphot_device.cuh"
 #include "bphot_params.h"
 
@@ -23,7 +23,6 @@ namespace bphot {
 
 constexpr int AP_THREADS = 128;
 constexpr int AP_WARPS = AP_THREADS / 32;
-constexpr int AP_WORKERS = AP_WARPS - 1;  // warps that do aperture sums during mmm
 
 BP_D float kmin(float a, float b) { return fminf(a, b); }
 BP_D float kmax(float a, float b) { return fmaxf(a, b); }
@@ -140,6 +139,12 @@ struct SortedView {
     int shift;
     BP_D double operator()(int i) const { return (double)p[i + (i >> shift)]; }
 };
+// Sorted keys in global memory (written by an earlier launch, read-only here).
+template <typename T>
+struct GlobalView {
+    const T* __restrict__ p;
+    BP_D double operator()(int i) const { return (double)__ldg(p + i); }
+};
 
 // First index in [0, n) whose element satisfies the monotone predicate (n if none): 32 probes
 // per round instead of one, so 4096 keys take 3 dependent shared-memory reads, not 12.
@@ -166,8 +171,8 @@ BP_D int warp_first_true(const Pred& pred, int n, int lane) {
 // mmm.py:106-314 on an already sorted, NaN-free vector, executed by ONE warp: the control code is
 // mmm_sorted() of bphot_math.cuh (all lanes carry identical scalars); the range sums are
 // lane-strided fp64 partials combined by a butterfly, so every lane sees the same bits.
-template <typename T>
-BP_D MmmResult mmm_warp(const SortedView<T> at, int nsky, double readnoise, int minsky, int mxiter, int lane) {
+template <typename View>
+BP_D MmmResult mmm_warp(const View at, int nsky, double readnoise, int minsky, int mxiter, int lane) {
     auto delta_sums = [&](int lo, int hi, double skymid, double* s1, double* s2) {
         double a = 0.0, q = 0.0;
         for (int i = lo + lane; i < hi; i += 32) {
@@ -224,32 +229,49 @@ BP_D StarGeom star_geom(const AperParams& P, double x, double y) {
     return g;
 }
 
-// P1: one warp's rows of the annulus gather (aper.py:240-267).  Per row only the columns that
-// can lie in the annulus are visited: [a0, a1] minus the strictly-inside-the-inner-circle span
-// [b0, b1]; the exact fp64 membership test of the reference decides.  Returns this lane's copy
-// of the warp's count of selected pixels (NaNs included, as aper's nsky counts them).
-template <typename T>
-BP_D int gather_rows(const AperParams& P, const T* __restrict__ stamp, const StarGeom& g, double rinsq, double routsq,
-                     T* keys, int* s_nvalid, int warp, int lane) {
-    int nsel = 0;
-    for (int r = warp; r < g.ny; r += AP_WARPS) {
+// P1a: candidate column spans of every stamp row, one row per thread (aper.py:240-267).  Row r can
+// only hold annulus pixels in [a0, a1] (outer chord, +-1 px) minus [b0, b1] (columns strictly inside
+// the inner circle with a 1 px margin); rows that miss the outer circle get an empty span.
+// span[4*r .. 4*r+3] = a0, b0, b1, a1.
+BP_D void row_spans(const StarGeom& g, double rinsq, double routsq, int* span, int tid) {
+    for (int r = tid; r < g.ny; r += AP_THREADS) {
         const double dyv = (double)r - g.dy, dysq = dyv * dyv;
         const double rem = routsq - dysq;
-        if (rem < 0.0) continue;  // rsq >= dysq > routsq for the whole row
-        const double hw = sqrt(rem) + 1.0;
-        int a0 = (int)floor(g.dx - hw), a1 = (int)ceil(g.dx + hw);
-        if (a0 < 0) a0 = 0;
-        if (a1 > g.nx - 1) a1 = g.nx - 1;
-        int b0 = a1 + 1, b1 = a1;  // empty exclusion span
-        const double remi = rinsq - dysq;
-        if (remi > 4.0) {  // columns with |c - dx| <= sqrt(remi) - 1 have rsq < rinsq
-            const double hwi = sqrt(remi) - 1.0;
-            int e0 = (int)ceil(g.dx - hwi), e1 = (int)floor(g.dx + hwi);
-            if (e0 < a0) e0 = a0;
-            if (e1 > a1) e1 = a1;
-            if (e0 <= e1) { b0 = e0; b1 = e1; }
+        int a0 = 0, a1 = -1, b0 = 0, b1 = -1;
+        if (rem >= 0.0) {  // otherwise rsq >= dysq > routsq for the whole row
+            const double hw = sqrt(rem) + 1.0;
+            a0 = (int)floor(g.dx - hw);
+            a1 = (int)ceil(g.dx + hw);
+            if (a0 < 0) a0 = 0;
+            if (a1 > g.nx - 1) a1 = g.nx - 1;
+            b0 = a1 + 1; b1 = a1;  // empty exclusion span
+            const double remi = rinsq - dysq;
+            if (remi > 4.0) {  // columns with |c - dx| <= sqrt(remi) - 1 have rsq < rinsq
+                const double hwi = sqrt(remi) - 1.0;
+                int e0 = (int)ceil(g.dx - hwi), e1 = (int)floor(g.dx + hwi);
+                if (e0 < a0) e0 = a0;
+                if (e1 > a1) e1 = a1;
+                if (e0 <= e1) { b0 = e0; b1 = e1; }
+            }
         }
+        span[4 * r + 0] = a0; span[4 * r + 1] = b0; span[4 * r + 2] = b1; span[4 * r + 3] = a1;
+    }
+}
+
+// P1b: one warp's rows of the annulus gather.  The reference's own fp64 test rin^2 <= rsq <= rout^2 and
+// bad-pixel window decide membership; loads are coalesced along the row.  Returns this lane's copy of the
+// warp's count of selected pixels (NaNs included, as aper's nsky counts them; the key array drops them).
+template <typename T>
+BP_D int gather_rows(const AperParams& P, const T* __restrict__ stamp, const StarGeom& g, double rinsq, double routsq,
+                     const int* span, T* keys, int* s_nvalid, int warp, int lane) {
+    int nsel = 0;
+    const bool window = P.badlo != P.badhi;
+    for (int r = warp; r < g.ny; r += AP_WARPS) {
+        const int4 sp = *reinterpret_cast<const int4*>(span + 4 * r);
+        const int a0 = sp.x, b0 = sp.y, b1 = sp.z, a1 = sp.w;
         const int nl = b0 - a0, tot = nl + (a1 - b1);
+        if (tot <= 0) continue;
+        const double dyv = (double)r - g.dy, dysq = dyv * dyv;
         const T* __restrict__ row = stamp + (size_t)r * P.pitch;
         for (int base = 0; base < tot; base += 32) {
             const int t = base + lane;
@@ -262,7 +284,7 @@ BP_D int gather_rows(const AperParams& P, const T* __restrict__ stamp, const Sta
                 if (rsq >= rinsq && rsq <= routsq) {
                     val = row[c];
                     const double dv = (double)val;
-                    sel = !(P.badlo != P.badhi && (dv < P.badlo || dv > P.badhi));
+                    sel = !(window && (dv < P.badlo || dv > P.badhi));
                     valid = sel && (val == val);  // mmm.py:106 drops NaNs; aper's nsky keeps them
                 }
             }
@@ -281,18 +303,61 @@ BP_D int gather_rows(const AperParams& P, const T* __restrict__ stamp, const Sta
     return nsel;
 }
 
-// P3 (worker warps): this warp's share of one aperture's pixel sums (aper.py:310-380).
-// `w` = worker index 0..AP_WORKERS-1; sx/sy/sw = 32 doubles of per-warp scratch each.
+// Per-warp list of pixels the aperture circle crosses (they need pixwt): centre, stamp position, weight.
+constexpr int AP_LIST = 64;
+struct CrossList {
+    double x[AP_LIST], y[AP_LIST], w[AP_LIST];
+    int rc[AP_LIST];
+};
+
+// One pixel value into the running sums, with the reference's bad-pixel bookkeeping (aper.py:359-378).
+template <typename T>
+BP_D void add_pixel(const AperParams& P, const T* __restrict__ stamp, int r, int c, double wgt, bool full, ApPartial& A) {
+    double v = (double)stamp[(size_t)r * P.pitch + c];
+    if (!isfinite(v)) { A.flags |= 1; v = 0.0; }  // aper.py:359-366
+    if (P.badlo < P.badhi && (v <= P.badlo || v >= P.badhi)) { A.flags |= 2; v = 0.0; }  // aper.py:367-378
+    if (P.exact || full) {
+        A.sfull = A.sfull + v * wgt;
+        A.nfull += 1;
+    } else {
+        A.spart = A.spart + v * wgt;
+        A.wpart = A.wpart + wgt;
+        A.npart += 1;
+    }
+}
+
+// Exact overlap weights of the listed pixels: four lanes per pixel, one per Oneside term, recombined in
+// Intarea's order of addition (pixwt.py:234-235); then every lane adds its pixels to the sums.
+template <typename T>
+BP_D void flush_cross_list(const AperParams& P, const T* __restrict__ stamp, const StarGeom& g, double ap,
+                           CrossList* L, int cnt, int lane, ApPartial& A) {
+    __syncwarp();
+    for (int g0 = 0; g0 < cnt; g0 += 8) {
+        const int j = g0 + (lane >> 2), side = lane & 3;
+        double sd = 0.0;
+        if (j < cnt) sd = pixwt_side(g.dx, g.dy, ap, L->x[j], L->y[j], side);
+        const double s1 = __shfl_down_sync(FULL, sd, 1), s2 = __shfl_down_sync(FULL, sd, 2), s3 = __shfl_down_sync(FULL, sd, 3);
+        if (side == 0 && j < cnt) L->w[j] = ((sd + s1) + s2) + s3;
+    }
+    __syncwarp();
+    for (int i = lane; i < cnt; i += 32) {
+        const double wgt = L->w[i];  // negative weights count as 0 (aper.py:329); only positive ones are used (:330)
+        if (wgt > 0.0) add_pixel<T>(P, stamp, L->rc[i] >> 16, L->rc[i] & 65535, wgt, false, A);
+    }
+    __syncwarp();
+}
+
+// This warp's share (chunks w, w+nw, ...) of one aperture's pixel sums (aper.py:310-380).
 template <typename T>
 BP_D ApPartial aperture_warp(const AperParams& P, const T* __restrict__ stamp, const StarGeom& g, double ap,
-                             int w, int lane, double* sx, double* sy, double* sw) {
+                             int w, int nw, int lane, CrossList* L) {
     ApPartial A;
     A.sfull = 0.0; A.spart = 0.0; A.wpart = 0.0; A.nfull = 0; A.npart = 0; A.flags = 0;
     const double bigrad = ap + 0.5, smallrad = ap / sqrt(2.) - 0.5;  // aper.py:179-181
     // candidate box: every pixel the reference can give a positive weight lies inside it in either compat mode
     // (py3: yy = row + col/nx shifts a pixel's y by < 1 row, aper.py:246-248)
-    int c0 = (int)floor(g.dx - bigrad) - 1, c1 = (int)ceil(g.dx + bigrad) + 1;
-    int r0 = (int)floor(g.dy - bigrad) - 2, r1 = (int)ceil(g.dy + bigrad) + 1;
+    int c0 = (int)floor(g.dx - bigrad), c1 = (int)ceil(g.dx + bigrad);
+    int r0 = (int)floor(g.dy - bigrad) - (P.exact && !P.compat_py2 ? 1 : 0), r1 = (int)ceil(g.dy + bigrad);
     if (c0 < 0) c0 = 0;
     if (c1 > g.nx - 1) c1 = g.nx - 1;
     if (r0 < 0) r0 = 0;
@@ -300,7 +365,8 @@ BP_D ApPartial aperture_warp(const AperParams& P, const T* __restrict__ stamp, c
     const int bw = c1 - c0 + 1, bh = r1 - r0 + 1;
     const int npx = (bw > 0 && bh > 0) ? bw * bh : 0;
     const unsigned lt = (1u << lane) - 1u;
-    for (int base = w * 32; base < npx; base += 32 * AP_WORKERS) {
+    int cnt = 0;
+    for (int base = w * 32; base < npx; base += 32 * nw) {
         const int p = base + lane;
         int r = 0, c = 0, cls = 0;
         double xxp = 0., yyp = 0., wgt = 0.;
@@ -328,38 +394,18 @@ BP_D ApPartial aperture_warp(const AperParams& P, const T* __restrict__ stamp, c
             }
         }
         const unsigned bmask = __ballot_sync(FULL, cls == 2);
-        if (bmask) {  // pixels the circle crosses: pixwt, one lane per pixel side
-            const int rank = __popc(bmask & lt), nb = __popc(bmask);
-            if (cls == 2) { sx[rank] = xxp; sy[rank] = yyp; }
-            __syncwarp();
-            for (int g0 = 0; g0 < nb; g0 += 8) {
-                const int j = g0 + (lane >> 2), side = lane & 3;
-                double s = 0.0;
-                if (j < nb) s = pixwt_side(g.dx, g.dy, ap, sx[j], sy[j], side);
-                const double s1 = __shfl_down_sync(FULL, s, 1), s2 = __shfl_down_sync(FULL, s, 2), s3 = __shfl_down_sync(FULL, s, 3);
-                if (side == 0 && j < nb) sw[j] = ((s + s1) + s2) + s3;  // Intarea's order of addition, pixwt.py:234-235
-            }
-            __syncwarp();
-            if (cls == 2) {
-                wgt = sw[rank];
-                if (wgt < 0.0) wgt = 0.0;  // aper.py:329
-            }
-            __syncwarp();
+        if (cls == 2) {
+            const int q = cnt + __popc(bmask & lt);
+            L->x[q] = xxp; L->y[q] = yyp; L->rc[q] = r * 65536 + c;
         }
-        if (cls == 3 || (cls != 0 && wgt > 0.0)) {
-            double v = (double)stamp[(size_t)r * P.pitch + c];
-            if (!isfinite(v)) { A.flags |= 1; v = 0.0; }  // aper.py:359-366
-            if (P.badlo < P.badhi && (v <= P.badlo || v >= P.badhi)) { A.flags |= 2; v = 0.0; }  // aper.py:367-378
-            if (P.exact || full) {
-                A.sfull = A.sfull + v * wgt;
-                A.nfull += 1;
-            } else {
-                A.spart = A.spart + v * wgt;
-                A.wpart = A.wpart + wgt;
-                A.npart += 1;
-            }
+        cnt += __popc(bmask);
+        if (cls == 1 || cls == 3) add_pixel<T>(P, stamp, r, c, wgt, full, A);
+        if (cnt > AP_LIST - 32) {
+            flush_cross_list<T>(P, stamp, g, ap, L, cnt, lane, A);
+            cnt = 0;
         }
     }
+    if (cnt > 0) flush_cross_list<T>(P, stamp, g, ap, L, cnt, lane, A);
     A.sfull = warp_sum(A.sfull);
     A.spart = warp_sum(A.spart);
     A.wpart = warp_sum(A.wpart);
@@ -369,35 +415,45 @@ BP_D ApPartial aperture_warp(const AperParams& P, const T* __restrict__ stamp, c
     return A;
 }
 
+// ------------------------------------------------------------ the two stages
+// The per-star work splits into a wide part (gather, sort, aperture sums: thousands of independent
+// pixels) and a narrow one (mmm: ~20 dependent clipping iterations on the sorted vector, enough work for
+// one warp only).  Run in one CTA, three of four warps idle behind the mmm warp for most of the star's
+// lifetime, and registers/shared memory of the sort cap the SM at 5 stars in flight.  So the stages are
+// separate launches over batches of stars: stage 1 (CTA per star) leaves each star's sorted annulus in a
+// global scratch row (11 KB, mostly L2-resident) and its raw aperture sums in the output arrays; stage 2
+// (WARP per star, ~40 stars in flight per SM) runs mmm on that row and finishes flux/error/magnitude.
+//
+// Stage-1 -> stage-2 hand-over, in place in the outputs: flux[s,k] = sum of weight*pixel (aper.py:380),
+// badflag[s,k] = raw flag bits, nsky[s] = annulus pixel count, mmm_iter[s] = number of sorted keys, or
+// -1 (star off the frame, aper.py:209-233) / -2 (nsky < minsky, aper.py:269-272).
+
 // K > 0: register sort of 128*K keys (P.sort_cap == 128*K).  K == 0: shared-memory sort of P.sort_cap keys.
 template <typename T, int K>
-__global__ void __launch_bounds__(AP_THREADS) aper_kernel(const AperParams P) {
+__global__ void __launch_bounds__(AP_THREADS) aper_stage1_kernel(const AperParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* keys = reinterpret_cast<T*>(smem_raw);
+    const size_t key_bytes = ((size_t)(K > 0 ? AP_THREADS * (K + 1) : P.sort_cap) * sizeof(T) + 15) & ~(size_t)15;
+    int* span = reinterpret_cast<int*>(smem_raw + key_bytes);
     __shared__ int s_nvalid;
     __shared__ int s_nsel[AP_WARPS];
-    __shared__ ApPartial s_part[BPHOT_MAX_APER][AP_WORKERS];
-    __shared__ MmmResult s_mmm;
-    __shared__ double s_scr[AP_WORKERS][3][32];
+    __shared__ ApPartial s_part[BPHOT_MAX_APER][AP_WARPS];
+    __shared__ CrossList s_list[AP_WARPS];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const T* __restrict__ img = reinterpret_cast<const T*>(P.img);
+    T* __restrict__ skeys = reinterpret_cast<T*>(P.skeys);
     const int naper = P.naper;
     const double rinsq = P.skyrad_in * P.skyrad_in, routsq = P.skyrad_out * P.skyrad_out;
 
-    for (int s = blockIdx.x; s < P.nstars; s += gridDim.x) {
+    for (int s = P.s0 + blockIdx.x; s < P.s0 + P.scount; s += gridDim.x) {
         const double x = P.xc[s], y = P.yc[s];
         // aper.py:209-210 (a NaN position crashes the reference; it is flagged bad here)
         const bool badstar = !(x >= 0.5) || !(x <= P.ncol - 1.5) || !(y >= 0.5) || !(y <= P.nrow - 1.5);
-        auto write_bad = [&](double skyv, double skyerrv, int nskyv, int iters) {
-            for (int k = tid; k < naper; k += AP_THREADS) {
-                const size_t o = (size_t)s * naper + k;
-                P.mag[o] = nan64(); P.magerr[o] = nan64(); P.flux[o] = nan64(); P.fluxerr[o] = nan64();
-                P.badflag[o] = 1;
-            }
-            if (tid == 0) { P.sky[s] = skyv; P.skyerr[s] = skyerrv; P.nsky[s] = nskyv; P.mmm_iter[s] = iters; }
-        };
-        if (badstar) { write_bad(0.0, 0.0, 0, 0); continue; }
+        if (badstar) {
+            if (tid == 0) { P.nsky[s] = 0; P.mmm_iter[s] = -1; }
+            continue;
+        }
         const StarGeom g = star_geom(P, x, y);
         const T* __restrict__ stamp = img + g.origin;
 
@@ -405,19 +461,22 @@ __global__ void __launch_bounds__(AP_THREADS) aper_kernel(const AperParams P) {
         if (!P.use_setsky) {
             // ---- P1: gather the annulus
             if (tid == 0) s_nvalid = 0;
+            row_spans(g, rinsq, routsq, span, tid);
             __syncthreads();
-            const int nsel = gather_rows<T>(P, stamp, g, rinsq, routsq, keys, &s_nvalid, warp, lane);
+            const int nsel = gather_rows<T>(P, stamp, g, rinsq, routsq, span, keys, &s_nvalid, warp, lane);
             if (lane == 0) s_nsel[warp] = nsel;
             __syncthreads();
 #pragma unroll
             for (int w = 0; w < AP_WARPS; w++) nsky_all += s_nsel[w];
             nvalid = s_nvalid < P.sort_cap ? s_nvalid : P.sort_cap;
+            if (nvalid > (int)P.sstride) nvalid = (int)P.sstride;
             if (nsky_all < P.minsky) {  // aper.py:269-272
-                write_bad(0.0, 0.0, nsky_all, 0);
+                if (tid == 0) { P.nsky[s] = nsky_all; P.mmm_iter[s] = -2; }
                 __syncthreads();  // the counters are reset by the next star
                 continue;
             }
-            // ---- P2: sort (mmm.py:119); the tail is padded with +inf
+            // ---- P2: sort (mmm.py:119); the tail is padded with +inf; sorted keys go to the scratch row
+            T* __restrict__ dst = skeys + (size_t)(s - P.s0) * P.sstride;
             if constexpr (K > 0) {
                 T r[K];
 #pragma unroll
@@ -427,51 +486,91 @@ __global__ void __launch_bounds__(AP_THREADS) aper_kernel(const AperParams P) {
                 }
                 __syncthreads();
                 cta_sort_regs<T, K>(r, keys, tid);
+                constexpr int VEC = 16 / sizeof(T);  // sstride is a multiple of VEC, rows are 16-byte aligned
 #pragma unroll
-                for (int q = 0; q < K; q++) keys[tid * (K + 1) + q] = r[q];
+                for (int q = 0; q < K; q += VEC) {
+                    const int e = tid * K + q;
+                    if (e < nvalid) {
+                        if constexpr (sizeof(T) == 4) *reinterpret_cast<float4*>(dst + e) = make_float4(r[q], r[q + 1], r[q + 2], r[q + 3]);
+                        else *reinterpret_cast<double2*>(dst + e) = make_double2(r[q], r[q + 1]);
+                    }
+                }
             } else {
                 int m = 2;
                 while (m < nvalid) m <<= 1;
                 for (int i = nvalid + tid; i < m; i += AP_THREADS) keys[i] = KeyTraits<T>::inf();
                 __syncthreads();
                 cta_bitonic_sort(keys, m, tid);
+                for (int i = tid; i < nvalid; i += AP_THREADS) dst[i] = keys[i];
             }
-            __syncthreads();
         }
 
-        // ---- P3: warp 0 -> mmm ; warps 1.. -> aperture sums
-        if (warp == 0) {
-            if (!P.use_setsky) {
-                SortedView<T> view;
-                view.p = keys;
-                view.shift = 31;
-                if constexpr (K > 0) view.shift = __ffs(K) - 1;
-                MmmResult R = mmm_warp<T>(view, nvalid, P.readnoise, P.minsky, P.mxiter, lane);
-                if (lane == 0) s_mmm = R;
-            }
-        } else {
-            const int w = warp - 1;
-            for (int k = 0; k < naper; k++) {
-                const double ap = P.apr[k];
-                ApPartial A;
-                A.sfull = 0.0; A.spart = 0.0; A.wpart = 0.0; A.nfull = 0; A.npart = 0; A.flags = 0;
-                if (g.edge >= ap) A = aperture_warp<T>(P, stamp, g, ap, w, lane, s_scr[w][0], s_scr[w][1], s_scr[w][2]);
-                if (lane == 0) s_part[k][w] = A;
+        // ---- P3: aperture sums, the four warps share each aperture's pixel box
+        for (int k = 0; k < naper; k++) {
+            const double ap = P.apr[k];
+            if (g.edge >= ap) {  // aper.py:311
+                const ApPartial A = aperture_warp<T>(P, stamp, g, ap, warp, AP_WARPS, lane, &s_list[warp]);
+                if (lane == 0) s_part[k][warp] = A;
             }
         }
         __syncthreads();
+        if (tid < naper) {
+            const int k = tid;
+            const size_t o = (size_t)s * naper + k;
+            const double ap = P.apr[k];
+            double total = 0.0;
+            int flags = 0;
+            if (g.edge >= ap) {
+                const double area = M_PI * ap * ap;
+                double sfull = 0.0, spart = 0.0, wpart = 0.0;
+                int nfull = 0, npart = 0;
+                for (int w = 0; w < AP_WARPS; w++) {
+                    const ApPartial& A = s_part[k][w];
+                    sfull = sfull + A.sfull; spart = spart + A.spart; wpart = wpart + A.wpart;
+                    nfull += A.nfull; npart += A.npart; flags |= A.flags;
+                }
+                total = sfull;
+                if (!P.exact && npart > 0) total = sfull + ((area - nfull) / wpart) * spart;  // aper.py:343-349
+                if (flags & 1) total = 0.0;  // fractn = 0 for the whole aperture, aper.py:366
+            }
+            P.flux[o] = total;
+            P.badflag[o] = (uint8_t)flags;
+        }
+        if (tid == 0) { P.nsky[s] = nsky_all; P.mmm_iter[s] = nvalid; }
+        __syncthreads();  // keys / s_part / counters are reused by the next star
+    }
+}
 
-        // ---- P4: combine (aper.py:290-300, 383-403)
+// Stage 2: one warp per star -- mmm on the sorted scratch row, then aper.py:290-300, 383-403.
+template <typename T>
+__global__ void __launch_bounds__(AP_THREADS) aper_stage2_kernel(const AperParams P) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int naper = P.naper;
+    const T* __restrict__ skeys = reinterpret_cast<const T*>(P.skeys);
+    for (int s = P.s0 + blockIdx.x * AP_WARPS + warp; s < P.s0 + P.scount; s += gridDim.x * AP_WARPS) {
+        const int status = P.mmm_iter[s], nsky_all = P.nsky[s];
+        auto write_bad = [&](double skyv, double skyerrv, int nskyv, int iters) {
+            if (lane < naper) {
+                const size_t o = (size_t)s * naper + lane;
+                P.mag[o] = nan64(); P.magerr[o] = nan64(); P.flux[o] = nan64(); P.fluxerr[o] = nan64();
+                P.badflag[o] = 1;
+            }
+            if (lane == 0) { P.sky[s] = skyv; P.skyerr[s] = skyerrv; P.nsky[s] = nskyv; P.mmm_iter[s] = iters; }
+        };
+        if (status == -1) { write_bad(0.0, 0.0, 0, 0); continue; }          // aper.py:221-233
+        if (status == -2) { write_bad(0.0, 0.0, nsky_all, 0); continue; }  // aper.py:269-272
         double skymod, skysig, skyvar, sigsq;
         int iters = 0, nsky_out;
         if (!P.use_setsky) {
-            skymod = s_mmm.skymod; skysig = s_mmm.sigma; iters = s_mmm.iters;
-            skyvar = skysig * skysig;
+            GlobalView<T> view;
+            view.p = skeys + (size_t)(s - P.s0) * P.sstride;
+            const MmmResult R = mmm_warp(view, status, P.readnoise, P.minsky, P.mxiter, lane);  // aper.py:288
+            skymod = R.skymod; skysig = R.sigma; iters = R.iters;
+            skyvar = skysig * skysig;  // aper.py:290-291
             sigsq = skyvar / nsky_all;
             nsky_out = nsky_all;
             if (skysig < 0.0) {  // aper.py:293-296, 411-412
                 write_bad(skymod, skysig, nsky_all, iters);
-                __syncthreads();
                 continue;
             }
             if (skysig > 999.99) skysig = 999;  // aper.py:298
@@ -481,26 +580,16 @@ __global__ void __launch_bounds__(AP_THREADS) aper_kernel(const AperParams P) {
             sigsq = skyvar / P.setsky[2];
             nsky_out = (int)P.setsky[2];
         }
-        if (tid < naper) {
-            const int k = tid;
-            const size_t o = (size_t)s * naper + k;
-            const double ap = P.apr[k];
+        if (lane < naper) {
+            const StarGeom g = star_geom(P, P.xc[s], P.yc[s]);
+            const size_t o = (size_t)s * naper + lane;
+            const double ap = P.apr[lane];
             if (!(g.edge >= ap)) {  // aper.py:311, 350-353
                 P.mag[o] = nan64(); P.magerr[o] = nan64(); P.flux[o] = nan64(); P.fluxerr[o] = nan64();
                 P.badflag[o] = 1;
             } else {
                 const double area = M_PI * ap * ap;
-                double sfull = 0.0, spart = 0.0, wpart = 0.0;
-                int nfull = 0, npart = 0, flags = 0;
-                for (int w = 0; w < AP_WORKERS; w++) {
-                    const ApPartial& A = s_part[k][w];
-                    sfull = sfull + A.sfull; spart = spart + A.spart; wpart = wpart + A.wpart;
-                    nfull += A.nfull; npart += A.npart; flags |= A.flags;
-                }
-                double total = sfull;
-                if (!P.exact && npart > 0) total = sfull + ((area - nfull) / wpart) * spart;  // aper.py:343-349
-                if (flags & 1) total = 0.0;  // fractn = 0 for the whole aperture, aper.py:366
-                const double apflux = total - skymod * area;  // aper.py:391
+                const double apflux = P.flux[o] - skymod * area;  // aper.py:391
                 const double err = sqrt(area * skyvar + fabs(apflux) / P.phpadu + sigsq * (area * area));  // aper.py:394-397
                 P.flux[o] = apflux;
                 P.fluxerr[o] = err;
@@ -511,11 +600,10 @@ __global__ void __launch_bounds__(AP_THREADS) aper_kernel(const AperParams P) {
                     P.magerr[o] = nan64();
                     P.mag[o] = nan64();
                 }
-                P.badflag[o] = flags ? 1 : 0;
+                P.badflag[o] = P.badflag[o] ? 1 : 0;
             }
         }
-        if (tid == 0) { P.sky[s] = skymod; P.skyerr[s] = skysig; P.nsky[s] = nsky_out; P.mmm_iter[s] = iters; }
-        __syncthreads();  // keys / s_part / s_mmm are reused by the next star
+        if (lane == 0) { P.sky[s] = skymod; P.skyerr[s] = skysig; P.nsky[s] = nsky_out; P.mmm_iter[s] = iters; }
     }
 }
 
@@ -573,7 +661,7 @@ __global__ void __launch_bounds__(AP_THREADS) mmm_kernel(const T* vec, const lon
         }
         __syncthreads();
         if (warp == 0) {
-            MmmResult R = mmm_warp<T>(view, n, readnoise, minsky, mxiter, lane);
+            MmmResult R = mmm_warp(view, n, readnoise, minsky, mxiter, lane);
             if (lane == 0) {
                 out3[3 * (size_t)v + 0] = R.skymod; out3[3 * (size_t)v + 1] = R.sigma; out3[3 * (size_t)v + 2] = R.skew;
                 iters[v] = R.iters;

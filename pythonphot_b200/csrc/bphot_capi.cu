@@ -37,6 +37,8 @@ int next_pow2(long long v) {
     return m;
 }
 
+constexpr int APER_BATCH = 65536;  // stars per stage-1 / stage-2 launch pair (scratch = batch * ~13 KB)
+
 struct DevInfo {
     int sms;
     int smem_optin;
@@ -133,38 +135,62 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     P.minsky = minsky; P.exact = exact ? 1 : 0; P.compat_py2 = compat_py2 ? 1 : 0; P.mxiter = 50;
     P.readnoise = readnoise;
     // register-sort variants hold 128*K keys; larger annuli fall back to the shared-memory sort (K = 0)
-    const int need = use_setsky ? 2 : next_pow2(annulus_bound(skyrad_in, skyrad_out));
+    const long long bound = use_setsky ? 4 : annulus_bound(skyrad_in, skyrad_out);
+    const int need = next_pow2(bound);
     const int K = need <= 1024 ? 8 : need <= 2048 ? 16 : need <= 4096 ? 32 : 0;
     P.sort_cap = K ? AP_THREADS * K : need;
     P.mag = d_mag; P.magerr = d_magerr; P.flux = d_flux; P.fluxerr = d_fluxerr;
     P.sky = d_sky; P.skyerr = d_skyerr; P.badflag = d_badflag; P.nsky = d_nsky; P.mmm_iter = d_mmm_iter;
-    const size_t smem = (size_t)(K ? AP_THREADS * (K + 1) : need) * esize(image_dtype);
+    P.span_rows = (int)(2. * skyrad_out) + 4;
+    const size_t es = esize(image_dtype);
+    const size_t key_bytes = ((size_t)(K ? AP_THREADS * (K + 1) : need) * es + 15) & ~(size_t)15;
+    const size_t smem = key_bytes + (size_t)P.span_rows * 16;
     DevInfo d;
     int rc = dev_info(&d);
     if (rc) return rc;
-    if (smem + 8192 > (size_t)d.smem_optin)
+    if (smem + 16384 > (size_t)d.smem_optin)
         return fail(BPHOT_ERR_CAPACITY, "bphot_aper: sky annulus [%g,%g] needs %zu B of shared memory per star (limit %d)",
                     skyrad_in, skyrad_out, smem, d.smem_optin);
-    int grid = 0;
+    // scratch rows of sorted annulus keys (stage 1 -> stage 2), one batch of stars at a time
+    P.sstride = (bound + 7) / 8 * 8;
+    const int batch = nstars < APER_BATCH ? nstars : APER_BATCH;
     cudaStream_t st = (cudaStream_t)stream;
-#define BP_LAUNCH_APER(T, KK)                                                               \
-    do {                                                                                    \
-        rc = persistent_grid(aper_kernel<T, KK>, AP_THREADS, smem, nstars, &grid);          \
-        if (rc) return rc;                                                                  \
-        aper_kernel<T, KK><<<grid, AP_THREADS, smem, st>>>(P);                              \
+    void* scratch = nullptr;
+    if (!use_setsky) CU_TRY(cudaMallocAsync(&scratch, (size_t)batch * P.sstride * es, st));
+    P.skeys = scratch;
+    int grid1 = 0, grid2 = 0;
+#define BP_STAGE1(T, KK)                                                                          \
+    do {                                                                                          \
+        rc = persistent_grid(aper_stage1_kernel<T, KK>, AP_THREADS, smem, P.scount, &grid1);      \
+        if (!rc) aper_stage1_kernel<T, KK><<<grid1, AP_THREADS, smem, st>>>(P);                   \
     } while (0)
-#define BP_LAUNCH_APER_K(T)                      \
-    do {                                         \
-        if (K == 8) BP_LAUNCH_APER(T, 8);        \
-        else if (K == 16) BP_LAUNCH_APER(T, 16); \
-        else if (K == 32) BP_LAUNCH_APER(T, 32); \
-        else BP_LAUNCH_APER(T, 0);               \
+#define BP_STAGE1_K(T)                       \
+    do {                                     \
+        if (K == 8) BP_STAGE1(T, 8);         \
+        else if (K == 16) BP_STAGE1(T, 16);  \
+        else if (K == 32) BP_STAGE1(T, 32);  \
+        else BP_STAGE1(T, 0);                \
     } while (0)
-    if (image_dtype == BPHOT_F32) BP_LAUNCH_APER_K(float);
-    else BP_LAUNCH_APER_K(double);
-#undef BP_LAUNCH_APER_K
-#undef BP_LAUNCH_APER
-    g_launches++;
+#define BP_STAGE2(T)                                                                                              \
+    do {                                                                                                          \
+        rc = persistent_grid(aper_stage2_kernel<T>, AP_THREADS, 0, (P.scount + AP_WARPS - 1) / AP_WARPS, &grid2); \
+        if (!rc) aper_stage2_kernel<T><<<grid2, AP_THREADS, 0, st>>>(P);                                          \
+    } while (0)
+    for (int s0 = 0; s0 < nstars && !rc; s0 += batch) {
+        P.s0 = s0;
+        P.scount = (nstars - s0) < batch ? (nstars - s0) : batch;
+        if (image_dtype == BPHOT_F32) BP_STAGE1_K(float);
+        else BP_STAGE1_K(double);
+        if (rc) break;
+        if (image_dtype == BPHOT_F32) BP_STAGE2(float);
+        else BP_STAGE2(double);
+        g_launches += 2;
+    }
+#undef BP_STAGE2
+#undef BP_STAGE1_K
+#undef BP_STAGE1
+    if (scratch) cudaFreeAsync(scratch, st);
+    if (rc) return rc;
     CU_TRY(cudaGetLastError());
     return BPHOT_OK;
 }

@@ -26,6 +26,11 @@ struct AperParams {
     int minsky, exact, compat_py2, mxiter;
     double readnoise;
     int sort_cap;  // power of two >= the largest possible annulus pixel count
+    // stage-1 -> stage-2 hand-over: sorted annulus keys of stars [s0, s0 + scount), `sstride` keys per star
+    void* skeys;
+    long long sstride;
+    int s0, scount;
+    int span_rows;  // rows of the per-CTA column-span table (>= stamp height)
     // outputs
     double* mag;      // [nstars, naper]
     double* magerr;   // [nstars, naper]
