@@ -430,7 +430,7 @@ BP_D ApPartial aperture_warp(const AperParams& P, const T* __restrict__ stamp, c
 
 // K > 0: register sort of 128*K keys (P.sort_cap == 128*K).  K == 0: shared-memory sort of P.sort_cap keys.
 template <typename T, int K>
-__global__ void __launch_bounds__(AP_THREADS) aper_stage1_kernel(const AperParams P) {
+__global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? 6 : 1) aper_stage1_kernel(const AperParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* keys = reinterpret_cast<T*>(smem_raw);
     const size_t key_bytes = ((size_t)(K > 0 ? AP_THREADS * (K + 1) : P.sort_cap) * sizeof(T) + 15) & ~(size_t)15;
@@ -446,7 +446,8 @@ __global__ void __launch_bounds__(AP_THREADS) aper_stage1_kernel(const AperParam
     const int naper = P.naper;
     const double rinsq = P.skyrad_in * P.skyrad_in, routsq = P.skyrad_out * P.skyrad_out;
 
-    for (int s = P.s0 + blockIdx.x; s < P.s0 + P.scount; s += gridDim.x) {
+    for (int i = P.s0 + blockIdx.x; i < P.s0 + P.scount; i += gridDim.x) {
+        const int s = P.order ? P.order[i] : i;  // stars are visited in image-tile order, results land at s
         const double x = P.xc[s], y = P.yc[s];
         // aper.py:209-210 (a NaN position crashes the reference; it is flagged bad here)
         const bool badstar = !(x >= 0.5) || !(x <= P.ncol - 1.5) || !(y >= 0.5) || !(y <= P.nrow - 1.5);
@@ -476,7 +477,7 @@ __global__ void __launch_bounds__(AP_THREADS) aper_stage1_kernel(const AperParam
                 continue;
             }
             // ---- P2: sort (mmm.py:119); the tail is padded with +inf; sorted keys go to the scratch row
-            T* __restrict__ dst = skeys + (size_t)(s - P.s0) * P.sstride;
+            T* __restrict__ dst = skeys + (size_t)(i - P.s0) * P.sstride;
             if constexpr (K > 0) {
                 T r[K];
 #pragma unroll
@@ -547,7 +548,8 @@ __global__ void __launch_bounds__(AP_THREADS) aper_stage2_kernel(const AperParam
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int naper = P.naper;
     const T* __restrict__ skeys = reinterpret_cast<const T*>(P.skeys);
-    for (int s = P.s0 + blockIdx.x * AP_WARPS + warp; s < P.s0 + P.scount; s += gridDim.x * AP_WARPS) {
+    for (int i = P.s0 + blockIdx.x * AP_WARPS + warp; i < P.s0 + P.scount; i += gridDim.x * AP_WARPS) {
+        const int s = P.order ? P.order[i] : i;
         const int status = P.mmm_iter[s], nsky_all = P.nsky[s];
         auto write_bad = [&](double skyv, double skyerrv, int nskyv, int iters) {
             if (lane < naper) {
@@ -563,7 +565,7 @@ __global__ void __launch_bounds__(AP_THREADS) aper_stage2_kernel(const AperParam
         int iters = 0, nsky_out;
         if (!P.use_setsky) {
             GlobalView<T> view;
-            view.p = skeys + (size_t)(s - P.s0) * P.sstride;
+            view.p = skeys + (size_t)(i - P.s0) * P.sstride;
             const MmmResult R = mmm_warp(view, status, P.readnoise, P.minsky, P.mxiter, lane);  // aper.py:288
             skymod = R.skymod; skysig = R.sigma; iters = R.iters;
             skyvar = skysig * skysig;  // aper.py:290-291

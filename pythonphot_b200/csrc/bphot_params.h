@@ -31,6 +31,7 @@ struct AperParams {
     long long sstride;
     int s0, scount;
     int span_rows;  // rows of the per-CTA column-span table (>= stamp height)
+    const int* order;  // visiting order of the stars (image-tile sorted), or null
     // outputs
     double* mag;      // [nstars, naper]
     double* magerr;   // [nstars, naper]
@@ -60,6 +61,7 @@ struct PkfitParams {
     const double* y;
     const double* sky;
     int nstars;
+    const int* order;  // visiting order of the stars (image-tile sorted), or null
     int cap;   // per-star pixel-list capacity
     int acap;  // columns / rows of the fitting box (capacity of the per-axis Gaussian factors)
     double* errmag;

@@ -550,7 +550,8 @@ __global__ void __launch_bounds__(PK_THREADS) pkfit_kernel(const PkfitParams P) 
     for (int i = threadIdx.x; i < ntab; i += PK_THREADS) psf[i] = P.psf[i];
     __syncthreads();
     const int wstride = gridDim.x * PK_WARPS;
-    for (int s = blockIdx.x * PK_WARPS + warp; s < P.nstars; s += wstride) {
+    for (int i = blockIdx.x * PK_WARPS + warp; i < P.nstars; i += wstride) {
+        const int s = P.order ? P.order[i] : i;  // stars are visited in image-tile order, results land at s
         FitOut o;
         if constexpr (V == 2) o = pkfit_forced_warp<TI, TN>(P, psf, W, AX, P.scale[s], P.x[s], P.y[s], P.sky[s], lane);
         else o = pkfit_recenter_warp<V, TI, TN>(P, psf, W, GIDX, AX, P.scale[s], P.x[s], P.y[s], P.sky[s], lane);
