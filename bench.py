@@ -225,20 +225,30 @@ def main():
         dist.broadcast_object_list(meta, src=0)
         if rank != 0:
             field = meta[0]
-    # star shard of this rank: same exposure, positions re-jittered per rank (distinct, equally costly shards)
-    rng = np.random.default_rng(1000 + rank)
-    jit = (lambda v: v + rng.normal(0.0, 0.02, v.size)) if rank > 0 else (lambda v: v)
-    xs, ys, xf, yf = jit(field["x"]), jit(field["y"]), jit(field["xfit"]), jit(field["yfit"])
-    pin = lambda v: torch.from_numpy(np.ascontiguousarray(v, dtype=np.float64)).pin_memory()
-    h_x, h_y, h_xf, h_yf = pin(xs), pin(ys), pin(xf), pin(yf)
-    h_one, h_sky = pin(np.ones(n)), pin(np.full(n, field["sky"]))
-    d_x, d_y, d_xf, d_yf = (t.to(dev) for t in (h_x, h_y, h_xf, h_yf))
+    # star list: `world` jittered copies of the field's list (n stars per GPU: weak scaling), known on rank 0, broadcast, then
+    # sharded by image tile (pythonphot_b200/shard.py): each rank fits one contiguous Morton-ordered shard
+    from pythonphot_b200 import shard
+    if rank == 0:
+        parts = {k: [] for k in ("x", "y", "xfit", "yfit")}
+        for r in range(world):
+            rng = np.random.default_rng(1000 + r)
+            for k in parts:
+                parts[k].append(field[k] + (rng.normal(0.0, 0.02, n) if r > 0 else 0.0))
+        full = [np.concatenate(parts[k]) for k in ("x", "y", "xfit", "yfit")]
+    else:
+        full = [None] * 4
+    cols = shard.broadcast_columns(full, world * n, dev, src=0) if world > 1 else torch.from_numpy(np.stack(full)).to(dev)
+    plan = shard.ShardPlan.for_stars(cols[0].cpu().numpy(), cols[1].cpu().numpy(), a.size, a.size, world)
+    assert plan.m == n
+    d_x, d_y, d_xf, d_yf = (plan.take(cols[i], rank) for i in range(4))
+    pin = lambda t: t.cpu().pin_memory()
+    h_x, h_y, h_xf, h_yf = pin(d_x), pin(d_y), pin(d_xf), pin(d_yf)
+    h_one, h_sky = torch.ones(n, dtype=torch.float64).pin_memory(), torch.full((n,), float(field["sky"]), dtype=torch.float64).pin_memory()
     d_one, d_sky = h_one.to(dev), h_sky.to(dev)
     pk = pp.pkfit_class(img_t, field["gauss"], field["psf"], field["ronois"], field["phpadu"], noise_t, mask_t)
     do_aper, do_fit = a.workload in ("both", "aper"), a.workload in ("both", "pkfit")
 
     bufs = {"aper": None, "fit": None}
-    gather = None
 
     def step(ev=None):
         if do_aper:
@@ -254,21 +264,16 @@ def main():
             bufs["fit"] = pk.fit_device(_lib.PKFIT_NORECENT, d_one, d_xf, d_yf, d_sky, FIT_RADIUS, out=bufs["fit"])
             if ev:
                 ev[3].record()
-        if world > 1:  # per-star result records are all-gathered (north_star); fp64 record per star
-            cols = []
+        if world > 1:  # the per-star result records are packed and all-gathered, then put back in caller order (north_star)
+            rec = {}
             if do_aper:
-                cols += [bufs["aper"]["flux"], bufs["aper"]["fluxerr"], bufs["aper"]["sky"].unsqueeze(1)]
+                rec.update({"a_" + k: v for k, v in bufs["aper"].items()})
             if do_fit:
-                cols += [bufs["fit"]["scale"].unsqueeze(1), bufs["fit"]["errmag"].unsqueeze(1)]
-            rec = torch.cat(cols, dim=1)
-            out = gather_buf(rec)
-            dist.all_gather_into_tensor(out, rec)
+                rec.update({"f_" + k: bufs["fit"][k] for k in ("errmag", "chi", "sharp", "scale", "niter")})
+            packed, _layout = shard.pack_records(rec)
+            gathered["rec"] = plan.gather(packed)
 
-    def gather_buf(rec):
-        nonlocal gather
-        if gather is None:
-            gather = torch.empty((world * rec.shape[0], rec.shape[1]), dtype=rec.dtype, device=dev)
-        return gather
+    gathered = {}
 
     for _ in range(max(a.warmup, 3)):
         step()

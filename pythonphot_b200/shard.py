@@ -1,0 +1,232 @@
+"""Star-sharded photometry over several GPUs of one node.
+
+Stars are independent units (aper.py:217 and README.md:73-75 loop over them one at a time), so the
+path shards by star list and needs exactly two collectives, both outside the kernels:
+
+  * the exposure (image, noise image, mask) is broadcast ONCE from the source rank over
+    NVLink/NVSwitch (``broadcast_exposure``) and stays replicated in every GPU's HBM;
+  * each rank runs the ordinary single-GPU kernels on its contiguous shard of the tile-ordered star
+    list and the fixed-width per-star result records are all-gathered (``ShardPlan.gather``).
+
+There is no collective inside a kernel, hence nothing to fuse.  The plumbing below is
+``torch.distributed`` only (NCCL on the GPU box; the same code runs under ``gloo`` with CPU tensors,
+which is how tests/test_shard_gloo.py covers it at world_size 2).  The N-GPU result equals the
+1-GPU result bit for bit after un-permuting, because every star's arithmetic is independent of
+which rank, CTA or batch it lands in.
+"""
+import numpy as np
+
+TILE_SHIFT = 6  # 64-pixel tiles, as SURVEY.md 8e
+
+
+def _dist():
+    import torch.distributed as dist
+    return dist
+
+
+def world_info(group=None):
+    """(rank, world) of the default/explicit process group, (0, 1) when torch.distributed is not up."""
+    dist = _dist()
+    if not (dist.is_available() and dist.is_initialized()):
+        return 0, 1
+    return dist.get_rank(group), dist.get_world_size(group)
+
+
+def _spread_bits(v):
+    """Interleave helper: 16-bit integers -> their bits at even positions of a 32-bit word."""
+    v = v.astype(np.uint32) & np.uint32(0xFFFF)
+    v = (v | (v << np.uint32(8))) & np.uint32(0x00FF00FF)
+    v = (v | (v << np.uint32(4))) & np.uint32(0x0F0F0F0F)
+    v = (v | (v << np.uint32(2))) & np.uint32(0x33333333)
+    v = (v | (v << np.uint32(1))) & np.uint32(0x55555555)
+    return v
+
+
+def morton_order(x, y, nrow, ncol, shift=TILE_SHIFT):
+    """Stable permutation that sorts stars by the Morton code of their 64x64-pixel image tile, so that a
+    contiguous shard covers a compact patch of the frame (stamp reads of one rank share L2 lines).
+    NaN / off-frame positions are clamped into the frame first (they still get a slot: the kernels report
+    them in band, aper.py:221-233)."""
+    xv = np.nan_to_num(np.asarray(x, dtype=np.float64), nan=0.0, posinf=float(ncol - 1), neginf=0.0)
+    yv = np.nan_to_num(np.asarray(y, dtype=np.float64), nan=0.0, posinf=float(nrow - 1), neginf=0.0)
+    tx = np.clip(xv, 0, max(ncol - 1, 0)).astype(np.int64) >> shift
+    ty = np.clip(yv, 0, max(nrow - 1, 0)).astype(np.int64) >> shift
+    code = _spread_bits(tx) | (_spread_bits(ty) << np.uint32(1))
+    return np.argsort(code, kind="stable")
+
+
+class ShardPlan(object):
+    """Which stars each rank processes, and how the gathered records go back into caller order.
+
+    ``perm`` (length n) is the visiting order; it is cut into ``world`` contiguous shards of ``m =
+    ceil(n / world)`` stars, the last shard(s) padded by repeating the final star (cheap, discarded
+    after the gather) so that every rank runs the same amount of work and the all-gather is regular."""
+
+    def __init__(self, n, world, perm=None):
+        self.n, self.world = int(n), int(world)
+        self.m = (self.n + self.world - 1) // self.world if self.n else 0
+        perm = np.arange(self.n, dtype=np.int64) if perm is None else np.asarray(perm, dtype=np.int64)
+        assert perm.shape == (self.n,)
+        pad = self.m * self.world - self.n
+        self.padded = np.concatenate([perm, np.full(pad, perm[-1] if self.n else 0, dtype=np.int64)]) if pad else perm
+        # position of star s in the gathered (rank-major) array
+        self.inverse = np.empty(self.n, dtype=np.int64)
+        self.inverse[perm] = np.arange(self.n, dtype=np.int64)
+
+    @classmethod
+    def for_stars(cls, x, y, nrow, ncol, world):
+        return cls(len(x), world, morton_order(x, y, nrow, ncol))
+
+    def indices(self, rank):
+        """Star indices (into the caller's list) of ``rank``'s shard, padding included."""
+        return self.padded[rank * self.m:(rank + 1) * self.m]
+
+    def take(self, column, rank):
+        """``rank``'s shard of a star-list column (numpy array or torch tensor, first axis = stars)."""
+        idx = self.indices(rank)
+        if isinstance(column, np.ndarray):
+            return np.ascontiguousarray(column[idx])
+        import torch
+        return column.index_select(0, torch.from_numpy(idx).to(column.device)).contiguous()
+
+    def gather(self, record, group=None):
+        """All-gather one per-star record tensor ``[m, ...]`` (same shape and dtype on every rank) and
+        return it as ``[n, ...]`` in the caller's star order, on every rank."""
+        import torch
+        dist = _dist()
+        rank, world = world_info(group)
+        assert world == self.world, "plan was made for %d ranks, group has %d" % (self.world, world)
+        assert record.shape[0] == self.m, "record has %d rows, shard has %d" % (record.shape[0], self.m)
+        record = record.contiguous()
+        if world == 1:
+            full = record
+        else:
+            full = torch.empty((world * self.m,) + tuple(record.shape[1:]), dtype=record.dtype, device=record.device)
+            dist.all_gather_into_tensor(full, record, group=group)
+        return full.index_select(0, torch.from_numpy(self.inverse).to(full.device))
+
+
+def pack_records(columns):
+    """Dict of per-star tensors ``[m]`` / ``[m, k]`` (fp64, int32, uint8 ...) -> one uint8 tensor ``[m, width]``
+    plus the layout needed to unpack: one all-gather per call instead of one per column."""
+    import torch
+    layout, parts = [], []
+    for name, t in columns.items():
+        t2 = t.reshape(t.shape[0], -1).contiguous()
+        b = t2.view(torch.uint8).reshape(t.shape[0], -1)
+        layout.append((name, t.dtype, tuple(t.shape[1:]), b.shape[1]))
+        parts.append(b)
+    return torch.cat(parts, dim=1), layout
+
+
+def unpack_records(packed, layout):
+    out, o = {}, 0
+    for name, dtype, tail, width in layout:
+        col = packed.new_empty((packed.shape[0], width))  # fresh buffer: canonical strides even for one row
+        col.copy_(packed[:, o:o + width])
+        out[name] = col.view(dtype).reshape((packed.shape[0],) + tail)
+        o += width
+    return out
+
+
+def broadcast_exposure(tensors, src=0, group=None):
+    """Broadcast the exposure tensors (image, noise, mask; already allocated with the right shape and dtype
+    on every rank) from ``src``.  One NCCL broadcast per tensor over NVLink; returns the tensors."""
+    dist = _dist()
+    _, world = world_info(group)
+    if world > 1:
+        for t in tensors:
+            if t is not None:
+                dist.broadcast(t, src=src, group=group)
+    return tensors
+
+
+def broadcast_columns(columns, n, device, src=0, group=None):
+    """Star-list columns (fp64) known on ``src`` -> a ``[ncol, n]`` fp64 tensor on every rank."""
+    import torch
+    dist = _dist()
+    rank, world = world_info(group)
+    if rank == src:
+        buf = torch.from_numpy(np.ascontiguousarray(np.stack([np.asarray(c, dtype=np.float64).reshape(-1) for c in columns]))).to(device)
+        assert buf.shape[1] == n
+    else:
+        buf = torch.empty((len(columns), n), dtype=torch.float64, device=device)
+    if world > 1:
+        dist.broadcast(buf, src=src, group=group)
+    return buf
+
+
+def run_sharded(plan, columns, compute, group=None):
+    """The generic sharded pass: ``columns`` = dict of full-length star-list columns (torch tensors on this
+    rank's device, identical on every rank); ``compute(shard_columns) -> dict of per-star result tensors``
+    runs this rank's shard (on the GPU box: the CUDA kernels); the records are packed, all-gathered once
+    and returned as a dict of full-length tensors in the caller's star order."""
+    rank, _ = world_info(group)
+    shard = {k: plan.take(v, rank) for k, v in columns.items()}
+    res = compute(shard)
+    packed, layout = pack_records(res)
+    return unpack_records(plan.gather(packed, group=group), layout)
+
+
+class ShardedPhotometry(object):
+    """One exposure replicated on every rank's GPU, star lists sharded (one process per GPU).
+
+    Every rank constructs it with the same shapes; only ``src`` needs to hold real pixel data
+    (numpy arrays or tensors), the other ranks may pass ``None`` plus ``shape``/``dtype``:
+
+        sp = ShardedPhotometry(image, gauss, psf, ronois, phpadu, noise, mask, shape=(nrow, ncol))
+        a = sp.aper(xc, yc, apr=np.array([3., 5., 8.]), skyrad=[40, 50], exact=True, ...)
+        f = sp.fit('pkfit_noise', scale, x, y, a['sky'], radius=5)
+
+    ``xc, yc ...`` must be identical on every rank (use ``broadcast_columns`` when only one rank has
+    them).  Results are dicts of CUDA tensors in the caller's star order, identical on every rank."""
+
+    def __init__(self, image, gauss, psf, ronois, phpadu, noiseim=None, maskim=None, shape=None,
+                 image_dtype=None, src=0, group=None, device=None, with_noise=None):
+        from . import _lib
+        from ._pkfit_core import PkfitEngine
+        torch = _lib.torch_cuda()
+        self.group, self.src = group, src
+        self.rank, self.world = world_info(group)
+        dev = _lib.device_of(device)
+        self.device = dev
+        if self.rank == src:
+            img_t = _lib.to_device_image(image, dev)
+            noise_t = _lib.to_device_image(noiseim, dev) if noiseim is not None else None
+            mask_t = _lib.to_device_mask(maskim, dev) if maskim is not None else None
+        else:
+            if shape is None:
+                raise ValueError("ranks other than src need shape=(nrow, ncol)")
+            dt = torch.float32 if image_dtype in (None, "float32", np.float32, torch.float32) else torch.float64
+            has_noise = with_noise if with_noise is not None else True
+            img_t = torch.empty(tuple(shape), dtype=dt, device=dev)
+            noise_t = torch.empty(tuple(shape), dtype=dt, device=dev) if has_noise else None
+            mask_t = torch.empty(tuple(shape), dtype=torch.uint8, device=dev) if has_noise else None
+        broadcast_exposure([img_t, noise_t, mask_t], src=src, group=group)
+        self.image_t = img_t
+        self.engine = PkfitEngine(img_t, gauss, psf, ronois, phpadu, noise_t, mask_t, device=dev)
+
+    def plan(self, x, y):
+        xh = x.cpu().numpy() if hasattr(x, "cpu") else np.asarray(x)
+        yh = y.cpu().numpy() if hasattr(y, "cpu") else np.asarray(y)
+        return ShardPlan.for_stars(xh, yh, self.image_t.shape[0], self.image_t.shape[1], self.world)
+
+    def aper(self, xc, yc, plan=None, **kw):
+        """Sharded ``aper.aper`` (aper.py:26-433): keywords as ``aper.aper_device``."""
+        from . import _lib
+        from .aper import aper_device
+        plan = plan or self.plan(xc, yc)
+        cols = {"x": _lib.to_device_f64(xc, self.device), "y": _lib.to_device_f64(yc, self.device)}
+        return run_sharded(plan, cols, lambda s: aper_device(self.image_t, s["x"], s["y"], **kw), group=self.group)
+
+    def fit(self, method, scale, x, y, sky, radius, maxiter=25, recenter=True, plan=None):
+        """Sharded ``pkfit`` / ``pkfit_noise`` / ``pkfit_norecent_noise`` over a star list."""
+        from . import _lib
+        variant = {"pkfit": _lib.PKFIT, "pkfit_noise": _lib.PKFIT_NOISE, "pkfit_norecent_noise": _lib.PKFIT_NORECENT}[method]
+        plan = plan or self.plan(x, y)
+        x_t = _lib.to_device_f64(x, self.device)
+        n = x_t.numel()
+        cols = {"x": x_t, "y": _lib.to_device_f64(y, self.device, n), "scale": _lib.to_device_f64(scale, self.device, n),
+                "sky": _lib.to_device_f64(sky, self.device, n)}
+        return run_sharded(plan, cols, lambda s: self.engine.fit_device(variant, s["scale"], s["x"], s["y"], s["sky"], radius,
+                                                                        maxiter=maxiter, recenter=recenter), group=self.group)
