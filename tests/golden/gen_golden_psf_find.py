@@ -1,0 +1,109 @@
+"""Golden vectors for getpsf.getpsf and find.find from the UNMODIFIED reference (authoring container only):
+
+    python tests/golden/gen_golden_psf_find.py
+
+Same rules as gen_golden.py: the reference is imported in-process through oracle/refloader.py, called with
+fp64 arrays, and its inputs are stored beside its outputs in ``golden_getpsf.npz`` / ``golden_find.npz``.
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+
+from oracle import refloader  # noqa: E402
+from pythonphot_b200 import synth  # noqa: E402
+
+GETPSF_CASES = [  # name, psfrad, fitrad, which stars (indices into the bright-star list)
+    ("r8_f3", 8, 3, None),
+    ("r6_f2p5", 6, 2.5, None),
+    ("single_star", 8, 3, [2]),
+    ("edge_star_first", 8, 3, "edge_first"),
+    ("fitrad_too_big", 4, 5, None),
+]
+FIND_CASES = [  # name, hmin, fwhm, roundlim, sharplim
+    ("fwhm4", 60.0, 4.1, [-1.0, 1.0], [0.2, 1.0]),
+    ("fwhm2p5_loose", 40.0, 2.5, [-2.0, 2.0], [0.1, 1.2]),
+    ("fwhm9_bigbox", 80.0, 9.0, [-1.0, 1.0], [0.2, 1.0]),
+    ("none_found", 1e9, 4.1, [-1.0, 1.0], [0.2, 1.0]),
+]
+
+
+def psf_field():
+    """A sparse field of bright stars: several usable PSF stars, one too close to the edge, a few NaN pixels
+    inside one star's window (exercises the NaN patching of getpsf.py:357-373)."""
+    f = synth.make_field(260, 280, 26, seed=21, dtype=np.float64, margin=20.0, edge_frac=0.0, nan_frac=0.0, sat_frac=0.0,
+                         scale_range=(30.0, 120.0), with_noise=False)
+    img = f["image"].copy()
+    x, y = f["x"].copy(), f["y"].copy()
+    # star 4 is moved next to the frame edge in the LIST (its window leaves the frame -> skipped)
+    x[4], y[4] = 5.3, 100.2
+    # NaNs in the outskirts of star 6's window
+    ix, iy = int(x[6]), int(y[6])
+    img[iy + 7, ix - 6] = np.nan
+    img[iy - 8, ix + 5] = np.nan
+    img[iy - 8, ix + 6] = np.nan
+    return img, x, y, f
+
+
+def gen_getpsf():
+    getpsf = refloader.load("getpsf")
+    aper = refloader.load("aper")
+    img, x, y, f = psf_field()
+    with refloader.quiet(), np.errstate(all="ignore"):
+        r = aper.aper(img, x, y, phpadu=f["phpadu"], apr=np.array([5.0]), zeropoint=25.0, skyrad=[15, 22], badpix=[-12000, 60000],
+                      exact=False, verbose=False)
+    mag, sky = np.asarray(r[0], float).reshape(-1), np.asarray(r[4], float).reshape(-1)
+    mag = np.where(np.isfinite(mag), mag, 99.0)
+    out = dict(image=img, x=x, y=y, mag=mag, sky=sky, ronois=np.float64(f["ronois"]), phpadu=np.float64(f["phpadu"]))
+    order = np.argsort(mag)  # brightest first, as a user would pick PSF stars
+    for name, psfrad, fitrad, sel in GETPSF_CASES:
+        o = [int(v) for v in order if v not in (4, 6)]
+        if sel is None:  # bright stars, with the edge star (4) and the NaN-window star (6) in the middle of the list
+            idpsf = np.array(o[:3] + [4] + o[3:8] + [6] + o[8:10])
+        elif sel == "edge_first":
+            idpsf = np.array([4, o[0], 6, o[1]])
+        else:
+            idpsf = order[np.array(sel)]
+        with refloader.quiet() as log, np.errstate(all="ignore"):
+            g, p, m = getpsf.getpsf(img, x, y, mag, sky, f["ronois"], f["phpadu"], idpsf, psfrad, fitrad, "unused.fits", verbose=False)
+        out[name + "__idpsf"] = np.asarray(idpsf)
+        out[name + "__gauss"] = np.asarray(g, dtype=np.float64)
+        out[name + "__psf"] = np.asarray(p, dtype=np.float64)
+        out[name + "__psfmag"] = np.float64(m)
+        out[name + "__nskipped"] = np.int64(log.getvalue().count("too near edge") + log.getvalue().count("No convergence"))
+    return out
+
+
+def gen_find():
+    find = refloader.load("find")
+    f = synth.make_field(300, 340, 260, seed=31, dtype=np.float64, margin=4.0, edge_frac=0.05, nan_frac=0.0, sat_frac=1e-4,
+                         scale_range=(1.0, 120.0), with_noise=False)
+    img = f["image"]
+    out = dict(image=img)
+    for name, hmin, fwhm, roundlim, sharplim in FIND_CASES:
+        with refloader.quiet(), np.errstate(all="ignore"):
+            r = find.find(img, hmin, fwhm, roundlim, sharplim, verbose=False)
+        if r is None:
+            r = [np.zeros(0)] * 5
+            out[name + "__none"] = np.int64(1)
+        for nm, a in zip(("x", "y", "flux", "sharp", "round"), r):
+            out["%s__%s" % (name, nm)] = np.asarray(a, dtype=np.float64)
+    return out
+
+
+def main(which=("getpsf", "find")):
+    if "getpsf" in which:
+        np.savez_compressed(os.path.join(HERE, "golden_getpsf.npz"), **gen_getpsf())
+    if "find" in which:
+        np.savez_compressed(os.path.join(HERE, "golden_find.npz"), **gen_find())
+    for fn in sorted(os.listdir(HERE)):
+        if fn.endswith(".npz"):
+            print(fn, os.path.getsize(os.path.join(HERE, fn)))
+
+
+if __name__ == "__main__":
+    main(sys.argv[1:] or ("getpsf", "find"))
