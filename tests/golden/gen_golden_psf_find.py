@@ -92,6 +92,16 @@ def gen_find():
             out[name + "__none"] = np.int64(1)
         for nm, a in zip(("x", "y", "flux", "sharp", "round"), r):
             out["%s__%s" % (name, nm)] = np.asarray(a, dtype=np.float64)
+    # NaN pixels: h is NaN around them, min(h) is NaN, so the border assignment (find.py:192-194) writes NaN
+    rng = np.random.default_rng(32)
+    nan_idx = rng.integers(0, img.size, 12)
+    img2 = img.copy()
+    img2.reshape(-1)[nan_idx] = np.nan
+    out["nan_idx"] = nan_idx
+    with refloader.quiet(), np.errstate(all="ignore"):
+        r = find.find(img2, 60.0, 4.1, [-1.0, 1.0], [0.2, 1.0], verbose=False)
+    for nm, a in zip(("x", "y", "flux", "sharp", "round"), r):
+        out["with_nans__%s" % nm] = np.asarray(a, dtype=np.float64)
     return out
 
 
