@@ -147,6 +147,31 @@ int bphot_psfmodel_device(const double* d_xx, const double* d_yy, long long n,
                           const double* d_gauss, const double* d_psf, int npsf, int table_coords,
                           double* d_out, void* stream);
 
+/*
+ * find.find(image, hmin, fwhm, roundlim, sharplim)            PythonPhot/find.py:8-394 (DAOFIND)
+ * Convolution with the lowered truncated Gaussian (find.py:106-188), threshold + local-maximum
+ * search (find.py:211-233), per-candidate sharpness / roundness / marginal-Gaussian centroid
+ * (find.py:259-346).  Stars come out in the reference's order (row-major order of their peak pixel).
+ *   max_out           capacity of the five output columns (fp64, device / host)
+ *   counts[5]         HOST int array, always filled: [0] stars meeting every criterion (the number of
+ *                     valid output rows), [1] local maxima above hmin, [2..4] rejected by sharpness,
+ *                     roundness, centroid (the figures find.py prints when verbose)
+ * The call synchronises `stream` (the counts decide the output size).  If counts[0] > max_out nothing
+ * is written and BPHOT_ERR_CAPACITY is returned; call again with larger columns.  counts[0] == 0 is
+ * the case in which the reference returns None.
+ */
+int bphot_find_device(const void* d_image, int image_dtype, int nrow, int ncol, long long pitch,
+                      double hmin, double fwhm, double round_lo, double round_hi,
+                      double sharp_lo, double sharp_hi, int max_out,
+                      double* d_x, double* d_y, double* d_flux, double* d_sharp, double* d_round,
+                      int* counts, void* stream);
+
+int bphot_find_host(const void* image, int image_dtype, int nrow, int ncol,
+                    double hmin, double fwhm, double round_lo, double round_hi,
+                    double sharp_lo, double sharp_hi, int max_out,
+                    double* x, double* y, double* flux, double* sharp, double* roundness,
+                    int* counts, int device);
+
 #ifdef __cplusplus
 }
 #endif

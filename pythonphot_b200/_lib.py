@@ -14,6 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 SO_PATH = os.path.join(CSRC, "libbphot.so")
 F32, F64 = 0, 1
+ERR_CAPACITY = -3
 PKFIT, PKFIT_NOISE, PKFIT_NORECENT = 0, 1, 2
 MAX_APERTURES = 16
 
@@ -37,6 +38,8 @@ _SIGNATURES = {
     "bphot_mmm_device": (C.c_int, [_vp, _i, _vp, _i, _i, _d, _i, _i, _vp, _vp, _vp]),
     "bphot_pixwt_device": (C.c_int, [_d, _d, _d, _vp, _vp, _ll, _vp, _vp]),
     "bphot_psfmodel_device": (C.c_int, [_vp, _vp, _ll, _vp, _vp, _i, _i, _vp, _vp]),
+    "bphot_find_device": (C.c_int, [_vp, _i, _i, _i, _ll, _d, _d, _d, _d, _d, _d, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "bphot_find_host": (C.c_int, [_vp, _i, _i, _i, _d, _d, _d, _d, _d, _d, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i]),
 }
 EXPORTS = tuple(_SIGNATURES)
 

@@ -8,10 +8,13 @@
 
 #include <atomic>
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_select.cuh>
+#include <thrust/iterator/counting_iterator.h>
 
 #include "../../include/bphot.h"
 #include "aper_kernel.cu"
 #include "pkfit_kernel.cu"
+#include "find_kernel.cu"
 
 namespace {
 
@@ -119,6 +122,100 @@ int make_star_order(const double* d_x, const double* d_y, int n, int nrow, int n
     g_launches += 1;  // ours; the radix sort passes are CUB's
     out->order = i_out;
     return 0;
+}
+
+
+// ---- find.py:106-183 on the host: everything that depends on fwhm alone
+double np_sum_host(const double* a, int n) {  // numpy's pairwise add-reduce (blocks of 128, 8 accumulators)
+    if (n < 8) {
+        double r = 0.0;
+        for (int i = 0; i < n; i++) r += a[i];
+        return r;
+    }
+    if (n <= 128) {
+        double r[8];
+        int i;
+        for (i = 0; i < 8; i++) r[i] = a[i];
+        for (i = 8; i < n - (n % 8); i += 8)
+            for (int j = 0; j < 8; j++) r[j] += a[i + j];
+        double res = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]));
+        for (; i < n; i++) res += a[i];
+        return res;
+    }
+    int n2 = n / 2;
+    n2 -= n2 % 8;
+    return np_sum_host(a, n2) + np_sum_host(a + n2, n - n2);
+}
+
+void find_constants(double fwhm, bphot::FindConsts* K) {
+    using bphot::FIND_MAXBOX;
+    memset(K, 0, sizeof(*K));
+    double radius = 0.637 * fwhm;  // find.py:106-107
+    if (radius < 2.001) radius = 2.001;
+    const double radsq = radius * radius;
+    int nhalf = (int)radius;
+    if (nhalf > (FIND_MAXBOX - 1) / 2) nhalf = (FIND_MAXBOX - 1) / 2;
+    const int nbox = 2 * nhalf + 1, nn = nbox * nbox;
+    const double sigsq = (fwhm / 2.35482) * (fwhm / 2.35482);
+    K->nhalf = nhalf; K->nbox = nbox; K->sigsq = sigsq;
+    double g[FIND_MAXBOX * FIND_MAXBOX], t[FIND_MAXBOX * FIND_MAXBOX], wt[FIND_MAXBOX], v[FIND_MAXBOX];
+    unsigned char mask[FIND_MAXBOX * FIND_MAXBOX];
+    int pixels = 0;
+    for (int r = 0; r < nbox; r++)
+        for (int c = 0; c < nbox; c++) {
+            const double d2 = (double)((r - nhalf) * (r - nhalf) + (c - nhalf) * (c - nhalf));  // find.py:123-126
+            mask[r * nbox + c] = d2 <= radsq;
+            pixels += mask[r * nbox + c];
+            g[r * nbox + c] = exp(-0.5 * d2 / sigsq);
+        }
+    for (int i = 0; i < nbox; i++) wt[i] = (double)(nhalf - abs(i - nhalf) + 1);  // find.py:150-152
+    for (int i = 0; i < nbox; i++) K->wt[i] = wt[i];
+    for (int r = 0; r < nbox; r++) {  // sgx = sum(g*xwt, 1)
+        for (int c = 0; c < nbox; c++) v[c] = g[r * nbox + c] * wt[c];
+        K->sgx[r] = np_sum_host(v, nbox);
+    }
+    K->p = np_sum_host(wt, nbox);
+    for (int c = 0; c < nbox; c++) {  // sgy = sum(g*ywt, 0): rows are added in order
+        double s = g[c] * wt[0];
+        for (int r = 1; r < nbox; r++) s += g[r * nbox + c] * wt[r];
+        K->sgy[c] = s;
+    }
+#define BP_VSUM(expr) ([&]() { for (int i = 0; i < nbox; i++) v[i] = (expr); return np_sum_host(v, nbox); }())
+    K->sumgx = BP_VSUM(wt[i] * K->sgy[i]);
+    K->sumgy = BP_VSUM(wt[i] * K->sgx[i]);
+    K->sumgsqy = BP_VSUM(wt[i] * K->sgy[i] * K->sgy[i]);
+    K->sumgsqx = BP_VSUM(wt[i] * K->sgx[i] * K->sgx[i]);
+    for (int i = 0; i < nbox; i++) {
+        const double vec = (double)(nhalf - i);
+        K->dgdx[i] = K->sgy[i] * vec;
+        K->dgdy[i] = K->sgx[i] * vec;
+    }
+    K->sdgdxs = BP_VSUM(wt[i] * (K->dgdx[i] * K->dgdx[i]));
+    K->sdgdx = BP_VSUM(wt[i] * K->dgdx[i]);
+    K->sdgdys = BP_VSUM(wt[i] * (K->dgdy[i] * K->dgdy[i]));
+    K->sdgdy = BP_VSUM(wt[i] * K->dgdy[i]);
+    K->sgdgdx = BP_VSUM(wt[i] * K->sgy[i] * K->dgdx[i]);
+    K->sgdgdy = BP_VSUM(wt[i] * K->sgx[i] * K->dgdy[i]);
+    // convolution kernel, find.py:174-179
+    for (int i = 0; i < nn; i++) K->c[i] = g[i] * mask[i];
+    double sumc = np_sum_host(K->c, nn);
+    for (int i = 0; i < nn; i++) t[i] = K->c[i] * K->c[i];
+    const double sumcsq = np_sum_host(t, nn) - sumc * sumc / pixels;
+    sumc = sumc / pixels;
+    for (int i = 0; i < nn; i++)
+        if (mask[i]) K->c[i] = (K->c[i] - sumc) / sumcsq;
+    // 1-D kernel of the roundness statistic, find.py:180-183
+    for (int i = 0; i < nbox; i++) v[i] = exp(-.5 * (double)((i - nhalf) * (i - nhalf)) / sigsq);
+    double c1[FIND_MAXBOX];
+    for (int i = 0; i < nbox; i++) c1[i] = v[i];
+    const double sumc1 = np_sum_host(c1, nbox) / nbox;
+    for (int i = 0; i < nbox; i++) v[i] = c1[i] * c1[i];
+    const double sumc1sq = np_sum_host(v, nbox) - sumc1;
+    for (int i = 0; i < nbox; i++) K->c1[i] = (c1[i] - sumc1) / sumc1sq;
+#undef BP_VSUM
+    for (int i = 0; i < nn; i++) K->ring[i] = mask[i];
+    K->ring[nhalf * nbox + nhalf] = 0;  // find.py:199-200
+    K->pixels = pixels - 1;
 }
 
 struct DevBuf {  // frees on scope exit
@@ -380,6 +477,136 @@ int bphot_psfmodel_device(const double* d_xx, const double* d_yy, long long n,
     bphot::psfmodel_kernel<<<(int)blocks, 128, 0, (cudaStream_t)stream>>>(d_xx, d_yy, n, d_gauss, d_psf, npsf, table_coords, d_out);
     g_launches++;
     CU_TRY(cudaGetLastError());
+    return BPHOT_OK;
+}
+
+int bphot_find_device(const void* d_image, int image_dtype, int nrow, int ncol, long long pitch,
+                      double hmin, double fwhm, double round_lo, double round_hi, double sharp_lo, double sharp_hi,
+                      int max_out, double* d_x, double* d_y, double* d_flux, double* d_sharp, double* d_round,
+                      int* counts, void* stream) {
+    using namespace bphot;
+    if (!d_image || !counts || nrow <= 0 || ncol <= 0 || max_out < 0) return fail(BPHOT_ERR_ARG, "bphot_find: null image/counts or bad shape");
+    if (image_dtype != BPHOT_F32 && image_dtype != BPHOT_F64) return fail(BPHOT_ERR_ARG, "bphot_find: image dtype %d", image_dtype);
+    if (!(fwhm >= 0.5)) return fail(BPHOT_ERR_ARG, "bphot_find: FWHM must be at least 0.5 pixels (find.py:103)");
+    if (max_out > 0 && (!d_x || !d_y || !d_flux || !d_sharp || !d_round)) return fail(BPHOT_ERR_ARG, "bphot_find: null output pointer");
+    const long long npix = (long long)nrow * ncol;
+    if (npix > 2147483647LL) return fail(BPHOT_ERR_ARG, "bphot_find: more than 2^31-1 pixels");
+    FindConsts hK;
+    find_constants(fwhm, &hK);
+    if (nrow < 2 * hK.nbox || ncol < 2 * hK.nbox) return fail(BPHOT_ERR_ARG, "bphot_find: image smaller than two convolution boxes (%d px)", hK.nbox);
+    for (int k = 0; k < 5; k++) counts[k] = 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    FindParams P;
+    memset(&P, 0, sizeof(P));
+    P.img = d_image; P.nrow = nrow; P.ncol = ncol; P.pitch = pitch > 0 ? pitch : ncol;
+    P.hmin = hmin; P.round_lo = round_lo; P.round_hi = round_hi; P.sharp_lo = sharp_lo; P.sharp_hi = sharp_hi;
+    const int tiles = ((ncol + FIND_TX - 1) / FIND_TX) * ((nrow + FIND_TY - 1) / FIND_TY);
+    P.nblocks = tiles;
+    // one stream-ordered block for the fixed-size scratch: h | blockmin | minh | consts | counts | flags
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const size_t o_h = 0, o_bm = o_h + up((size_t)npix * 8), o_mh = o_bm + up((size_t)tiles * 8), o_K = o_mh + 256,
+                 o_cnt = o_K + up(sizeof(FindConsts)), o_fl = o_cnt + 256, total = o_fl + up((size_t)npix);
+    char* base = nullptr;
+    CU_TRY(cudaMallocAsync((void**)&base, total, st));
+    void* extra = nullptr;  // candidate-sized scratch, allocated once the count is known
+    auto cleanup = [&]() { if (extra) cudaFreeAsync(extra, st); cudaFreeAsync(base, st); };
+#define CU_TRY_F(expr)                                                                                   \
+    do {                                                                                                 \
+        cudaError_t e_ = (expr);                                                                         \
+        if (e_ != cudaSuccess) { cleanup(); return fail(BPHOT_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e_)); } \
+    } while (0)
+    P.h = reinterpret_cast<double*>(base + o_h); P.blockmin = reinterpret_cast<double*>(base + o_bm);
+    P.minh = reinterpret_cast<double*>(base + o_mh); P.K = reinterpret_cast<const FindConsts*>(base + o_K);
+    P.counts = reinterpret_cast<int*>(base + o_cnt); P.flags = reinterpret_cast<unsigned char*>(base + o_fl);
+    CU_TRY_F(cudaMemcpyAsync(base + o_K, &hK, sizeof(FindConsts), cudaMemcpyHostToDevice, st));
+    const size_t tile_bytes = (size_t)(FIND_TX + 2 * hK.nhalf) * (FIND_TY + 2 * hK.nhalf) * 8;
+    if (image_dtype == BPHOT_F32) find_convolve_kernel<float><<<tiles, FIND_THREADS, tile_bytes, st>>>(P);
+    else find_convolve_kernel<double><<<tiles, FIND_THREADS, tile_bytes, st>>>(P);
+    find_min_kernel<<<1, FIND_THREADS, 0, st>>>(P);
+    long long cb = (npix + FIND_THREADS - 1) / FIND_THREADS;
+    if (cb > 148 * 16) cb = 148 * 16;
+    find_candidate_kernel<<<(int)cb, FIND_THREADS, 0, st>>>(P);
+    g_launches += 3;
+    int hc[6] = {0, 0, 0, 0, 0, 0};
+    CU_TRY_F(cudaMemcpyAsync(hc, P.counts, sizeof(hc), cudaMemcpyDeviceToHost, st));
+    CU_TRY_F(cudaStreamSynchronize(st));
+    const int ncand = hc[0];
+    counts[1] = ncand;
+    if (ncand == 0) { cleanup(); CU_TRY(cudaGetLastError()); return BPHOT_OK; }
+    // candidate-sized scratch: cand | sel | nsel | cx cy cflux csharp cround | cok | cub temp
+    size_t tmp1 = 0, tmp2 = 0;
+    thrust::counting_iterator<int> iota(0);
+    CU_TRY_F(cub::DeviceSelect::Flagged(nullptr, tmp1, iota, (const unsigned char*)nullptr, (int*)nullptr, (int*)nullptr, (int)npix, st));
+    CU_TRY_F(cub::DeviceSelect::Flagged(nullptr, tmp2, iota, (const unsigned char*)nullptr, (int*)nullptr, (int*)nullptr, ncand, st));
+    const size_t tmpb = up(tmp1 > tmp2 ? tmp1 : tmp2), col = up((size_t)ncand * 8);
+    const size_t e_cand = 0, e_sel = e_cand + up((size_t)ncand * 4), e_n = e_sel + up((size_t)ncand * 4), e_col = e_n + 256,
+                 e_ok = e_col + 5 * col, e_tmp = e_ok + up((size_t)ncand), etotal = e_tmp + tmpb;
+    CU_TRY_F(cudaMallocAsync(&extra, etotal, st));
+    char* eb = reinterpret_cast<char*>(extra);
+    int* d_cand = reinterpret_cast<int*>(eb + e_cand);
+    int* d_sel = reinterpret_cast<int*>(eb + e_sel);
+    int* d_n = reinterpret_cast<int*>(eb + e_n);
+    size_t tb = tmpb;
+    CU_TRY_F(cub::DeviceSelect::Flagged(eb + e_tmp, tb, iota, P.flags, d_cand, d_n, (int)npix, st));
+    P.cand = d_cand; P.ncand = ncand;
+    P.cx = reinterpret_cast<double*>(eb + e_col); P.cy = reinterpret_cast<double*>(eb + e_col + col);
+    P.cflux = reinterpret_cast<double*>(eb + e_col + 2 * col); P.csharp = reinterpret_cast<double*>(eb + e_col + 3 * col);
+    P.cround = reinterpret_cast<double*>(eb + e_col + 4 * col); P.cok = reinterpret_cast<unsigned char*>(eb + e_ok);
+    int sb = (ncand + 127) / 128;
+    if (sb > 148 * 16) sb = 148 * 16;
+    if (image_dtype == BPHOT_F32) find_stats_kernel<float><<<sb, 128, 0, st>>>(P);
+    else find_stats_kernel<double><<<sb, 128, 0, st>>>(P);
+    g_launches += 1;
+    tb = tmpb;
+    CU_TRY_F(cub::DeviceSelect::Flagged(eb + e_tmp, tb, iota, P.cok, d_sel, d_n, ncand, st));
+    CU_TRY_F(cudaMemcpyAsync(hc, P.counts, sizeof(hc), cudaMemcpyDeviceToHost, st));
+    CU_TRY_F(cudaStreamSynchronize(st));
+    counts[0] = hc[4]; counts[2] = hc[1]; counts[3] = hc[2]; counts[4] = hc[3];
+    const int nstars = hc[4];
+    if (nstars > max_out) {
+        cleanup();
+        return fail(BPHOT_ERR_CAPACITY, "bphot_find: %d stars found, output arrays hold %d (counts[0] has the size needed)", nstars, max_out);
+    }
+    if (nstars > 0) {
+        P.sel = d_sel; P.nsel = nstars;
+        P.ox = d_x; P.oy = d_y; P.oflux = d_flux; P.osharp = d_sharp; P.oround = d_round;
+        int gb = (nstars + 255) / 256;
+        if (gb > 148 * 8) gb = 148 * 8;
+        find_gather_kernel<<<gb, 256, 0, st>>>(P);
+        g_launches += 1;
+        CU_TRY_F(cudaStreamSynchronize(st));
+    }
+    cleanup();
+#undef CU_TRY_F
+    CU_TRY(cudaGetLastError());
+    return BPHOT_OK;
+}
+
+int bphot_find_host(const void* image, int image_dtype, int nrow, int ncol,
+                    double hmin, double fwhm, double round_lo, double round_hi, double sharp_lo, double sharp_hi,
+                    int max_out, double* x, double* y, double* flux, double* sharp, double* roundness,
+                    int* counts, int device) {
+    if (bphot_device_count() < 1) return fail(BPHOT_ERR_NODEVICE, "no CUDA device (libbphot has no CPU fallback)");
+    if (!image || nrow <= 0 || ncol <= 0 || max_out < 0 || !counts) return fail(BPHOT_ERR_ARG, "bphot_find_host: bad argument");
+    if (image_dtype != BPHOT_F32 && image_dtype != BPHOT_F64) return fail(BPHOT_ERR_ARG, "bphot_find_host: image dtype %d", image_dtype);
+    CU_TRY(cudaSetDevice(device));
+    DevBuf dimg, dout;
+    CU_TRY(dimg.alloc((size_t)nrow * ncol * esize(image_dtype)));
+    CU_TRY(cudaMemcpyAsync(dimg.p, image, (size_t)nrow * ncol * esize(image_dtype), cudaMemcpyHostToDevice, 0));
+    const size_t col = (size_t)max_out * 8;
+    CU_TRY(dout.alloc(5 * col));
+    double* o = dout.as<double>();
+    int rc = bphot_find_device(dimg.p, image_dtype, nrow, ncol, ncol, hmin, fwhm, round_lo, round_hi, sharp_lo, sharp_hi, max_out,
+                               o, o + max_out, o + 2 * (size_t)max_out, o + 3 * (size_t)max_out, o + 4 * (size_t)max_out, counts, 0);
+    if (rc) return rc;
+    const size_t nb = (size_t)counts[0] * 8;
+    if (nb) {
+        CU_TRY(cudaMemcpy(x, o, nb, cudaMemcpyDeviceToHost));
+        CU_TRY(cudaMemcpy(y, o + max_out, nb, cudaMemcpyDeviceToHost));
+        CU_TRY(cudaMemcpy(flux, o + 2 * (size_t)max_out, nb, cudaMemcpyDeviceToHost));
+        CU_TRY(cudaMemcpy(sharp, o + 3 * (size_t)max_out, nb, cudaMemcpyDeviceToHost));
+        CU_TRY(cudaMemcpy(roundness, o + 4 * (size_t)max_out, nb, cudaMemcpyDeviceToHost));
+    }
     return BPHOT_OK;
 }
 

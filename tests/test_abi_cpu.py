@@ -47,6 +47,11 @@ def test_no_cpu_fallback(lib):
         pp.pkfit_class(img, np.ones(5), np.zeros((41, 41)), 1.0, 1.0)
     with pytest.raises(lib.BphotError):
         pp.mmm.mmm(np.arange(100.0))
+    with pytest.raises(lib.BphotError):
+        pp.find.find(img, 10.0, 4.0, verbose=False)
+    with pytest.raises(lib.BphotError):
+        pp.getpsf.getpsf(img + 1.0, np.array([32.0]), np.array([32.0]), np.array([10.0]), np.array([0.0]), 1.0, 1.0, [0], 4, 2, None,
+                         verbose=False)
     # the host-buffer C entry point reports "no device" instead of computing anything
     z = np.zeros(1)
     rc = lib.lib().bphot_aper_host(lib.nptr(img), 0, 64, 64, lib.nptr(z), lib.nptr(z), 1, 1.0, lib.nptr(z), 1, 25.0, 40.0, 50.0,
