@@ -265,13 +265,17 @@ def main():
             if ev:
                 ev[3].record()
         if world > 1:  # the per-star result records are packed and all-gathered, then put back in caller order (north_star)
+            if ev:
+                ev[4].record()
             rec = {}
             if do_aper:
                 rec.update({"a_" + k: v for k, v in bufs["aper"].items()})
             if do_fit:
                 rec.update({"f_" + k: bufs["fit"][k] for k in ("errmag", "chi", "sharp", "scale", "niter")})
             packed, _layout = shard.pack_records(rec)
-            gathered["rec"] = plan.gather(packed)
+            gathered["rec"] = {dt: plan.gather(block) for dt, block in packed.items()}
+            if ev:
+                ev[5].record()
 
     gathered = {}
 
@@ -279,7 +283,7 @@ def main():
         step()
     torch.cuda.synchronize()
     launches0 = _lib.launch_count()
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(a.steps)]
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(6)] for _ in range(a.steps)]
     sampler = ClockSampler(local_rank)
     if world > 1:
         dist.barrier()
@@ -298,10 +302,11 @@ def main():
     ms_total = t_start.elapsed_time(t_end)
     ms_aper = float(np.mean([e[0].elapsed_time(e[1]) for e in evs])) if do_aper else 0.0
     ms_fit = float(np.mean([e[2].elapsed_time(e[3]) for e in evs])) if do_fit else 0.0
+    ms_gather = float(np.mean([e[4].elapsed_time(e[5]) for e in evs])) if world > 1 else 0.0
     if world > 1:
-        tt = torch.tensor([ms_total, ms_aper, ms_fit], dtype=torch.float64, device=dev)
+        tt = torch.tensor([ms_total, ms_aper, ms_fit, ms_gather], dtype=torch.float64, device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        ms_total, ms_aper, ms_fit = (float(v) for v in tt.tolist())
+        ms_total, ms_aper, ms_fit, ms_gather = (float(v) for v in tt.tolist())
     ms_step = ms_total / a.steps
     value = world * n / (ms_step * 1e-3)
 
@@ -368,6 +373,8 @@ def main():
                                "achieved_gbs": n * b_fit / (ms_fit * 1e-3) / 1e9,
                                "mean_niter": float(nit.double().mean().item()),
                                "frac_niter_25": float((nit == 25).double().mean().item())}
+        if world > 1:
+            stages["gather"] = {"ms": ms_gather, "what": "pack per dtype + NCCL all-gather + un-permute of the per-star records"}
         dom = "aper" if ms_aper >= ms_fit else "pkfit"
         ach = stages[dom]["achieved_gbs"]
         roofline = {"bound": "hbm", "kernel": "aper_kernel<float>" if dom == "aper" else "pkfit_kernel<float,float>",

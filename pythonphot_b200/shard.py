@@ -72,6 +72,15 @@ class ShardPlan(object):
         # position of star s in the gathered (rank-major) array
         self.inverse = np.empty(self.n, dtype=np.int64)
         self.inverse[perm] = np.arange(self.n, dtype=np.int64)
+        self._dev = {}  # (which, device) -> index tensor, uploaded once
+
+    def _index_t(self, which, rank, device):
+        import torch
+        key = (which, rank, str(device))
+        if key not in self._dev:
+            idx = self.inverse if which == "inverse" else self.indices(rank)
+            self._dev[key] = torch.from_numpy(np.ascontiguousarray(idx)).to(device)
+        return self._dev[key]
 
     @classmethod
     def for_stars(cls, x, y, nrow, ncol, world):
@@ -86,8 +95,7 @@ class ShardPlan(object):
         idx = self.indices(rank)
         if isinstance(column, np.ndarray):
             return np.ascontiguousarray(column[idx])
-        import torch
-        return column.index_select(0, torch.from_numpy(idx).to(column.device)).contiguous()
+        return column.index_select(0, self._index_t("shard", rank, column.device)).contiguous()
 
     def gather(self, record, group=None):
         """All-gather one per-star record tensor ``[m, ...]`` (same shape and dtype on every rank) and
@@ -103,29 +111,30 @@ class ShardPlan(object):
         else:
             full = torch.empty((world * self.m,) + tuple(record.shape[1:]), dtype=record.dtype, device=record.device)
             dist.all_gather_into_tensor(full, record, group=group)
-        return full.index_select(0, torch.from_numpy(self.inverse).to(full.device))
+        return full.index_select(0, self._index_t("inverse", 0, full.device))
 
 
 def pack_records(columns):
-    """Dict of per-star tensors ``[m]`` / ``[m, k]`` (fp64, int32, uint8 ...) -> one uint8 tensor ``[m, width]``
-    plus the layout needed to unpack: one all-gather per call instead of one per column."""
+    """Dict of per-star tensors ``[m]`` / ``[m, k]`` -> one ``[m, width]`` tensor PER DTYPE plus the layout needed
+    to unpack, so that a pass costs one all-gather and one un-permute per dtype (fp64, int32, uint8) instead of
+    one per column, and every copy moves whole typed words."""
     import torch
-    layout, parts = [], []
+    groups, layout = {}, []
     for name, t in columns.items():
-        t2 = t.reshape(t.shape[0], -1).contiguous()
-        b = t2.view(torch.uint8).reshape(t.shape[0], -1)
-        layout.append((name, t.dtype, tuple(t.shape[1:]), b.shape[1]))
-        parts.append(b)
-    return torch.cat(parts, dim=1), layout
+        t2 = t.reshape(t.shape[0], -1)
+        parts = groups.setdefault(t.dtype, [])
+        start = sum(p.shape[1] for p in parts)
+        parts.append(t2)
+        layout.append((name, t.dtype, tuple(t.shape[1:]), start, t2.shape[1]))
+    packed = {dt: (parts[0].contiguous() if len(parts) == 1 else torch.cat(parts, dim=1)) for dt, parts in groups.items()}
+    return packed, layout
 
 
 def unpack_records(packed, layout):
-    out, o = {}, 0
-    for name, dtype, tail, width in layout:
-        col = packed.new_empty((packed.shape[0], width))  # fresh buffer: canonical strides even for one row
-        col.copy_(packed[:, o:o + width])
-        out[name] = col.view(dtype).reshape((packed.shape[0],) + tail)
-        o += width
+    out = {}
+    for name, dtype, tail, start, width in layout:
+        block = packed[dtype]
+        out[name] = block[:, start:start + width].reshape((block.shape[0],) + tail)
     return out
 
 
@@ -165,7 +174,7 @@ def run_sharded(plan, columns, compute, group=None):
     shard = {k: plan.take(v, rank) for k, v in columns.items()}
     res = compute(shard)
     packed, layout = pack_records(res)
-    return unpack_records(plan.gather(packed, group=group), layout)
+    return unpack_records({dt: plan.gather(block, group=group) for dt, block in packed.items()}, layout)
 
 
 class ShardedPhotometry(object):

@@ -99,8 +99,9 @@ def test_morton_order_groups_tiles():
 def test_pack_unpack_roundtrip():
     cols = {"a": torch.randn(9, 3, dtype=torch.float64), "b": torch.arange(9, dtype=torch.int32),
             "c": torch.randint(0, 2, (9, 3), dtype=torch.uint8)}
+    cols["d"] = torch.randn(9, dtype=torch.float64)
     packed, layout = shard.pack_records(cols)
-    assert packed.shape == (9, 3 * 8 + 4 + 3)
+    assert {dt: tuple(b.shape) for dt, b in packed.items()} == {torch.float64: (9, 4), torch.int32: (9, 1), torch.uint8: (9, 3)}
     back = shard.unpack_records(packed, layout)
     for k in cols:
         assert torch.equal(back[k], cols[k])
