@@ -136,12 +136,24 @@ def to_device_image(a, device, allow=("float32", "float64")):
 
 
 def to_device_mask(a, device):
-    """mask image -> uint8 CUDA tensor, nonzero = masked (pkfit_noise.py:206-208 tests mask == 0)."""
+    """mask image -> uint8 CUDA tensor, nonzero = masked (pkfit_noise.py:206-208 tests mask == 0).
+
+    uint8 / bool masks are uploaded as they are (the kernels test ``!= 0`` themselves); other dtypes are
+    reduced to 0/1 on the device after the upload, never on the host."""
     torch = torch_cuda()
     if isinstance(a, torch.Tensor):
-        t = (a != 0).to(torch.uint8).to(device, non_blocking=True)
+        t = a.to(device, non_blocking=True)
+        if t.dtype == torch.bool:
+            t = t.view(torch.uint8)
+        elif t.dtype != torch.uint8:
+            t = (t != 0).view(torch.uint8)
     else:
-        t = torch.from_numpy(np.ascontiguousarray(np.asarray(a) != 0).view(np.uint8)).to(device, non_blocking=True)
+        a = np.asarray(a)
+        if a.dtype == np.bool_:
+            a = a.view(np.uint8)
+        t = torch.from_numpy(np.ascontiguousarray(a)).to(device, non_blocking=True)
+        if t.dtype != torch.uint8:
+            t = (t != 0).view(torch.uint8)
     return t.contiguous()
 
 

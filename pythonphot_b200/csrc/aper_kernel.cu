@@ -229,78 +229,93 @@ BP_D StarGeom star_geom(const AperParams& P, double x, double y) {
     return g;
 }
 
-// P1a: candidate column spans of every stamp row, one row per thread (aper.py:240-267).  Row r can
-// only hold annulus pixels in [a0, a1] (outer chord, +-1 px) minus [b0, b1] (columns strictly inside
-// the inner circle with a 1 px margin); rows that miss the outer circle get an empty span.
-// span[4*r .. 4*r+3] = a0, b0, b1, a1.
-BP_D void row_spans(const StarGeom& g, double rinsq, double routsq, int* span, int tid) {
+// P1a: EXACT column spans of every stamp row, one row per thread (aper.py:240-267).  In floating point
+// rsq(c) = (c-dx)^2 + dysq is monotone in |c-dx| (every operation rounds monotonically), so the columns of row r
+// with rsq <= rout^2 form one interval [a0, a1] and those with rsq < rin^2 one interval [b0, b1] inside it; both
+// are found from a sqrt estimate and then corrected with the reference's own fp64 test, at most a few steps.
+// The annulus pixels of the row are [a0, b0) and (b1, a1]; span[4r..4r+3] = a0, b0, b1, a1 and rowoff[r] = number of
+// annulus pixels in the rows above (filled by row_offsets), so pixel t of row r owns key slot rowoff[r] + t.
+BP_D void row_spans(const StarGeom& g, double rinsq, double routsq, int* span, int* rowoff, int tid) {
     for (int r = tid; r < g.ny; r += AP_THREADS) {
         const double dyv = (double)r - g.dy, dysq = dyv * dyv;
-        const double rem = routsq - dysq;
+        auto rsq_at = [&](int c) { const double dxv = (double)c - g.dx; return dxv * dxv + dysq; };
         int a0 = 0, a1 = -1, b0 = 0, b1 = -1;
+        const double rem = routsq - dysq;
         if (rem >= 0.0) {  // otherwise rsq >= dysq > routsq for the whole row
-            const double hw = sqrt(rem) + 1.0;
-            a0 = (int)floor(g.dx - hw);
-            a1 = (int)ceil(g.dx + hw);
-            if (a0 < 0) a0 = 0;
-            if (a1 > g.nx - 1) a1 = g.nx - 1;
-            b0 = a1 + 1; b1 = a1;  // empty exclusion span
+            const double hw = sqrt(rem);
+            int lo = (int)floor(g.dx - hw) - 1, hi = (int)ceil(g.dx + hw) + 1;  // both surely outside
+            while (lo <= hi && !(rsq_at(lo) <= routsq)) lo++;
+            while (hi >= lo && !(rsq_at(hi) <= routsq)) hi--;
+            int e0 = 1, e1 = 0;  // columns strictly inside the inner circle
             const double remi = rinsq - dysq;
-            if (remi > 4.0) {  // columns with |c - dx| <= sqrt(remi) - 1 have rsq < rinsq
-                const double hwi = sqrt(remi) - 1.0;
-                int e0 = (int)ceil(g.dx - hwi), e1 = (int)floor(g.dx + hwi);
-                if (e0 < a0) e0 = a0;
-                if (e1 > a1) e1 = a1;
+            if (remi > 0.0) {
+                const double hwi = sqrt(remi);
+                e0 = (int)floor(g.dx - hwi) - 1;
+                e1 = (int)ceil(g.dx + hwi) + 1;
+                while (e0 <= e1 && !(rsq_at(e0) < rinsq)) e0++;
+                while (e1 >= e0 && !(rsq_at(e1) < rinsq)) e1--;
+            }
+            if (lo < 0) lo = 0;
+            if (hi > g.nx - 1) hi = g.nx - 1;
+            if (lo <= hi) {
+                a0 = lo; a1 = hi;
+                if (e0 < lo) e0 = lo;
+                if (e1 > hi) e1 = hi;
                 if (e0 <= e1) { b0 = e0; b1 = e1; }
+                else { b0 = hi + 1; b1 = hi; }
             }
         }
         span[4 * r + 0] = a0; span[4 * r + 1] = b0; span[4 * r + 2] = b1; span[4 * r + 3] = a1;
+        rowoff[r] = (b0 - a0) + (a1 - b1);
     }
 }
 
-// P1b: one warp's rows of the annulus gather.  The reference's own fp64 test rin^2 <= rsq <= rout^2 and
-// bad-pixel window decide membership; loads are coalesced along the row.  Returns this lane's copy of the
-// warp's count of selected pixels (NaNs included, as aper's nsky counts them; the key array drops them).
+// Exclusive prefix sum of the per-row pixel counts, by one warp; returns the total (all lanes).
+BP_D int row_offsets(int* rowoff, int ny, int lane) {
+    int carry = 0;
+    for (int base = 0; base < ny; base += 32) {
+        const int r = base + lane;
+        const int v = r < ny ? rowoff[r] : 0;
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int up = __shfl_up_sync(FULL, inc, o);
+            if (lane >= o) inc += up;
+        }
+        if (r < ny) rowoff[r] = carry + inc - v;
+        carry += __shfl_sync(FULL, inc, 31);
+    }
+    return carry;
+}
+
+// P1b: one warp's rows of the annulus gather: coalesced loads along the row, every pixel goes to its own slot, so
+// there is no ballot, no atomic and no dependence between loads.  Pixels the reference drops (outside the bad-pixel
+// window, aper.py:260-266; NaN, mmm.py:106) leave +inf in their slot -- the sort does not care where the padding
+// sits.  Returns, per lane, partial counts: x = pixels rejected by the window, y = selected pixels that are NaN.
 template <typename T>
-BP_D int gather_rows(const AperParams& P, const T* __restrict__ stamp, const StarGeom& g, double rinsq, double routsq,
-                     const int* span, T* keys, int* s_nvalid, int warp, int lane) {
-    int nsel = 0;
+BP_D int2 gather_rows(const AperParams& P, const T* __restrict__ stamp, const StarGeom& g, const int* span, const int* rowoff,
+                      T* __restrict__ keys, int warp, int lane) {
+    int nrej = 0, nnan = 0;
     const bool window = P.badlo != P.badhi;
     for (int r = warp; r < g.ny; r += AP_WARPS) {
         const int4 sp = *reinterpret_cast<const int4*>(span + 4 * r);
         const int a0 = sp.x, b0 = sp.y, b1 = sp.z, a1 = sp.w;
         const int nl = b0 - a0, tot = nl + (a1 - b1);
-        if (tot <= 0) continue;
-        const double dyv = (double)r - g.dy, dysq = dyv * dyv;
+        const int off = rowoff[r];
         const T* __restrict__ row = stamp + (size_t)r * P.pitch;
-        for (int base = 0; base < tot; base += 32) {
-            const int t = base + lane;
-            bool sel = false, valid = false;
-            T val = T(0);
-            if (t < tot) {
-                const int c = t < nl ? a0 + t : b1 + 1 + (t - nl);
-                const double dxv = (double)c - g.dx;
-                const double rsq = dxv * dxv + dysq;
-                if (rsq >= rinsq && rsq <= routsq) {
-                    val = row[c];
-                    const double dv = (double)val;
-                    sel = !(window && (dv < P.badlo || dv > P.badhi));
-                    valid = sel && (val == val);  // mmm.py:106 drops NaNs; aper's nsky keeps them
-                }
-            }
-            const unsigned m_all = __ballot_sync(FULL, sel), m_val = __ballot_sync(FULL, valid);
-            nsel += __popc(m_all);
-            if (m_val == 0u) continue;
-            int base_idx = 0;
-            if (lane == 0) base_idx = atomicAdd(s_nvalid, __popc(m_val));
-            base_idx = __shfl_sync(FULL, base_idx, 0);
-            if (valid) {
-                const int idx = base_idx + __popc(m_val & ((1u << lane) - 1u));
-                if (idx < P.sort_cap) keys[idx] = val;
-            }
+        for (int t = lane; t < tot; t += 32) {
+            const int c = t < nl ? a0 + t : b1 + 1 + (t - nl);
+            const T val = row[c];
+            const double dv = (double)val;
+            const bool rej = window && (dv < P.badlo || dv > P.badhi);
+            const bool isnan_ = !rej && !(val == val);
+            nrej += rej;
+            nnan += isnan_;
+            const int idx = off + t;
+            if (idx < P.sort_cap) keys[idx] = (rej || isnan_) ? KeyTraits<T>::inf() : val;
         }
     }
-    return nsel;
+    return make_int2(nrej, nnan);
 }
 
 // Per-warp list of pixels the aperture circle crosses (they need pixwt): centre, stamp position, weight.
@@ -435,8 +450,9 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? 6 : 
     T* keys = reinterpret_cast<T*>(smem_raw);
     const size_t key_bytes = ((size_t)(K > 0 ? AP_THREADS * (K + 1) : P.sort_cap) * sizeof(T) + 15) & ~(size_t)15;
     int* span = reinterpret_cast<int*>(smem_raw + key_bytes);
-    __shared__ int s_nvalid;
-    __shared__ int s_nsel[AP_WARPS];
+    int* rowoff = span + 4 * P.span_rows;
+    __shared__ int s_ntot;
+    __shared__ int s_nrej[AP_WARPS], s_nnan[AP_WARPS];
     __shared__ ApPartial s_part[BPHOT_MAX_APER][AP_WARPS];
     __shared__ CrossList s_list[AP_WARPS];
 
@@ -461,19 +477,28 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? 6 : 
         int nsky_all = 0, nvalid = 0;
         if (!P.use_setsky) {
             // ---- P1: gather the annulus
-            if (tid == 0) s_nvalid = 0;
-            row_spans(g, rinsq, routsq, span, tid);
+            row_spans(g, rinsq, routsq, span, rowoff, tid);
             __syncthreads();
-            const int nsel = gather_rows<T>(P, stamp, g, rinsq, routsq, span, keys, &s_nvalid, warp, lane);
-            if (lane == 0) s_nsel[warp] = nsel;
+            if (warp == 0) {
+                const int tot = row_offsets(rowoff, g.ny, lane);
+                if (lane == 0) s_ntot = tot;
+            }
             __syncthreads();
+            const int2 cnt = gather_rows<T>(P, stamp, g, span, rowoff, keys, warp, lane);
+            const int wrej = warp_sum_int(cnt.x), wnan = warp_sum_int(cnt.y);
+            if (lane == 0) { s_nrej[warp] = wrej; s_nnan[warp] = wnan; }
+            __syncthreads();
+            int nrej = 0, nnan = 0;
 #pragma unroll
-            for (int w = 0; w < AP_WARPS; w++) nsky_all += s_nsel[w];
-            nvalid = s_nvalid < P.sort_cap ? s_nvalid : P.sort_cap;
-            if (nvalid > (int)P.sstride) nvalid = (int)P.sstride;
+            for (int w = 0; w < AP_WARPS; w++) { nrej += s_nrej[w]; nnan += s_nnan[w]; }
+            int nslots = s_ntot < P.sort_cap ? s_ntot : P.sort_cap;  // key slots in use (some hold +inf)
+            if (nslots > (int)P.sstride) nslots = (int)P.sstride;
+            nsky_all = s_ntot - nrej;       // aper.py:267 counts NaNs
+            nvalid = nsky_all - nnan;       // mmm.py:106 drops them
+            if (nvalid > nslots) nvalid = nslots;
             if (nsky_all < P.minsky) {  // aper.py:269-272
                 if (tid == 0) { P.nsky[s] = nsky_all; P.mmm_iter[s] = -2; }
-                __syncthreads();  // the counters are reset by the next star
+                __syncthreads();  // the tables are rewritten by the next star
                 continue;
             }
             // ---- P2: sort (mmm.py:119); the tail is padded with +inf; sorted keys go to the scratch row
@@ -483,7 +508,7 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? 6 : 
 #pragma unroll
                 for (int q = 0; q < K; q++) {
                     const int idx = q * AP_THREADS + tid;  // any bijection will do before sorting
-                    r[q] = idx < nvalid ? keys[idx] : KeyTraits<T>::inf();
+                    r[q] = idx < nslots ? keys[idx] : KeyTraits<T>::inf();
                 }
                 __syncthreads();
                 cta_sort_regs<T, K>(r, keys, tid);
@@ -498,8 +523,8 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? 6 : 
                 }
             } else {
                 int m = 2;
-                while (m < nvalid) m <<= 1;
-                for (int i = nvalid + tid; i < m; i += AP_THREADS) keys[i] = KeyTraits<T>::inf();
+                while (m < nslots) m <<= 1;
+                for (int i = nslots + tid; i < m; i += AP_THREADS) keys[i] = KeyTraits<T>::inf();
                 __syncthreads();
                 cta_bitonic_sort(keys, m, tid);
                 for (int i = tid; i < nvalid; i += AP_THREADS) dst[i] = keys[i];

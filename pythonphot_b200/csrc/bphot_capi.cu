@@ -282,7 +282,7 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     P.span_rows = (int)(2. * skyrad_out) + 4;
     const size_t es = esize(image_dtype);
     const size_t key_bytes = ((size_t)(K ? AP_THREADS * (K + 1) : need) * es + 15) & ~(size_t)15;
-    const size_t smem = key_bytes + (size_t)P.span_rows * 16;
+    const size_t smem = key_bytes + (size_t)P.span_rows * 20;  // keys | span[4*rows] | rowoff[rows]
     DevInfo d;
     int rc = dev_info(&d);
     if (rc) return rc;
