@@ -1,17 +1,17 @@
 // aper_kernel.cu -- concentric-aperture photometry + mmm sky (sm_100a).
 //
 // Replaces the per-star Python loop of PythonPhot/aper.py:217-417 and its callees
-// mmm.mmm (mmm.py:7-314) and pixwt.Pixwt (pixwt.py:8-235), in two launches per batch of stars.
+// mmm.mmm (mmm.py:7-314) and pixwt.Pixwt (pixwt.py:8-235), in three kernels.
 // Stage 1, one 128-thread CTA per star:
 //   P1  the four warps gather the sky-annulus pixels of the (2*skyrad_out+1)^2 stamp into shared
-//       memory, row by row, visiting only the two column spans of each row that can intersect
-//       the annulus (coalesced; aper.py:240-267);
+//       memory, row by row, visiting exactly the two column spans of each row that lie in the
+//       annulus (coalesced, every pixel has its own key slot; aper.py:240-267);
 //   P2  the keys are sorted (np.sort at mmm.py:119) by a bitonic network that lives in REGISTERS:
 //       each thread holds K consecutive keys, compare-exchanges between a thread's own keys are
 //       FMNMX pairs, exchanges inside a warp are shuffles, and only the 3 (K=32) stages that cross
-//       warps go through shared memory; the sorted vector goes to a global scratch row;
-//   P3  aperture sums: pixels are classified geometrically (inside / outside / crossed by the
-//       circle) and only crossed pixels go through pixwt, four lanes per pixel (one per side).
+//       warps go through shared memory; the sorted vector goes to a global scratch row.
+// Aperture sums, one WARP per star: pixels are classified geometrically (inside / outside / crossed
+// by the circle) and only crossed pixels go through pixwt, four lanes per pixel (one per side).
 // Stage 2, one WARP per star: the mmm clipping loop on the sorted row (32-way ballot searches in
 // place of the reference's index walk, fp64 range sums by warp shuffle), then flux / error /
 // magnitude (aper.py:383-403).
@@ -453,13 +453,10 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? 6 : 
     int* rowoff = span + 4 * P.span_rows;
     __shared__ int s_ntot;
     __shared__ int s_nrej[AP_WARPS], s_nnan[AP_WARPS];
-    __shared__ ApPartial s_part[BPHOT_MAX_APER][AP_WARPS];
-    __shared__ CrossList s_list[AP_WARPS];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const T* __restrict__ img = reinterpret_cast<const T*>(P.img);
     T* __restrict__ skeys = reinterpret_cast<T*>(P.skeys);
-    const int naper = P.naper;
     const double rinsq = P.skyrad_in * P.skyrad_in, routsq = P.skyrad_out * P.skyrad_out;
 
     for (int i = P.s0 + blockIdx.x; i < P.s0 + P.scount; i += gridDim.x) {
@@ -531,39 +528,43 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? 6 : 
             }
         }
 
-        // ---- P3: aperture sums, the four warps share each aperture's pixel box
+        if (tid == 0) { P.nsky[s] = nsky_all; P.mmm_iter[s] = nvalid; }
+        __syncthreads();  // keys / tables / counters are reused by the next star
+    }
+}
+
+// Aperture sums, one WARP per star (aper.py:310-380): no CTA-wide barrier, a small code footprint of its own, and
+// ~40 stars in flight per SM.  Leaves flux[s,k] = sum of weight*pixel and badflag[s,k] = raw flag bits for stage 2.
+template <typename T>
+__global__ void __launch_bounds__(AP_THREADS) aper_sums_kernel(const AperParams P) {
+    __shared__ CrossList s_list[AP_WARPS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const T* __restrict__ img = reinterpret_cast<const T*>(P.img);
+    const int naper = P.naper;
+    for (int i = blockIdx.x * AP_WARPS + warp; i < P.nstars; i += gridDim.x * AP_WARPS) {
+        const int s = P.order ? P.order[i] : i;
+        const double x = P.xc[s], y = P.yc[s];
+        if (!(x >= 0.5) || !(x <= P.ncol - 1.5) || !(y >= 0.5) || !(y <= P.nrow - 1.5)) continue;  // aper.py:209-210, flagged by stage 1
+        const StarGeom g = star_geom(P, x, y);
+        const T* __restrict__ stamp = img + g.origin;
         for (int k = 0; k < naper; k++) {
-            const double ap = P.apr[k];
-            if (g.edge >= ap) {  // aper.py:311
-                const ApPartial A = aperture_warp<T>(P, stamp, g, ap, warp, AP_WARPS, lane, &s_list[warp]);
-                if (lane == 0) s_part[k][warp] = A;
-            }
-        }
-        __syncthreads();
-        if (tid < naper) {
-            const int k = tid;
-            const size_t o = (size_t)s * naper + k;
             const double ap = P.apr[k];
             double total = 0.0;
             int flags = 0;
-            if (g.edge >= ap) {
+            if (g.edge >= ap) {  // aper.py:311
+                const ApPartial A = aperture_warp<T>(P, stamp, g, ap, 0, 1, lane, &s_list[warp]);
                 const double area = M_PI * ap * ap;
-                double sfull = 0.0, spart = 0.0, wpart = 0.0;
-                int nfull = 0, npart = 0;
-                for (int w = 0; w < AP_WARPS; w++) {
-                    const ApPartial& A = s_part[k][w];
-                    sfull = sfull + A.sfull; spart = spart + A.spart; wpart = wpart + A.wpart;
-                    nfull += A.nfull; npart += A.npart; flags |= A.flags;
-                }
-                total = sfull;
-                if (!P.exact && npart > 0) total = sfull + ((area - nfull) / wpart) * spart;  // aper.py:343-349
+                total = A.sfull;
+                if (!P.exact && A.npart > 0) total = A.sfull + ((area - A.nfull) / A.wpart) * A.spart;  // aper.py:343-349
+                flags = A.flags;
                 if (flags & 1) total = 0.0;  // fractn = 0 for the whole aperture, aper.py:366
             }
-            P.flux[o] = total;
-            P.badflag[o] = (uint8_t)flags;
+            if (lane == 0) {
+                const size_t o = (size_t)s * naper + k;
+                P.flux[o] = total;
+                P.badflag[o] = (uint8_t)flags;
+            }
         }
-        if (tid == 0) { P.nsky[s] = nsky_all; P.mmm_iter[s] = nvalid; }
-        __syncthreads();  // keys / s_part / counters are reused by the next star
     }
 }
 

@@ -318,6 +318,18 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
         rc = persistent_grid(aper_stage2_kernel<T>, AP_THREADS, 0, (P.scount + AP_WARPS - 1) / AP_WARPS, &grid2); \
         if (!rc) aper_stage2_kernel<T><<<grid2, AP_THREADS, 0, st>>>(P);                                          \
     } while (0)
+    {   // aperture sums of every star (independent of the sky): one launch, warp per star
+        int grida = 0;
+        const long long nb = ((long long)nstars + AP_WARPS - 1) / AP_WARPS;
+        if (image_dtype == BPHOT_F32) {
+            rc = persistent_grid(aper_sums_kernel<float>, AP_THREADS, 0, nb, &grida);
+            if (!rc) aper_sums_kernel<float><<<grida, AP_THREADS, 0, st>>>(P);
+        } else {
+            rc = persistent_grid(aper_sums_kernel<double>, AP_THREADS, 0, nb, &grida);
+            if (!rc) aper_sums_kernel<double><<<grida, AP_THREADS, 0, st>>>(P);
+        }
+        g_launches += 1;
+    }
     for (int s0 = 0; s0 < nstars && !rc; s0 += batch) {
         P.s0 = s0;
         P.scount = (nstars - s0) < batch ? (nstars - s0) : batch;
