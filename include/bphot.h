@@ -49,6 +49,14 @@ const char* bphot_last_error(void);
 int bphot_device_count(void);
 /* number of kernels this library has launched in this process (bench.py's gpu_launches) */
 long long bphot_launch_count(void);
+/*
+ * Measurement aid (bench.py's roofline): while enabled, every launch of the four hot kernels is bracketed by CUDA
+ * events on its own stream and the owning call synchronises before it returns.  bphot_profile(1) also clears the
+ * accumulators; returns the previous setting.  bphot_kernel_times fills ms[4] / launches[4] with the summed
+ * durations and launch counts of 0 aper_stage1 (gather + sort), 1 aper_sums, 2 aper_stage2 (mmm), 3 pkfit.
+ */
+int bphot_profile(int enable);
+int bphot_kernel_times(double* ms, long long* launches);
 
 /*
  * aper.aper(image, xc, yc, phpadu, apr, zeropoint, skyrad, badpix, setskyval, minsky,

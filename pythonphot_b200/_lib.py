@@ -27,6 +27,8 @@ _SIGNATURES = {
     "bphot_last_error": (C.c_char_p, []),
     "bphot_device_count": (C.c_int, []),
     "bphot_launch_count": (C.c_longlong, []),
+    "bphot_profile": (C.c_int, [_i]),
+    "bphot_kernel_times": (C.c_int, [_vp, _vp]),
     "bphot_aper_device": (C.c_int, [_vp, _i, _i, _i, _ll, _vp, _vp, _i, _d, _vp, _i, _d, _d, _d, _d, _d, _i, _vp, _i, _i,
                                     _d, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "bphot_aper_host": (C.c_int, [_vp, _i, _i, _i, _vp, _vp, _i, _d, _vp, _i, _d, _d, _d, _d, _d, _i, _vp, _i, _i,
@@ -82,6 +84,22 @@ def check(rc):
 
 def launch_count():
     return int(lib().bphot_launch_count())
+
+
+KERNEL_CLASSES = ("aper_stage1", "aper_sums", "aper_stage2", "pkfit")
+
+
+def profile(enable):
+    """Switch per-kernel event timing in the library on/off (see include/bphot.h)."""
+    return int(lib().bphot_profile(int(bool(enable))))
+
+
+def kernel_times():
+    """{kernel class: (summed ms, launches)} accumulated since profile(True)."""
+    ms = (C.c_double * 4)()
+    n = (C.c_longlong * 4)()
+    check(lib().bphot_kernel_times(C.cast(ms, C.c_void_p), C.cast(n, C.c_void_p)))
+    return {k: (float(ms[i]), int(n[i])) for i, k in enumerate(KERNEL_CLASSES)}
 
 
 def torch_cuda():

@@ -23,6 +23,12 @@ namespace bphot {
 
 constexpr int AP_THREADS = 128;
 constexpr int AP_WARPS = AP_THREADS / 32;
+#ifndef AP_S1_CTAS
+#define AP_S1_CTAS 6  // resident stage-1 CTAs per SM the register budget is compiled for (K = 32, fp32 keys)
+#endif
+#ifndef AP_SUMS_CTAS
+#define AP_SUMS_CTAS 6
+#endif
 
 BP_D float kmin(float a, float b) { return fminf(a, b); }
 BP_D float kmax(float a, float b) { return fmaxf(a, b); }
@@ -297,22 +303,43 @@ BP_D int2 gather_rows(const AperParams& P, const T* __restrict__ stamp, const St
                       T* __restrict__ keys, int warp, int lane) {
     int nrej = 0, nnan = 0;
     const bool window = P.badlo != P.badhi;
-    for (int r = warp; r < g.ny; r += AP_WARPS) {
-        const int4 sp = *reinterpret_cast<const int4*>(span + 4 * r);
-        const int a0 = sp.x, b0 = sp.y, b1 = sp.z, a1 = sp.w;
-        const int nl = b0 - a0, tot = nl + (a1 - b1);
-        const int off = rowoff[r];
-        const T* __restrict__ row = stamp + (size_t)r * P.pitch;
-        for (int t = lane; t < tot; t += 32) {
-            const int c = t < nl ? a0 + t : b1 + 1 + (t - nl);
-            const T val = row[c];
-            const double dv = (double)val;
-            const bool rej = window && (dv < P.badlo || dv > P.badhi);
-            const bool isnan_ = !rej && !(val == val);
-            nrej += rej;
-            nnan += isnan_;
-            const int idx = off + t;
-            if (idx < P.sort_cap) keys[idx] = (rej || isnan_) ? KeyTraits<T>::inf() : val;
+    constexpr int U = 4;  // rows in flight per warp: U independent loads per lane before the first use
+    for (int r0 = warp; r0 < g.ny; r0 += U * AP_WARPS) {
+        int a0[U], nl[U], skip[U], tot[U], off[U];
+        const T* __restrict__ row[U];
+        int maxtot = 0;
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int r = r0 + u * AP_WARPS;
+            tot[u] = 0;
+            if (r < g.ny) {
+                const int4 sp = *reinterpret_cast<const int4*>(span + 4 * r);
+                a0[u] = sp.x;
+                nl[u] = sp.y - sp.x;
+                skip[u] = sp.z + 1 - sp.y;  // width of the excluded inner span
+                tot[u] = nl[u] + (sp.w - sp.z);
+                off[u] = rowoff[r];
+                row[u] = stamp + (size_t)r * P.pitch;
+            }
+            maxtot = tot[u] > maxtot ? tot[u] : maxtot;
+        }
+        for (int t = lane; t < maxtot; t += 32) {
+            T val[U];
+#pragma unroll
+            for (int u = 0; u < U; u++)
+                if (t < tot[u]) val[u] = row[u][a0[u] + t + (t < nl[u] ? 0 : skip[u])];
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                if (t < tot[u]) {
+                    const double dv = (double)val[u];
+                    const bool rej = window && (dv < P.badlo || dv > P.badhi);
+                    const bool isnan_ = !rej && !(val[u] == val[u]);
+                    nrej += rej;
+                    nnan += isnan_;
+                    const int idx = off[u] + t;
+                    if (idx < P.sort_cap) keys[idx] = (rej || isnan_) ? KeyTraits<T>::inf() : val[u];
+                }
+            }
         }
     }
     return make_int2(nrej, nnan);
@@ -445,7 +472,7 @@ BP_D ApPartial aperture_warp(const AperParams& P, const T* __restrict__ stamp, c
 
 // K > 0: register sort of 128*K keys (P.sort_cap == 128*K).  K == 0: shared-memory sort of P.sort_cap keys.
 template <typename T, int K>
-__global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? 6 : 1) aper_stage1_kernel(const AperParams P) {
+__global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S1_CTAS : 1) aper_stage1_kernel(const AperParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* keys = reinterpret_cast<T*>(smem_raw);
     const size_t key_bytes = ((size_t)(K > 0 ? AP_THREADS * (K + 1) : P.sort_cap) * sizeof(T) + 15) & ~(size_t)15;
@@ -536,7 +563,7 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? 6 : 
 // Aperture sums, one WARP per star (aper.py:310-380): no CTA-wide barrier, a small code footprint of its own, and
 // ~40 stars in flight per SM.  Leaves flux[s,k] = sum of weight*pixel and badflag[s,k] = raw flag bits for stage 2.
 template <typename T>
-__global__ void __launch_bounds__(AP_THREADS) aper_sums_kernel(const AperParams P) {
+__global__ void __launch_bounds__(AP_THREADS, AP_SUMS_CTAS) aper_sums_kernel(const AperParams P) {
     __shared__ CrossList s_list[AP_WARPS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const T* __restrict__ img = reinterpret_cast<const T*>(P.img);

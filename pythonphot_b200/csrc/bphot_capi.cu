@@ -21,6 +21,45 @@ namespace {
 thread_local char g_err[512] = "";
 std::atomic<long long> g_launches{0};
 
+// Optional per-kernel timing (bphot_profile / bphot_kernel_times): CUDA events recorded on the launch stream around
+// each launch of the four hot kernels; the call that owns them synchronises the stream before returning.
+enum { KT_APER_STAGE1 = 0, KT_APER_SUMS = 1, KT_APER_STAGE2 = 2, KT_PKFIT = 3, KT_N = 4 };
+std::atomic<int> g_profile{0};
+double g_kt_ms[KT_N] = {0, 0, 0, 0};
+long long g_kt_n[KT_N] = {0, 0, 0, 0};
+struct LaunchTimer {
+    struct Rec { cudaEvent_t a, b; int cls; };
+    Rec recs[64];
+    int n = 0;
+    cudaStream_t st;
+    bool on;
+    explicit LaunchTimer(cudaStream_t s) : st(s), on(g_profile.load() != 0) {}
+    void begin(int cls) {
+        if (!on) return;
+        if (n == 64) flush();
+        Rec& r = recs[n];
+        r.cls = cls;
+        cudaEventCreate(&r.a); cudaEventCreate(&r.b);
+        cudaEventRecord(r.a, st);
+    }
+    void end() {
+        if (!on) return;
+        cudaEventRecord(recs[n].b, st);
+        n++;
+    }
+    void flush() {
+        if (!on || n == 0) return;
+        cudaStreamSynchronize(st);
+        for (int i = 0; i < n; i++) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, recs[i].a, recs[i].b) == cudaSuccess) { g_kt_ms[recs[i].cls] += ms; g_kt_n[recs[i].cls] += 1; }
+            cudaEventDestroy(recs[i].a); cudaEventDestroy(recs[i].b);
+        }
+        n = 0;
+    }
+    ~LaunchTimer() { flush(); }
+};
+
 int fail(int code, const char* fmt, ...) {
     va_list ap;
     va_start(ap, fmt);
@@ -41,7 +80,13 @@ int next_pow2(long long v) {
     return m;
 }
 
-constexpr int APER_BATCH = 65536;  // stars per stage-1 / stage-2 launch pair (scratch = batch * ~13 KB)
+#ifndef AP_BATCH
+#define AP_BATCH 65536
+#endif
+#ifndef AP_S2_CTAS
+#define AP_S2_CTAS 0  // 0 = as many stage-2 CTAs per SM as fit
+#endif
+constexpr int APER_BATCH = AP_BATCH;  // stars per stage-1 / stage-2 launch pair (scratch = batch * ~13 KB)
 
 struct DevInfo {
     int sms;
@@ -218,6 +263,21 @@ void find_constants(double fwhm, bphot::FindConsts* K) {
     K->pixels = pixels - 1;
 }
 
+// the log10 table of bphot_math.cuh is filled once per device, on the caller's stream before the first mmm launch
+int ensure_log10_table(cudaStream_t st) {
+    static std::atomic<unsigned long long> done{0};
+    int dev = 0;
+    CU_TRY(cudaGetDevice(&dev));
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (done.load() & bit) return 0;
+    bphot::log10_table_kernel<<<8, 256, 0, st>>>();
+    CU_TRY(cudaGetLastError());
+    CU_TRY(cudaStreamSynchronize(st));  // other streams may launch mmm right after this call returns
+    done.fetch_or(bit);
+    g_launches += 1;
+    return 0;
+}
+
 struct DevBuf {  // frees on scope exit
     void* p = nullptr;
     ~DevBuf() { if (p) cudaFree(p); }
@@ -232,6 +292,17 @@ extern "C" {
 int bphot_version(void) { return BPHOT_VERSION; }
 const char* bphot_last_error(void) { return g_err; }
 long long bphot_launch_count(void) { return g_launches.load(); }
+
+int bphot_profile(int enable) {
+    const int prev = g_profile.exchange(enable ? 1 : 0);
+    if (enable) for (int k = 0; k < KT_N; k++) { g_kt_ms[k] = 0.; g_kt_n[k] = 0; }
+    return prev;
+}
+int bphot_kernel_times(double* ms, long long* launches) {
+    if (!ms || !launches) return fail(BPHOT_ERR_ARG, "bphot_kernel_times: null pointer");
+    for (int k = 0; k < KT_N; k++) { ms[k] = g_kt_ms[k]; launches[k] = g_kt_n[k]; }
+    return BPHOT_OK;
+}
 
 int bphot_device_count(void) {
     int n = 0;
@@ -293,6 +364,8 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     P.sstride = (bound + 7) / 8 * 8;
     const int batch = nstars < APER_BATCH ? nstars : APER_BATCH;
     cudaStream_t st = (cudaStream_t)stream;
+    rc = ensure_log10_table(st);
+    if (rc) return rc;
     void* scratch = nullptr;
     if (!use_setsky) CU_TRY(cudaMallocAsync(&scratch, (size_t)batch * P.sstride * es, st));
     P.skeys = scratch;
@@ -301,6 +374,7 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     if (rc) return rc;
     P.order = ord.order;
     int grid1 = 0, grid2 = 0;
+    LaunchTimer lt(st);
 #define BP_STAGE1(T, KK)                                                                          \
     do {                                                                                          \
         rc = persistent_grid(aper_stage1_kernel<T, KK>, AP_THREADS, smem, P.scount, &grid1);      \
@@ -316,11 +390,13 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
 #define BP_STAGE2(T)                                                                                              \
     do {                                                                                                          \
         rc = persistent_grid(aper_stage2_kernel<T>, AP_THREADS, 0, (P.scount + AP_WARPS - 1) / AP_WARPS, &grid2); \
+        if (!rc && AP_S2_CTAS > 0 && grid2 > AP_S2_CTAS * d.sms) grid2 = AP_S2_CTAS * d.sms;                      \
         if (!rc) aper_stage2_kernel<T><<<grid2, AP_THREADS, 0, st>>>(P);                                          \
     } while (0)
     {   // aperture sums of every star (independent of the sky): one launch, warp per star
         int grida = 0;
         const long long nb = ((long long)nstars + AP_WARPS - 1) / AP_WARPS;
+        lt.begin(KT_APER_SUMS);
         if (image_dtype == BPHOT_F32) {
             rc = persistent_grid(aper_sums_kernel<float>, AP_THREADS, 0, nb, &grida);
             if (!rc) aper_sums_kernel<float><<<grida, AP_THREADS, 0, st>>>(P);
@@ -328,21 +404,27 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
             rc = persistent_grid(aper_sums_kernel<double>, AP_THREADS, 0, nb, &grida);
             if (!rc) aper_sums_kernel<double><<<grida, AP_THREADS, 0, st>>>(P);
         }
+        lt.end();
         g_launches += 1;
     }
     for (int s0 = 0; s0 < nstars && !rc; s0 += batch) {
         P.s0 = s0;
         P.scount = (nstars - s0) < batch ? (nstars - s0) : batch;
+        lt.begin(KT_APER_STAGE1);
         if (image_dtype == BPHOT_F32) BP_STAGE1_K(float);
         else BP_STAGE1_K(double);
+        lt.end();
         if (rc) break;
+        lt.begin(KT_APER_STAGE2);
         if (image_dtype == BPHOT_F32) BP_STAGE2(float);
         else BP_STAGE2(double);
+        lt.end();
         g_launches += 2;
     }
 #undef BP_STAGE2
 #undef BP_STAGE1_K
 #undef BP_STAGE1
+    lt.flush();
     if (scratch) cudaFreeAsync(scratch, st);
     ord.release(st);
     if (rc) return rc;
@@ -402,6 +484,8 @@ int bphot_pkfit_device(int variant, const void* d_image, int image_dtype,
     rc = make_star_order(d_x, d_y, nstars, nrow, ncol, st, &ord);
     if (rc) return rc;
     P.order = ord.order;
+    LaunchTimer lt(st);
+    lt.begin(KT_PKFIT);
 #define BP_LAUNCH(V, TI, TN)                                                              \
     do {                                                                                  \
         rc = persistent_grid(pkfit_kernel<V, TI, TN>, PK_THREADS, smem, nblocks, &grid);  \
@@ -422,6 +506,8 @@ int bphot_pkfit_device(int variant, const void* d_image, int image_dtype,
     else BP_LAUNCH_T(2);
 #undef BP_LAUNCH_T
 #undef BP_LAUNCH
+    lt.end();
+    lt.flush();
     ord.release(st);
     g_launches++;
     CU_TRY(cudaGetLastError());
@@ -444,6 +530,8 @@ int bphot_mmm_device(const void* d_vec, int dtype, const long long* d_offs, int 
     if (smem + 1024 > (size_t)d.smem_optin) return fail(BPHOT_ERR_CAPACITY, "bphot_mmm: vector of %d elements exceeds shared memory", max_len);
     int grid = 0;
     cudaStream_t st = (cudaStream_t)stream;
+    rc = ensure_log10_table(st);
+    if (rc) return rc;
 #define BP_LAUNCH_MMM(T, KK)                                                                                         \
     do {                                                                                                             \
         rc = persistent_grid(mmm_kernel<T, KK>, AP_THREADS, smem, nvec, &grid);                                      \

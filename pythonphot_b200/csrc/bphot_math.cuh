@@ -365,6 +365,23 @@ BP_HD int mmm_walk_max(const Get& at, const First& first, int nsky, int maximm, 
 // The functors let a whole warp share the reductions on the device (every lane must receive the same
 // bits) and a plain loop stand in on the host (tests/hostcheck).  Failure modes keep the reference's
 // in-band codes (sigma = -1).
+// log10 of a pixel count (mmm.py:186).  Every lane of the mmm warp evaluates it with the same argument once per
+// clipping iteration (~100 fp64 instructions each time, 13 % of stage 2), so the device reads it from a table that
+// log10_table_kernel fills with the very same libm call: identical bits, one L1 hit.
+constexpr int MMM_LOG10_TAB = 8192;
+#if defined(__CUDACC__)
+__device__ double g_log10_tab[MMM_LOG10_TAB + 1];
+__global__ void log10_table_kernel() {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i <= MMM_LOG10_TAB; i += gridDim.x * blockDim.x) g_log10_tab[i] = log10((double)i);
+}
+#endif
+BP_HD double mmm_log10n(int n) {
+#if defined(__CUDA_ARCH__)
+    if (n >= 0 && n <= MMM_LOG10_TAB) return g_log10_tab[n];
+#endif
+    return log10((double)n);
+}
+
 struct MmmResult {
     double skymod, sigma, skew;
     int iters;
@@ -414,7 +431,7 @@ BP_HD MmmResult mmm_sorted(const Get& at, const DSums& delta_sums, const PSum& p
             R.skymod = skymod; R.sigma = -1.0; R.iters = niter;
             return R;
         }
-        double r = log10((double)(maximm - minimm));  // mmm.py:186-187
+        double r = mmm_log10n(maximm - minimm);  // mmm.py:186-187
         const double r2 = (-0.1042 * r + 1.1695) * r + 0.8895;
         r = 2. > r2 ? 2. : r2;
         const double cut = r * sigma + 0.5 * fabs(skymn - skymod);  // mmm.py:191-193
