@@ -190,6 +190,21 @@ def to_device_f64(a, device, n=None):
     return t.contiguous()
 
 
+def to_host(tensors):
+    """CUDA tensors -> numpy arrays through page-locked memory: the copies are queued back to back on the current
+    stream (full PCIe rate, ~20x a pageable ``.cpu()``) and synchronised once.  The arrays own their buffers: each
+    is backed by a pinned block from torch's caching host allocator, which takes the block back when the array dies."""
+    torch = torch_cuda()
+    hosts = []
+    for t in tensors:
+        h = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+        h.copy_(t, non_blocking=True)
+        hosts.append(h)
+    if tensors:
+        torch.cuda.current_stream(tensors[0].device).synchronize()
+    return [h.numpy() for h in hosts]
+
+
 def host_f64(a):
     return np.ascontiguousarray(np.atleast_1d(np.asarray(a, dtype=np.float64)).reshape(-1))
 

@@ -86,8 +86,8 @@ class PkfitEngine(object):
             cols += ["chi2"]
         # one device->host transfer for the fp64 columns
         f64cols = [c for c in cols if c != "niter"]
-        packed = torch.stack([o[c] for c in f64cols]).cpu().numpy()
-        niter = o["niter"].cpu().numpy()
+        with torch.cuda.device(dev):
+            packed, niter = _lib.to_host([torch.stack([o[c] for c in f64cols]), o["niter"]])
         res = []
         for c in cols:
             a = niter if c == "niter" else packed[f64cols.index(c)]

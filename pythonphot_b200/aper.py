@@ -118,7 +118,8 @@ def aper(image, xc, yc, phpadu=1, apr=5, zeropoint=25,
     o = aper_device(img_t, xc_t, yc_t, phpadu=phpadu, apr=apr, zeropoint=zeropoint, skyrad=skyrad, badpix=badpix,
                     setskyval=setskyval, minsky=_minsky_value(minsky), exact=exact, readnoise=readnoise,
                     compat=compat)
-    h = {k: v.cpu().numpy() for k, v in o.items()}
+    with torch.cuda.device(dev):
+        h = dict(zip(o.keys(), _lib.to_host(list(o.values()))))
     mag, magerr, flux, fluxerr = h['mag'], h['magerr'], h['flux'], h['fluxerr']
     sky, skyerr = h['sky'], h['skyerr']
     badflag = h['badflag'].astype(np.float64)  # the reference stores 0./1. (aper.py:174)

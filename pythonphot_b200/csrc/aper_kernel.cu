@@ -26,6 +26,9 @@ constexpr int AP_WARPS = AP_THREADS / 32;
 #ifndef AP_S1_CTAS
 #define AP_S1_CTAS 6  // resident stage-1 CTAs per SM the register budget is compiled for (K = 32, fp32 keys)
 #endif
+#ifndef AP_S2_MINB
+#define AP_S2_MINB 1  // minimum resident stage-2 CTAs per SM the register budget is compiled for
+#endif
 #ifndef AP_SUMS_CTAS
 #define AP_SUMS_CTAS 6
 #endif
@@ -597,7 +600,7 @@ __global__ void __launch_bounds__(AP_THREADS, AP_SUMS_CTAS) aper_sums_kernel(con
 
 // Stage 2: one warp per star -- mmm on the sorted scratch row, then aper.py:290-300, 383-403.
 template <typename T>
-__global__ void __launch_bounds__(AP_THREADS) aper_stage2_kernel(const AperParams P) {
+__global__ void __launch_bounds__(AP_THREADS, AP_S2_MINB) aper_stage2_kernel(const AperParams P) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int naper = P.naper;
     const T* __restrict__ skeys = reinterpret_cast<const T*>(P.skeys);

@@ -71,7 +71,8 @@ def find(image,
         print(' No. of sources rejected by CENTROID  criteria', cnt["badcntrd"])
     if cnt["nstars"] == 0:
         return None  # find.py:373
-    h = cols.cpu().numpy()
+    with torch.cuda.device(dev):
+        h = _lib.to_host([cols.contiguous()])[0]
     x, y, flux, sharp, roundness = (np.ascontiguousarray(h[i]) for i in range(5))
     if doprint:
         import time
