@@ -47,15 +47,26 @@ BP_HD double pw_oneside(double x, double y0, double y1, double r) {
     const bool has_a1 = (z0 != 1);                // leading arc starts at y0
     const bool has_a2 = (z1 != 1) && (z1 != z0);  // trailing arc ends at y1
     const bool has_c = !(z0 == z1 && z0 != 1);    // chord between them
+    // Arc end points.  Most calls need no arc or exactly one (leading OR trailing); both only when the unit segment
+    // spans the whole chord (2*yh < 1, near tangency).  A warp runs a call site if ANY lane needs it, so the arcs go
+    // through a PRIMARY site (the leading arc if there is one, else the trailing one) and a rarely taken SECONDARY
+    // site (trailing arc when both exist): half the fp64 atan work of two always-taken sites, same values, same
+    // left-to-right order of addition.
+    const double a1_end = (z1 == z0) ? y1 : (z0 == 0 ? -yh : yh);
+    const double a2_beg = (z1 == 2) ? yh : -yh;
+    const bool any_arc = has_a1 || has_a2;
+    double prim = 0.0, sec = 0.0;
+    if (any_arc) prim = pw_arc(x, has_a1 ? y0 : a2_beg, has_a1 ? a1_end : y1, r);
+    if (has_a1 && has_a2) sec = pw_arc(x, a2_beg, y1, r);
     double res = 0.0;
-    if (has_a1) res = pw_arc(x, y0, (z1 == z0) ? y1 : (z0 == 0 ? -yh : yh), r);
+    if (has_a1) res = prim;
     if (has_c) {
         const double cs = (z0 == 1) ? y0 : (z0 == 0 ? -yh : yh);
         const double ce = (z1 == 1) ? y1 : (z1 == 2 ? yh : -yh);
         const double ch = pw_chord(x, cs, ce);
         res = has_a1 ? res + ch : ch;
     }
-    if (has_a2) res = res + pw_arc(x, (z1 == 2) ? yh : -yh, y1, r);
+    if (has_a2) res = res + (has_a1 ? sec : prim);
     return res;
 }
 
