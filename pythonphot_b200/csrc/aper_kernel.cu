@@ -598,70 +598,84 @@ __global__ void __launch_bounds__(AP_THREADS, AP_SUMS_CTAS) aper_sums_kernel(con
     }
 }
 
-// Stage 2: one warp per star -- mmm on the sorted scratch row, then aper.py:290-300, 383-403.
+// Stage 2: one warp per star -- mmm on the sorted scratch row (aper.py:288).  Writes the per-star sky columns only:
+// sky = skymod, skyerr = mmm's sigma UNCLAMPED (aper_finalize_kernel needs it for skyvar and clamps it afterwards),
+// nsky, mmm_iter.  The per-aperture columns belong to aper_sums_kernel (raw sums, possibly running concurrently on
+// another stream) and aper_finalize_kernel.
 template <typename T>
 __global__ void __launch_bounds__(AP_THREADS, AP_S2_MINB) aper_stage2_kernel(const AperParams P) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int naper = P.naper;
     const T* __restrict__ skeys = reinterpret_cast<const T*>(P.skeys);
     for (int i = P.s0 + blockIdx.x * AP_WARPS + warp; i < P.s0 + P.scount; i += gridDim.x * AP_WARPS) {
         const int s = P.order ? P.order[i] : i;
         const int status = P.mmm_iter[s], nsky_all = P.nsky[s];
-        auto write_bad = [&](double skyv, double skyerrv, int nskyv, int iters) {
-            if (lane < naper) {
-                const size_t o = (size_t)s * naper + lane;
-                P.mag[o] = nan64(); P.magerr[o] = nan64(); P.flux[o] = nan64(); P.fluxerr[o] = nan64();
-                P.badflag[o] = 1;
-            }
-            if (lane == 0) { P.sky[s] = skyv; P.skyerr[s] = skyerrv; P.nsky[s] = nskyv; P.mmm_iter[s] = iters; }
-        };
-        if (status == -1) { write_bad(0.0, 0.0, 0, 0); continue; }          // aper.py:221-233
-        if (status == -2) { write_bad(0.0, 0.0, nsky_all, 0); continue; }  // aper.py:269-272
-        double skymod, skysig, skyvar, sigsq;
-        int iters = 0, nsky_out;
-        if (!P.use_setsky) {
+        double skymod = 0.0, skysig = 0.0;
+        int iters = 0, nsky_out = nsky_all;
+        if (status == -1) nsky_out = 0;   // star off the frame, aper.py:221-233: sky = skyerr = 0
+        else if (status == -2) {}         // nsky < minsky, aper.py:269-272: sky = skyerr = 0
+        else if (!P.use_setsky) {
             GlobalView<T> view;
             view.p = skeys + (size_t)(i - P.s0) * P.sstride;
-            const MmmResult R = mmm_warp(view, status, P.readnoise, P.minsky, P.mxiter, lane);  // aper.py:288
+            const MmmResult R = mmm_warp(view, status, P.readnoise, P.minsky, P.mxiter, lane);
             skymod = R.skymod; skysig = R.sigma; iters = R.iters;
-            skyvar = skysig * skysig;  // aper.py:290-291
-            sigsq = skyvar / nsky_all;
-            nsky_out = nsky_all;
-            if (skysig < 0.0) {  // aper.py:293-296, 411-412
-                write_bad(skymod, skysig, nsky_all, iters);
-                continue;
-            }
-            if (skysig > 999.99) skysig = 999;  // aper.py:298
         } else {  // aper.py:302-308
             skymod = P.setsky[0]; skysig = P.setsky[1];
-            skyvar = skysig * skysig;
-            sigsq = skyvar / P.setsky[2];
             nsky_out = (int)P.setsky[2];
         }
-        if (lane < naper) {
-            const StarGeom g = star_geom(P, P.xc[s], P.yc[s]);
-            const size_t o = (size_t)s * naper + lane;
-            const double ap = P.apr[lane];
-            if (!(g.edge >= ap)) {  // aper.py:311, 350-353
-                P.mag[o] = nan64(); P.magerr[o] = nan64(); P.flux[o] = nan64(); P.fluxerr[o] = nan64();
-                P.badflag[o] = 1;
-            } else {
-                const double area = M_PI * ap * ap;
-                const double apflux = P.flux[o] - skymod * area;  // aper.py:391
-                const double err = sqrt(area * skyvar + fabs(apflux) / P.phpadu + sigsq * (area * area));  // aper.py:394-397
-                P.flux[o] = apflux;
-                P.fluxerr[o] = err;
-                if (apflux > 0.0) {  // aper.py:399-403
-                    P.magerr[o] = 1.0857 * err / apflux;
-                    P.mag[o] = P.zeropoint - 2.5 * log10(apflux);
-                } else {
-                    P.magerr[o] = nan64();
-                    P.mag[o] = nan64();
+        if (lane == 0) { P.sky[s] = skymod; P.skyerr[s] = skysig; P.nsky[s] = nsky_out; P.mmm_iter[s] = iters; }
+    }
+}
+
+// Last step, one thread per star: sky-subtracted flux, error, magnitude and flags from the raw aperture sums and the
+// sky columns (aper.py:290-300, 383-403, 411-417).
+__global__ void __launch_bounds__(256) aper_finalize_kernel(const AperParams P) {
+    const int naper = P.naper;
+    for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < P.nstars; s += gridDim.x * blockDim.x) {
+        const double x = P.xc[s], y = P.yc[s];
+        const bool badstar = !(x >= 0.5) || !(x <= P.ncol - 1.5) || !(y >= 0.5) || !(y <= P.nrow - 1.5);  // aper.py:209-210
+        const double skymod = P.sky[s];
+        double skysig = P.skyerr[s];
+        bool bad = badstar;
+        double skyvar = 0.0, sigsq = 0.0;
+        if (!bad) {
+            if (!P.use_setsky) {
+                const int nsky_all = P.nsky[s];
+                if (nsky_all < P.minsky) bad = true;  // aper.py:269-272
+                else {
+                    skyvar = skysig * skysig;  // aper.py:290-291
+                    sigsq = skyvar / nsky_all;
+                    if (skysig < 0.0) bad = true;  // aper.py:293-296: sky and skyerr = -1 stay as mmm left them
+                    else if (skysig > 999.99) P.skyerr[s] = 999;  // aper.py:298
                 }
-                P.badflag[o] = P.badflag[o] ? 1 : 0;
+            } else {
+                skyvar = skysig * skysig;
+                sigsq = skyvar / P.setsky[2];
             }
         }
-        if (lane == 0) { P.sky[s] = skymod; P.skyerr[s] = skysig; P.nsky[s] = nsky_out; P.mmm_iter[s] = iters; }
+        StarGeom g;
+        if (!bad) g = star_geom(P, x, y);
+        for (int k = 0; k < naper; k++) {
+            const size_t o = (size_t)s * naper + k;
+            const double ap = P.apr[k];
+            if (bad || !(g.edge >= ap)) {  // aper.py:221-233, 311, 350-353
+                P.mag[o] = nan64(); P.magerr[o] = nan64(); P.flux[o] = nan64(); P.fluxerr[o] = nan64();
+                P.badflag[o] = 1;
+                continue;
+            }
+            const double area = M_PI * ap * ap;
+            const double apflux = P.flux[o] - skymod * area;  // aper.py:391
+            const double err = sqrt(area * skyvar + fabs(apflux) / P.phpadu + sigsq * (area * area));  // aper.py:394-397
+            P.flux[o] = apflux;
+            P.fluxerr[o] = err;
+            if (apflux > 0.0) {  // aper.py:399-403
+                P.magerr[o] = 1.0857 * err / apflux;
+                P.mag[o] = P.zeropoint - 2.5 * log10(apflux);
+            } else {
+                P.magerr[o] = nan64();
+                P.mag[o] = nan64();
+            }
+            P.badflag[o] = P.badflag[o] ? 1 : 0;
+        }
     }
 }
 

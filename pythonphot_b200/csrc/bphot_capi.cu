@@ -23,10 +23,10 @@ std::atomic<long long> g_launches{0};
 
 // Optional per-kernel timing (bphot_profile / bphot_kernel_times): CUDA events recorded on the launch stream around
 // each launch of the four hot kernels; the call that owns them synchronises the stream before returning.
-enum { KT_APER_STAGE1 = 0, KT_APER_SUMS = 1, KT_APER_STAGE2 = 2, KT_PKFIT = 3, KT_N = 4 };
+enum { KT_APER_STAGE1 = 0, KT_APER_SUMS = 1, KT_APER_STAGE2 = 2, KT_PKFIT = 3, KT_APER_FINAL = 4, KT_N = 5 };
 std::atomic<int> g_profile{0};
-double g_kt_ms[KT_N] = {0, 0, 0, 0};
-long long g_kt_n[KT_N] = {0, 0, 0, 0};
+double g_kt_ms[KT_N] = {0, 0, 0, 0, 0};
+long long g_kt_n[KT_N] = {0, 0, 0, 0, 0};
 struct LaunchTimer {
     struct Rec { cudaEvent_t a, b; int cls; };
     Rec recs[64];
@@ -82,6 +82,12 @@ int next_pow2(long long v) {
 
 #ifndef AP_BATCH
 #define AP_BATCH 65536
+#endif
+#ifndef AP_SIDE_STREAM
+#define AP_SIDE_STREAM 0  // measured: co-running aper_sums with stage 1/2 does not pay; kept as a build knob
+#endif
+#ifndef AP_SUMS_SIDE_CTAS
+#define AP_SUMS_SIDE_CTAS 2  // CTAs per SM of the aperture-sum kernel while it shares the SMs with stage 1 / stage 2 (0 = no cap)
 #endif
 #ifndef AP_S2_CTAS
 #define AP_S2_CTAS 0  // 0 = as many stage-2 CTAs per SM as fit
@@ -263,6 +269,23 @@ void find_constants(double fwhm, bphot::FindConsts* K) {
     K->pixels = pixels - 1;
 }
 
+// one non-blocking side stream per device, created on first use and kept for the life of the process
+int side_stream(cudaStream_t* out) {
+    static std::atomic<cudaStream_t> streams[64];
+    int dev = 0;
+    CU_TRY(cudaGetDevice(&dev));
+    cudaStream_t s = streams[dev & 63].load();
+    if (!s) {
+        cudaStream_t created = nullptr;
+        CU_TRY(cudaStreamCreateWithFlags(&created, cudaStreamNonBlocking));
+        cudaStream_t expected = nullptr;
+        if (streams[dev & 63].compare_exchange_strong(expected, created)) s = created;
+        else { cudaStreamDestroy(created); s = expected; }
+    }
+    *out = s;
+    return 0;
+}
+
 // the log10 table of bphot_math.cuh is filled once per device, on the caller's stream before the first mmm launch
 int ensure_log10_table(cudaStream_t st) {
     static std::atomic<unsigned long long> done{0};
@@ -300,7 +323,7 @@ int bphot_profile(int enable) {
 }
 int bphot_kernel_times(double* ms, long long* launches) {
     if (!ms || !launches) return fail(BPHOT_ERR_ARG, "bphot_kernel_times: null pointer");
-    for (int k = 0; k < KT_N; k++) { ms[k] = g_kt_ms[k]; launches[k] = g_kt_n[k]; }
+    for (int k = 0; k < 4; k++) { ms[k] = g_kt_ms[k]; launches[k] = g_kt_n[k]; }  // the finalize kernel is not reported
     return BPHOT_OK;
 }
 
@@ -393,19 +416,37 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
         if (!rc && AP_S2_CTAS > 0 && grid2 > AP_S2_CTAS * d.sms) grid2 = AP_S2_CTAS * d.sms;                      \
         if (!rc) aper_stage2_kernel<T><<<grid2, AP_THREADS, 0, st>>>(P);                                          \
     } while (0)
-    {   // aperture sums of every star (independent of the sky): one launch, warp per star
+    // Aperture sums of every star (independent of the sky): one launch, warp per star.  The kernel is bound by the
+    // fp64 pipe (atan in pixwt) while stage 1 is bound by integer/fp32 issue and shuffles, so it runs on a side stream,
+    // concurrently with the stage-1 / stage-2 batches, on a few CTAs per SM; the finalize kernel joins the two.
+    // While per-kernel timing is on (bphot_profile) everything stays on the caller's stream, one kernel at a time.
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    if (AP_SIDE_STREAM && !lt.on && nstars >= ORDER_MIN_STARS) {
+        rc = side_stream(&side);
+        if (rc) { if (scratch) cudaFreeAsync(scratch, st); ord.release(st); return rc; }
+        cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming);
+        cudaEventRecord(ev_fork, st);
+        cudaStreamWaitEvent(side, ev_fork, 0);
+    }
+    {
         int grida = 0;
         const long long nb = ((long long)nstars + AP_WARPS - 1) / AP_WARPS;
+        cudaStream_t sa = side ? side : st;
         lt.begin(KT_APER_SUMS);
         if (image_dtype == BPHOT_F32) {
             rc = persistent_grid(aper_sums_kernel<float>, AP_THREADS, 0, nb, &grida);
-            if (!rc) aper_sums_kernel<float><<<grida, AP_THREADS, 0, st>>>(P);
+            if (!rc && side && AP_SUMS_SIDE_CTAS > 0 && grida > AP_SUMS_SIDE_CTAS * d.sms) grida = AP_SUMS_SIDE_CTAS * d.sms;
+            if (!rc) aper_sums_kernel<float><<<grida, AP_THREADS, 0, sa>>>(P);
         } else {
             rc = persistent_grid(aper_sums_kernel<double>, AP_THREADS, 0, nb, &grida);
-            if (!rc) aper_sums_kernel<double><<<grida, AP_THREADS, 0, st>>>(P);
+            if (!rc && side && AP_SUMS_SIDE_CTAS > 0 && grida > AP_SUMS_SIDE_CTAS * d.sms) grida = AP_SUMS_SIDE_CTAS * d.sms;
+            if (!rc) aper_sums_kernel<double><<<grida, AP_THREADS, 0, sa>>>(P);
         }
         lt.end();
         g_launches += 1;
+        if (side) cudaEventRecord(ev_join, side);
     }
     for (int s0 = 0; s0 < nstars && !rc; s0 += batch) {
         P.s0 = s0;
@@ -424,6 +465,19 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
 #undef BP_STAGE2
 #undef BP_STAGE1_K
 #undef BP_STAGE1
+    if (side) {
+        cudaStreamWaitEvent(st, ev_join, 0);
+        cudaEventDestroy(ev_fork);
+        cudaEventDestroy(ev_join);
+    }
+    if (!rc) {
+        int gf = (nstars + 255) / 256;
+        if (gf > d.sms * 8) gf = d.sms * 8;
+        lt.begin(KT_APER_FINAL);
+        aper_finalize_kernel<<<gf, 256, 0, st>>>(P);
+        lt.end();
+        g_launches += 1;
+    }
     lt.flush();
     if (scratch) cudaFreeAsync(scratch, st);
     ord.release(st);
