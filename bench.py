@@ -309,6 +309,13 @@ def main():
         ms_total, ms_aper, ms_fit, ms_gather = (float(v) for v in tt.tolist())
     ms_step = ms_total / a.steps
     value = world * n / (ms_step * 1e-3)
+    per_rank = None
+    if world > 1:  # each rank's own stage times (load balance of the shards)
+        mine = torch.tensor([float(np.mean([e[0].elapsed_time(e[1]) for e in evs])) if do_aper else 0.0,
+                             float(np.mean([e[2].elapsed_time(e[3]) for e in evs])) if do_fit else 0.0], dtype=torch.float64, device=dev)
+        allr = torch.empty((world, 2), dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(allr, mine)
+        per_rank = {"aper_ms": [round(v, 2) for v in allr[:, 0].tolist()], "pkfit_ms": [round(v, 2) for v in allr[:, 1].tolist()]}
 
     # ---- one extra, untimed-for-`value` pass with the library's own CUDA events around every kernel launch (on the launch
     # stream): per-kernel average launch durations for the roofline
@@ -382,6 +389,7 @@ def main():
                                "mean_niter": float(nit.double().mean().item()),
                                "frac_niter_25": float((nit == 25).double().mean().item())}
         if world > 1:
+            stages["per_rank"] = per_rank
             stages["gather"] = {"ms": ms_gather, "what": "pack per dtype + NCCL all-gather + un-permute of the per-star records"}
         # per-kernel algorithmic bytes per star: the shares of SURVEY 8d's per-star figures that each kernel moves
         es = img_t.element_size()

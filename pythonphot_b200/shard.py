@@ -83,8 +83,16 @@ class ShardPlan(object):
         return self._dev[key]
 
     @classmethod
-    def for_stars(cls, x, y, nrow, ncol, world):
-        return cls(len(x), world, morton_order(x, y, nrow, ncol))
+    def for_stars(cls, x, y, nrow, ncol, world, chunk=4096):
+        """Tile-ordered stars dealt to the ranks in chunks of ``chunk`` consecutive stars (chunk c -> rank c mod world):
+        a chunk keeps the L2 locality of its image tiles, and every rank sees the same mix of crowded, sparse and
+        frame-edge regions, so per-rank run times stay level (one contiguous Morton patch per rank measured 20 % apart
+        on 8 GPUs)."""
+        perm = morton_order(x, y, nrow, ncol)
+        if world > 1 and chunk > 0:
+            owner = (np.arange(perm.size) // chunk) % world
+            perm = perm[np.argsort(owner, kind="stable")]
+        return cls(len(x), world, perm)
 
     def indices(self, rank):
         """Star indices (into the caller's list) of ``rank``'s shard, padding included."""
