@@ -27,7 +27,7 @@ constexpr int AP_WARPS = AP_THREADS / 32;
 #define AP_S1_CTAS 6  // resident stage-1 CTAs per SM the register budget is compiled for (K = 32, fp32 keys)
 #endif
 #ifndef AP_S2_MINB
-#define AP_S2_MINB 1  // minimum resident stage-2 CTAs per SM the register budget is compiled for
+#define AP_S2_MINB 9  // minimum resident stage-2 CTAs per SM the register budget is compiled for
 #endif
 #ifndef AP_SUMS_CTAS
 #define AP_SUMS_CTAS 6

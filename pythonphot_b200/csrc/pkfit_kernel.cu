@@ -23,6 +23,22 @@
 
 namespace bphot {
 
+// Out-of-line warp reductions for the fit kernels (PK_NOINLINE_SUMS=1): ~45 inlined fp64 butterfly reductions were a
+// third of the kernel's 80 KB of code and the fit warps stalled on instruction fetch.
+#ifndef PK_NOINLINE_SUMS
+#define PK_NOINLINE_SUMS 0
+#endif
+#if PK_NOINLINE_SUMS
+__device__ __noinline__ double pk_sum(double v) { return warp_sum(v); }
+__device__ __noinline__ double pk_min(double v) { return warp_min(v); }
+__device__ __noinline__ double pk_max(double v) { return warp_max(v); }
+#else
+BP_D double pk_sum(double v) { return warp_sum(v); }
+BP_D double pk_min(double v) { return warp_min(v); }
+BP_D double pk_max(double v) { return warp_max(v); }
+#endif
+
+
 constexpr int PK_WARPS = 4;
 constexpr int PK_THREADS = PK_WARPS * 32;
 constexpr int PK_NARR_FIT = 10;     // per-warp scratch arrays of `cap` doubles, recentring variants
@@ -231,8 +247,8 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
     if (ngood == 0) return fit_nan(S, false, false);  // :225-236
     __syncwarp();
     // dao_value.py:60-84: any point off the look-up table zeroes the model for ALL points
-    xmin = 2. * warp_min(xmin) + half; xmax = 2. * warp_max(xmax) + half;
-    ymin = 2. * warp_min(ymin) + half; ymax = 2. * warp_max(ymax) + half;
+    xmin = 2. * pk_min(xmin) + half; xmax = 2. * pk_max(xmax) + half;
+    ymin = 2. * pk_min(ymin) + half; ymax = 2. * pk_max(ymax) + half;
     const bool guard = (xmin < 1.) || (xmax > npsf - 2.) || (ymin < 1.) || (ymax > npsf - 2.);
     for (int q = lane; q < ngood; q += 32) {
         double mval = 0., dvx = 0., dvy = 0.;
@@ -301,22 +317,22 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
         if (nkept == 0) return fit_nan(S, false, true);  // :347-356 (every pixel rejected)
         nl = warp_sum_int(nl);
         if (nl == 0) return fit_nan(S, false, false);    // :391-401
-        numer = warp_sum(numer); denom = warp_sum(denom);
-        S.chi2 = warp_sum(s3) / (double)(nl - 1);          // :409-410
-        schi = warp_sum(schi);
+        numer = pk_sum(numer); denom = pk_sum(denom);
+        S.chi2 = pk_sum(s3) / (double)(nl - 1);          // :409-410
+        schi = pk_sum(schi);
         S.chi = schi;
-        sumwt = warp_sum(sumwt);
+        sumwt = pk_sum(sumwt);
         {   // :416-424; python min(): a NaN first element wins
-            wmin = warp_min(wmin);
+            wmin = pk_min(wmin);
             const bool fn = __any_sync(FULL, wfirst_nan);
             if (!fn && wmin > 100000) return fit_nan(S, false, false);
         }
         double v[3], c[3][3];
-        v[0] = warp_sum(v0); v[1] = warp_sum(v1); v[2] = warp_sum(v2);
-        c[0][0] = warp_sum(c00); c[1][1] = warp_sum(c11); c[2][2] = warp_sum(c22);
-        c[0][1] = c[1][0] = warp_sum(c01);
-        c[0][2] = c[2][0] = warp_sum(c02);
-        c[1][2] = c[2][1] = warp_sum(c12);
+        v[0] = pk_sum(v0); v[1] = pk_sum(v1); v[2] = pk_sum(v2);
+        c[0][0] = pk_sum(c00); c[1][1] = pk_sum(c11); c[2][2] = pk_sum(c22);
+        c[0][1] = c[1][0] = pk_sum(c01);
+        c[0][2] = c[2][0] = pk_sum(c02);
+        c[1][2] = c[2][1] = pk_sum(c12);
         if (!fit_tail<2>(P, gauss, S, v, c, numer, denom, schi, sumwt, &loop)) return fit_nan(S, false, false);
     }
     return fit_out(S);
@@ -406,8 +422,8 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
         if (ngood == 0) return fit_nan(S, false, false);  // pkfit.py:211-219
         __syncwarp();
         // dao_value.py:60-84: any point off the look-up table zeroes the model for ALL points
-        xmin = 2. * warp_min(xmin) + half; xmax = 2. * warp_max(xmax) + half;
-        ymin = 2. * warp_min(ymin) + half; ymax = 2. * warp_max(ymax) + half;
+        xmin = 2. * pk_min(xmin) + half; xmax = 2. * pk_max(xmax) + half;
+        ymin = 2. * pk_min(ymin) + half; ymax = 2. * pk_max(ymax) + half;
         const bool guard = (xmin < 1.) || (xmax > npsf - 2.) || (ymin < 1.) || (ymax > npsf - 2.);
 
         // ---- pass B: model, residuals (pkfit.py:224-283)
@@ -520,16 +536,16 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
             }
         }
         if (nl == 0) return fit_nan(S, false, false);  // pkfit.py:325-333
-        numer = warp_sum(numer); denom = warp_sum(denom);
-        schi = warp_sum(schi);
+        numer = pk_sum(numer); denom = pk_sum(denom);
+        schi = pk_sum(schi);
         S.chi = schi;
-        sumwt = warp_sum(sumwt);
+        sumwt = pk_sum(sumwt);
         double v[3], c[3][3];
-        v[0] = warp_sum(v0); v[1] = warp_sum(v1); v[2] = warp_sum(v2);
-        c[0][0] = warp_sum(c00); c[1][1] = warp_sum(c11); c[2][2] = warp_sum(c22);
-        c[0][1] = c[1][0] = warp_sum(c01);
-        c[0][2] = c[2][0] = warp_sum(c02);
-        c[1][2] = c[2][1] = warp_sum(c12);
+        v[0] = pk_sum(v0); v[1] = pk_sum(v1); v[2] = pk_sum(v2);
+        c[0][0] = pk_sum(c00); c[1][1] = pk_sum(c11); c[2][2] = pk_sum(c22);
+        c[0][1] = c[1][0] = pk_sum(c01);
+        c[0][2] = c[2][0] = pk_sum(c02);
+        c[1][2] = c[2][1] = pk_sum(c12);
         if (!fit_tail<V>(P, gauss, S, v, c, numer, denom, schi, sumwt, &loop)) return fit_nan(S, false, false);
         __syncwarp();
     }
