@@ -25,6 +25,9 @@ namespace bphot {
 
 // Out-of-line warp reductions for the fit kernels (PK_NOINLINE_SUMS=1): ~45 inlined fp64 butterfly reductions were a
 // third of the kernel's 80 KB of code and the fit warps stalled on instruction fetch.
+#ifndef PK_U
+#define PK_U 1  // 32-pixel chunks of the forced fit's pixel list handled per pass (2 and 3 measured slower: registers)
+#endif
 #ifndef PK_NOINLINE_SUMS
 #define PK_NOINLINE_SUMS 0
 #endif
@@ -271,47 +274,61 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
         double wmin = KeyTraits<double>::inf();
         bool wfirst_nan = false, seen = false;
         int nkept = 0, nl = 0;
-        for (int base = 0; base < ngood; base += 32) {
-            const int q = base + lane;
-            bool keep = false, lil = false;
-            double df = 0., rel = 0., sigsq = 1., wt = 0., t0 = 0., t1 = 0., t2 = 0., dfs = 0.;
-            if (q < ngood) {
-                t0 = MV[q];
-                const double sg = SIG[q];
-                df = FSUB[q] - S.scale * t0 - sky;  // :278
-                rel = df / sg;                       // :327
-                keep = !(later && fabs(rel / chiold) >= 10.);  // :341-373 (rejection restarts from the full list)
-                sigsq = sg * sg;
-                dfs = DFS[q];
-                lil = keep && (dfs == dfs);
-            }
-            const unsigned mk = __ballot_sync(FULL, keep);
-            if (lil) {  // :377-410
-                numer = numer + dfs * df / sigsq;
-                denom = denom + dfs * dfs / sigsq;
-                s3 = s3 + df * df / sigsq;
-                nl++;
-            }
-            if (keep) {
-                wt = W0[q];
-                schi = schi + wt * fabs(rel);  // :411
-                sumwt = sumwt + wt;
-                wt = wt / sigsq;               // :414
-                wmin = fmin(wmin, wt);
-                if (!seen && (mk & lt) == 0u) wfirst_nan = (wt != wt);
-                if (later) {                   // :426-427
-                    const double e = 0.4 * rel / chiold;
-                    const double e2 = e * e, e4 = e2 * e2;
-                    wt = wt / (1. + e4 * e4);
+        // PK_U chunks of 32 pixels per pass: the divisions of the chunks are independent and overlap; the sums still
+        // take the pixels in list order (chunk by chunk), so every partial sum has the bits it had with one chunk per pass
+        for (int base0 = 0; base0 < ngood; base0 += 32 * PK_U) {
+            bool keep[PK_U], lil[PK_U];
+            double df[PK_U], rel[PK_U], sigsq[PK_U], t0[PK_U], dfs[PK_U], wt[PK_U], t1[PK_U], t2[PK_U], wtr[PK_U];
+#pragma unroll
+            for (int u = 0; u < PK_U; u++) {
+                const int q = base0 + 32 * u + lane;
+                keep[u] = false; lil[u] = false;
+                df[u] = 0.; rel[u] = 0.; sigsq[u] = 1.; t0[u] = 0.; dfs[u] = 0.; wt[u] = 0.; t1[u] = 0.; t2[u] = 0.; wtr[u] = 0.;
+                if (q < ngood) {
+                    t0[u] = MV[q];
+                    const double sg = SIG[q];
+                    df[u] = FSUB[q] - S.scale * t0[u] - sky;  // :278
+                    rel[u] = df[u] / sg;                       // :327
+                    keep[u] = !(later && fabs(rel[u] / chiold) >= 10.);  // :341-373 (rejection restarts from the full list)
+                    sigsq[u] = sg * sg;
+                    dfs[u] = DFS[q];
+                    lil[u] = keep[u] && (dfs[u] == dfs[u]);
+                    if (keep[u]) {
+                        wt[u] = W0[q];
+                        wtr[u] = wt[u] / sigsq[u];  // :414
+                        t1[u] = -S.scale * DVX[q];
+                        t2[u] = -S.scale * DVY[q];
+                    }
                 }
-                t1 = -S.scale * DVX[q];
-                t2 = -S.scale * DVY[q];
-                v0 = v0 + df * t0 * wt; v1 = v1 + df * t1 * wt; v2 = v2 + df * t2 * wt;
-                c00 = c00 + t0 * t0 * wt; c01 = c01 + t0 * t1 * wt; c02 = c02 + t0 * t2 * wt;
-                c11 = c11 + t1 * t1 * wt; c12 = c12 + t1 * t2 * wt; c22 = c22 + t2 * t2 * wt;
-                nkept++;
             }
-            if (mk) seen = true;
+#pragma unroll
+            for (int u = 0; u < PK_U; u++) {
+                if (base0 + 32 * u >= ngood) break;  // warp-uniform
+                const unsigned mk = __ballot_sync(FULL, keep[u]);
+                if (lil[u]) {  // :377-410
+                    numer = numer + dfs[u] * df[u] / sigsq[u];
+                    denom = denom + dfs[u] * dfs[u] / sigsq[u];
+                    s3 = s3 + df[u] * df[u] / sigsq[u];
+                    nl++;
+                }
+                if (keep[u]) {
+                    schi = schi + wt[u] * fabs(rel[u]);  // :411
+                    sumwt = sumwt + wt[u];
+                    double w = wtr[u];
+                    wmin = fmin(wmin, w);
+                    if (!seen && (mk & lt) == 0u) wfirst_nan = (w != w);
+                    if (later) {                   // :426-427
+                        const double e = 0.4 * rel[u] / chiold;
+                        const double e2 = e * e, e4 = e2 * e2;
+                        w = w / (1. + e4 * e4);
+                    }
+                    v0 = v0 + df[u] * t0[u] * w; v1 = v1 + df[u] * t1[u] * w; v2 = v2 + df[u] * t2[u] * w;
+                    c00 = c00 + t0[u] * t0[u] * w; c01 = c01 + t0[u] * t1[u] * w; c02 = c02 + t0[u] * t2[u] * w;
+                    c11 = c11 + t1[u] * t1[u] * w; c12 = c12 + t1[u] * t2[u] * w; c22 = c22 + t2[u] * t2[u] * w;
+                    nkept++;
+                }
+                if (mk) seen = true;
+            }
         }
         nkept = warp_sum_int(nkept);
         if (nkept == 0) return fit_nan(S, false, true);  // :347-356 (every pixel rejected)
