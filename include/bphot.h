@@ -180,6 +180,25 @@ int bphot_find_host(const void* image, int image_dtype, int nrow, int ncol,
                     double* x, double* y, double* flux, double* sharp, double* roundness,
                     int* counts, int device);
 
+/*
+ * cntrd.cntrd(img, x, y, fwhm, extendbox, keepcenter)         PythonPhot/cntrd.py:7-231
+ * Derivative-search centroid around approximate positions x[npts], y[npts] (device, fp64).
+ * extend_x / extend_y: the `extendbox` keyword (scalar -> both); keepcenter as the keyword.
+ * Outputs: xcen, ycen (fp64; -1, -1 where the reference gives up) and status (int32):
+ */
+#define BPHOT_CNTRD_OK 0
+#define BPHOT_CNTRD_EDGE 1             /* 'too near edge of image'            cntrd.py:113-119 */
+#define BPHOT_CNTRD_MOVED_EDGE 2       /* 'moved too near edge of image'      cntrd.py:146-152 */
+#define BPHOT_CNTRD_X_NOT_DECREASING 3 /* 'Unable to compute X centroid'      cntrd.py:181-186 */
+#define BPHOT_CNTRD_X_OUT_OF_RANGE 4   /* 'Computed X centroid out of range'  cntrd.py:188-193 */
+#define BPHOT_CNTRD_Y_NOT_DECREASING 5 /* cntrd.py:202-207 */
+#define BPHOT_CNTRD_Y_OUT_OF_RANGE 6   /* cntrd.py:209-214 */
+#define BPHOT_CNTRD_NO_FINITE_PIXEL 7  /* search box all NaN (the reference raises) */
+int bphot_cntrd_device(const void* d_image, int image_dtype, int nrow, int ncol, long long pitch,
+                       const double* d_x, const double* d_y, int npts, double fwhm,
+                       int extend_x, int extend_y, int keepcenter,
+                       double* d_xcen, double* d_ycen, int* d_status, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -13,7 +13,7 @@ hand-written CUDA in ``csrc/`` behind the C ABI of ``include/bphot.h``; there is
 from . import _lib  # noqa: F401
 from . import aper, pkfit, pkfit_noise, pkfit_norecent_noise  # noqa: F401
 from . import mmm, pixwt, dao_value, daoerf, rinter  # noqa: F401
-from . import getpsf, rdpsf, find, shard  # noqa: F401
+from . import getpsf, rdpsf, find, cntrd, shard  # noqa: F401
 from ._pkfit_core import PkfitEngine as _PkfitEngine
 
 
@@ -28,4 +28,4 @@ class pkfit_class(_PkfitEngine):
 
 
 __all__ = ["aper", "pkfit", "pkfit_noise", "pkfit_norecent_noise", "mmm", "pixwt", "dao_value", "daoerf",
-           "rinter", "getpsf", "rdpsf", "find", "shard", "pkfit_class"]
+           "rinter", "getpsf", "rdpsf", "find", "cntrd", "shard", "pkfit_class"]

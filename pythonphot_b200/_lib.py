@@ -41,6 +41,7 @@ _SIGNATURES = {
     "bphot_pixwt_device": (C.c_int, [_d, _d, _d, _vp, _vp, _ll, _vp, _vp]),
     "bphot_psfmodel_device": (C.c_int, [_vp, _vp, _ll, _vp, _vp, _i, _i, _vp, _vp]),
     "bphot_find_device": (C.c_int, [_vp, _i, _i, _i, _ll, _d, _d, _d, _d, _d, _d, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "bphot_cntrd_device": (C.c_int, [_vp, _i, _i, _i, _ll, _vp, _vp, _i, _d, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "bphot_find_host": (C.c_int, [_vp, _i, _i, _i, _d, _d, _d, _d, _d, _d, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i]),
 }
 EXPORTS = tuple(_SIGNATURES)

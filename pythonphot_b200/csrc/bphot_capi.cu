@@ -736,6 +736,51 @@ int bphot_find_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     return BPHOT_OK;
 }
 
+int bphot_cntrd_device(const void* d_image, int image_dtype, int nrow, int ncol, long long pitch,
+                       const double* d_x, const double* d_y, int npts, double fwhm,
+                       int extend_x, int extend_y, int keepcenter,
+                       double* d_xcen, double* d_ycen, int* d_status, void* stream) {
+    using namespace bphot;
+    if (!d_image || nrow <= 0 || ncol <= 0 || npts < 0 || extend_x < 0 || extend_y < 0) return fail(BPHOT_ERR_ARG, "bphot_cntrd: null image or bad shape");
+    if (image_dtype != BPHOT_F32 && image_dtype != BPHOT_F64) return fail(BPHOT_ERR_ARG, "bphot_cntrd: image dtype %d", image_dtype);
+    if (npts == 0) return BPHOT_OK;
+    if (!d_x || !d_y || !d_xcen || !d_ycen || !d_status) return fail(BPHOT_ERR_ARG, "bphot_cntrd: null star list or output pointer");
+    CntrdConsts hK;
+    memset(&hK, 0, sizeof(hK));
+    int nhalf = (int)(0.637 * fwhm);  // cntrd.py:91-93
+    if (nhalf < 2) nhalf = 2;
+    const int nbox = 2 * nhalf + 1;
+    if (nbox > CNTRD_MAXBOX) return fail(BPHOT_ERR_CAPACITY, "bphot_cntrd: fwhm %g needs a %d-pixel box (limit %d)", fwhm, nbox, CNTRD_MAXBOX);
+    hK.nhalf = nhalf; hK.nbox = nbox; hK.ir = nhalf - 1 < 1 ? 1 : nhalf - 1;
+    hK.ex = extend_x; hK.ey = extend_y; hK.keepcenter = keepcenter ? 1 : 0;
+    double t[CNTRD_MAXBOX];
+    for (int k = 0; k < nbox - 1; k++) {  // cntrd.py:165-170
+        hK.dd[k] = (double)k + 0.5 - nhalf;
+        hK.w[k] = 1. - 0.5 * (fabs(hK.dd[k]) - 0.5) / (nhalf - 0.5);
+        hK.wdd[k] = hK.w[k] * hK.dd[k];
+        t[k] = hK.w[k] * (hK.dd[k] * hK.dd[k]);
+    }
+    hK.sumc = np_sum_host(hK.w, nbox - 1);
+    hK.sumxsq = np_sum_host(t, nbox - 1);
+    cudaStream_t st = (cudaStream_t)stream;
+    CntrdConsts* dK = nullptr;
+    CU_TRY(cudaMallocAsync((void**)&dK, sizeof(CntrdConsts), st));
+    cudaError_t e = cudaMemcpyAsync(dK, &hK, sizeof(CntrdConsts), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);  // hK lives on this stack frame
+    if (e != cudaSuccess) { cudaFreeAsync(dK, st); return fail(BPHOT_ERR_CUDA, "bphot_cntrd: %s", cudaGetErrorString(e)); }
+    CntrdParams P;
+    P.img = d_image; P.nrow = nrow; P.ncol = ncol; P.pitch = pitch > 0 ? pitch : ncol;
+    P.x = d_x; P.y = d_y; P.npts = npts; P.K = dK; P.xcen = d_xcen; P.ycen = d_ycen; P.status = d_status;
+    int blocks = (npts + 127) / 128;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (image_dtype == BPHOT_F32) cntrd_kernel<float><<<blocks, 128, 0, st>>>(P);
+    else cntrd_kernel<double><<<blocks, 128, 0, st>>>(P);
+    g_launches += 1;
+    cudaFreeAsync(dK, st);
+    CU_TRY(cudaGetLastError());
+    return BPHOT_OK;
+}
+
 int bphot_find_host(const void* image, int image_dtype, int nrow, int ncol,
                     double hmin, double fwhm, double round_lo, double round_hi, double sharp_lo, double sharp_hi,
                     int max_out, double* x, double* y, double* flux, double* sharp, double* roundness,

@@ -288,4 +288,99 @@ __global__ void find_gather_kernel(const FindParams P) {
     }
 }
 
+// ------------------------------------------------------------------ cntrd
+// cntrd.cntrd (PythonPhot/cntrd.py:84-231): derivative-search centroid around approximate positions, one thread
+// per star (the boxes are a few dozen pixels).  Status codes are BPHOT_CNTRD_* of include/bphot.h.
+constexpr int CNTRD_MAXBOX = 63;  // nbox = 2*max(int(0.637 fwhm), 2) + 1
+struct CntrdConsts {  // cntrd.py:91-100, 165-171: everything that depends on fwhm alone (host-computed)
+    int nhalf, nbox, ir, ex, ey, keepcenter;
+    double w[CNTRD_MAXBOX], dd[CNTRD_MAXBOX], wdd[CNTRD_MAXBOX];  // weights, offsets, w*dd
+    double sumc, sumxsq;
+};
+struct CntrdParams {
+    const void* img;
+    int nrow, ncol;
+    long long pitch;
+    const double* x;
+    const double* y;
+    int npts;
+    const CntrdConsts* K;
+    double* xcen;
+    double* ycen;
+    int* status;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(128) cntrd_kernel(const CntrdParams P) {
+    __shared__ CntrdConsts sK;
+    {
+        const int* src = reinterpret_cast<const int*>(P.K);
+        int* dst = reinterpret_cast<int*>(&sK);
+        for (int i = threadIdx.x; i < (int)(sizeof(CntrdConsts) / 4); i += 128) dst[i] = src[i];
+    }
+    __syncthreads();
+    const int nhalf = sK.nhalf, nbox = sK.nbox, ir = sK.ir, nd = nbox - 1;
+    const T* __restrict__ img = reinterpret_cast<const T*>(P.img);
+    double d[CNTRD_MAXBOX], v[CNTRD_MAXBOX];
+    for (int i = blockIdx.x * 128 + threadIdx.x; i < P.npts; i += gridDim.x * 128) {
+        const double x = P.x[i], y = P.y[i];
+        const double ix = rint(x), iy = rint(y);  // np.round: half to even (cntrd.py:107-108)
+        auto fail = [&](int code) { P.xcen[i] = -1.0; P.ycen[i] = -1.0; P.status[i] = code; };
+        double xmax = ix, ymax = iy;
+        if (!sK.keepcenter) {  // cntrd.py:112-141: brightest pixel of the (extended) search box
+            const int hx = nhalf + sK.ex, hy = nhalf + sK.ey;
+            if (!(ix >= hx) || !(ix + hx <= P.ncol - 1) || !(iy >= hy) || !(iy + hy <= P.nrow - 1)) { fail(1); continue; }
+            const T* __restrict__ big = img + (size_t)((long long)iy - hy) * P.pitch + ((long long)ix - hx);
+            double mx = 0.0;
+            bool any = false;
+            for (int r = 0; r <= 2 * hy; r++)
+                for (int c = 0; c <= 2 * hx; c++) {
+                    const double val = (double)big[(size_t)r * P.pitch + c];
+                    if (val == val && (!any || val > mx)) { mx = val; any = true; }
+                }
+            if (!any) { fail(7); continue; }  // the reference raises on an all-NaN box
+            long long sx = 0, sy = 0;
+            int nmax = 0;
+            for (int r = 0; r <= 2 * hy; r++)
+                for (int c = 0; c <= 2 * hx; c++)
+                    if ((double)big[(size_t)r * P.pitch + c] == mx) { sx += c; sy += r; nmax++; }
+            const double jx = nmax > 1 ? rint((double)sx / nmax) : (double)sx;  // cntrd.py:133-138
+            const double jy = nmax > 1 ? rint((double)sy / nmax) : (double)sy;
+            xmax = ix - hx + jx;
+            ymax = iy - hy + jy;
+        }
+        if (!(xmax >= nhalf) || !(xmax + nhalf <= P.ncol - 1) || !(ymax >= nhalf) || !(ymax + nhalf <= P.nrow - 1)) { fail(2); continue; }
+        const T* __restrict__ box = img + (size_t)((long long)ymax - nhalf) * P.pitch + ((long long)xmax - nhalf);
+        auto at = [&](int r, int c) -> double { return (double)box[(size_t)r * P.pitch + c]; };
+        // X: first differences along x, summed over the 2*ir+1 central rows in row order (cntrd.py:175-177)
+        for (int c = 0; c < nd; c++) {
+            double s = at(nhalf - ir, c + 1) - at(nhalf - ir, c);
+            for (int r = nhalf - ir + 1; r <= nhalf + ir; r++) s = s + (at(r, c + 1) - at(r, c));
+            d[c] = s;
+        }
+        for (int c = 0; c < nd; c++) v[c] = sK.w[c] * d[c];
+        double sumd = np_sum(v, nd);
+        for (int c = 0; c < nd; c++) v[c] = sK.wdd[c] * d[c];  // (w*dd)*deriv, cntrd.py:179
+        double sumxd = np_sum(v, nd);
+        if (sumxd >= 0) { fail(3); continue; }
+        const double dx = sK.sumxsq * sumd / (sK.sumc * sumxd);
+        if (fabs(dx) > nhalf) { fail(4); continue; }
+        // Y (cntrd.py:196-211)
+        for (int r = 0; r < nd; r++) {  // np.sum(deriv, 1): pairwise along each row of 2*ir+1 differences
+            for (int c = 0; c <= 2 * ir; c++) v[c] = at(r + 1, nhalf - ir + c) - at(r, nhalf - ir + c);
+            d[r] = np_sum(v, 2 * ir + 1);
+        }
+        for (int r = 0; r < nd; r++) v[r] = sK.w[r] * d[r];
+        sumd = np_sum(v, nd);
+        for (int r = 0; r < nd; r++) v[r] = sK.w[r] * d[r] * sK.dd[r];  // (w*deriv)*dd, cntrd.py:200
+        sumxd = np_sum(v, nd);
+        if (sumxd >= 0) { fail(5); continue; }
+        const double dy = sK.sumxsq * sumd / (sK.sumc * sumxd);
+        if (fabs(dy) > nhalf) { fail(6); continue; }
+        P.xcen[i] = xmax - dx;
+        P.ycen[i] = ymax - dy;
+        P.status[i] = 0;
+    }
+}
+
 }  // namespace bphot

@@ -105,15 +105,54 @@ def gen_find():
     return out
 
 
-def main(which=("getpsf", "find")):
+CNTRD_CASES = [  # name, fwhm, extendbox, keepcenter
+    ("fwhm4", 4.1, False, False),
+    ("fwhm4_extend3", 4.1, 3, False),
+    ("fwhm4_extend_xy", 4.1, (1, 4), False),
+    ("fwhm7_keepcenter", 7.0, False, True),
+    ("fwhm2", 2.0, False, False),
+]
+
+
+def gen_cntrd():
+    """cntrd.cntrd on approximate star positions: jittered truth, frame-edge positions, a rounded (integer-valued,
+    tie-prone) copy of the frame, NaN pixels near two stars."""
+    cntrd = refloader.load("cntrd")
+    f = synth.make_field(220, 260, 180, seed=41, dtype=np.float64, margin=3.0, edge_frac=0.1, nan_frac=0.0, sat_frac=2e-4,
+                         scale_range=(3.0, 150.0), with_noise=False)
+    rng = np.random.default_rng(42)
+    x = f["x"] + rng.normal(0, 0.8, f["x"].size)
+    y = f["y"] + rng.normal(0, 0.8, f["y"].size)
+    img = f["image"].copy()
+    for k in (3, 17):
+        img[int(round(f["y"][k])) + 1, int(round(f["x"][k])) - 1] = np.nan
+    out = dict(image=img, x=x, y=y)
+    for tag, frame in (("", img), ("rounded__", np.round(img / 50.0) * 50.0)):
+        for name, fwhm, ext, keep in CNTRD_CASES:
+            with refloader.quiet(), np.errstate(all="ignore"):
+                xc, yc = cntrd.cntrd(frame, x.copy(), y.copy(), fwhm, verbose=False, extendbox=ext, keepcenter=keep)
+            out[tag + name + "__xcen"] = np.asarray(xc, dtype=np.float64)
+            out[tag + name + "__ycen"] = np.asarray(yc, dtype=np.float64)
+    k = int(np.flatnonzero(out["fwhm4__xcen"] > 0)[0])
+    with refloader.quiet():
+        xs, ys = cntrd.cntrd(img, float(x[k]), float(y[k]), 4.1, verbose=False)
+    out["scalar__k"] = np.int64(k)
+    out["scalar__xy"] = np.array([xs, ys], dtype=np.float64)
+    return out
+
+
+
+def main(which=("getpsf", "find", "cntrd")):
     if "getpsf" in which:
         np.savez_compressed(os.path.join(HERE, "golden_getpsf.npz"), **gen_getpsf())
     if "find" in which:
         np.savez_compressed(os.path.join(HERE, "golden_find.npz"), **gen_find())
+    if "cntrd" in which:
+        np.savez_compressed(os.path.join(HERE, "golden_cntrd.npz"), **gen_cntrd())
     for fn in sorted(os.listdir(HERE)):
         if fn.endswith(".npz"):
             print(fn, os.path.getsize(os.path.join(HERE, fn)))
 
 
 if __name__ == "__main__":
-    main(sys.argv[1:] or ("getpsf", "find"))
+    main(sys.argv[1:] or ("getpsf", "find", "cntrd"))
