@@ -156,7 +156,7 @@ def run_reference(a, rank):
     oracle.build()
     field = make_field(a)
     nt = oracle.max_threads()
-    nsample = a.cpu_sample or 20000
+    nsample = a.cpu_sample or 400000
     for _ in range(max(a.warmup, 0)):
         cpu_baseline(field, a, max(nsample // 10, 500))
     vals, t0 = [], time.perf_counter()
@@ -432,7 +432,7 @@ def main():
         if world == 1 and not a.no_cpu_baseline:
             from oracle import oracle
             oracle.build()
-            line["cpu_baseline"] = cpu_baseline(field, a, a.cpu_sample or 20000)
+            line["cpu_baseline"] = cpu_baseline(field, a, a.cpu_sample or 400000)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
