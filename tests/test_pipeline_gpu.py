@@ -1,0 +1,26 @@
+"""find -> cntrd -> aper -> getpsf -> pkfit_noise chained through the drop-in modules (the reference notebook's flow)."""
+import numpy as np
+import pytest
+
+
+@pytest.mark.gpu
+def test_notebook_pipeline_recovers_the_planted_stars():
+    import importlib.util
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("pipeline_example", os.path.join(root, "examples", "pipeline.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    r = mod.run(size=1024, nstars=1500, seed=7, verbose=False)
+    f = r["field"]
+    xc, yc = r["xy"]
+    assert xc.size > 900  # most planted stars are detected and centroided
+    # every centroid sits on a planted star (nearest neighbour within half a pixel for the bright ones)
+    d2 = (xc[:, None] - f["x"][None, :]) ** 2 + (yc[:, None] - f["y"][None, :]) ** 2
+    near = d2.min(axis=1)
+    assert np.median(np.sqrt(near)) < 0.15
+    # the PSF model recovered from the frame has the planted Gaussian widths to a few percent
+    assert abs(r["gauss"][3] - f["gauss"][3]) < 0.08 and abs(r["gauss"][4] - f["gauss"][4]) < 0.08
+    # recentring fits converge for the bulk of the stars and recover the planted fluxes of isolated bright stars
+    conv = (r["niter"] > 0) & (r["niter"] < 25) & np.isfinite(r["scale"])
+    assert conv.mean() > 0.8
