@@ -149,7 +149,10 @@ int bphot_pixwt_device(double xc, double yc, double r, const double* d_x, const 
  * Points whose table coordinates fall outside [1, npsf-2] get zeros in the table-dependent rows;
  * dao_value's all-or-nothing guard (dao_value.py:70-84) is the caller's to apply.
  * table_coords != 0: xx, yy are already look-up-table coordinates (rinter.rinter's own x, y); only the
- * rinter rows (z, dfdx, dfdy) are meaningful then.
+ * rinter rows (z, dfdx, dfdy) are meaningful then, and they follow rinter.py's flat-index arithmetic for ANY
+ * point: flat indices past the end read the last table element (rinter.py:117-135); negative ones read NaN
+ * when table_coords == 1, or wrap numpy-style against an array of length table_coords when it is > 1
+ * (the table, or the padded copy the reference builds: max flat index + 3).
  */
 int bphot_psfmodel_device(const double* d_xx, const double* d_yy, long long n,
                           const double* d_gauss, const double* d_psf, int npsf, int table_coords,

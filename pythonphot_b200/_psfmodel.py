@@ -21,6 +21,6 @@ def evaluate(xx, yy, gauss, psf, device=None, table_coords=False):
     out_t = torch.empty((12, xx_t.numel()), dtype=torch.float64, device=dev)
     with torch.cuda.device(dev):
         rc = _lib.lib().bphot_psfmodel_device(_lib.ptr(xx_t), _lib.ptr(yy_t), xx_t.numel(), _lib.ptr(g_t), _lib.ptr(psf_t),
-                                              int(psf_h.shape[1]), int(bool(table_coords)), _lib.ptr(out_t), _lib.stream_ptr(dev))
+                                              int(psf_h.shape[1]), int(table_coords), _lib.ptr(out_t), _lib.stream_ptr(dev))
     _lib.check(rc)
     return out_t.cpu().numpy()

@@ -159,13 +159,19 @@ BP_HD double daoerf_from_axes(double a0, double fx, double ex, double fy, double
 }
 
 // One row of rinter.py:161-184: cubic through the flat neighbours k-1..k+2 of the table.
-// Flat indices past the end read the last element (rinter.py:117-135 pads the table with it).
-BP_HD void rinter_row(const double* p, long plen, long k, double xd, double* val, double* der) {
-    const long last = plen - 1;
-    const double pm = p[(k - 1) < plen ? (k - 1) : last];
-    const double p0 = p[k < plen ? k : last];
-    const double p1 = p[(k + 1) < plen ? (k + 1) : last];
-    const double p2 = p[(k + 2) < plen ? (k + 2) : last];
+// Flat indices past the end read the last element (rinter.py:117-135 pads the table with it).  Negative flat indices
+// (points above the first table row) wrap like numpy's: `wrap` is the length of the array the reference indexes
+// (the table, or its padded copy); with wrap = 0 they read NaN.
+BP_HD double rinter_at(const double* p, long plen, long idx, long wrap) {
+    if (idx < 0) idx += wrap;
+    if (idx < 0) return NAN;
+    return p[idx < plen ? idx : plen - 1];
+}
+BP_HD void rinter_row(const double* p, long plen, long k, double xd, double* val, double* der, long wrap = 0) {
+    const double pm = rinter_at(p, plen, k - 1, wrap);
+    const double p0 = rinter_at(p, plen, k, wrap);
+    const double p1 = rinter_at(p, plen, k + 1, wrap);
+    const double p2 = rinter_at(p, plen, k + 2, wrap);
     const double c1 = 0.5 * (p1 - pm);
     const double c2 = 2. * p1 + pm - 0.5 * (5. * p0 + p2);
     const double c3 = 0.5 * (3. * (p0 - p1) + p2 - pm);
@@ -174,16 +180,16 @@ BP_HD void rinter_row(const double* p, long plen, long k, double xd, double* val
 }
 
 // rinter.py:98-195 for one point of an [nr, nc] table (row-major, x = column).
-BP_HD double rinter(const double* p, int nr, int nc, double x, double y, double* dfdx, double* dfdy) {
+BP_HD double rinter(const double* p, int nr, int nc, double x, double y, double* dfdx, double* dfdy, long wrap = 0) {
     const long plen = (long)nr * nc;
     const long i = (long)x, j = (long)y;  // rinter.py:98 (truncation)
     const double xd = x - (double)i, yd = y - (double)j;
     const long km = (long)nc * (j - 1) + i;  // rinter.py:101-104
     double ym, y0, y1, y2, gm, g0, g1, g2;
-    rinter_row(p, plen, km, xd, &ym, &gm);
-    rinter_row(p, plen, km + nc, xd, &y0, &g0);
-    rinter_row(p, plen, km + 2L * nc, xd, &y1, &g1);
-    rinter_row(p, plen, km + 3L * nc, xd, &y2, &g2);
+    rinter_row(p, plen, km, xd, &ym, &gm, wrap);
+    rinter_row(p, plen, km + nc, xd, &y0, &g0, wrap);
+    rinter_row(p, plen, km + 2L * nc, xd, &y1, &g1, wrap);
+    rinter_row(p, plen, km + 3L * nc, xd, &y2, &g2, wrap);
     {  // rinter.py:185-188: the y-cubic of the four row derivatives
         const double d1 = 0.5 * (g1 - gm);
         const double d2 = 2. * g1 + gm - 0.5 * (5. * g0 + g2);

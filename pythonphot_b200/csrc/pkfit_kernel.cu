@@ -601,6 +601,7 @@ __global__ void __launch_bounds__(PK_THREADS) pkfit_kernel(const PkfitParams P) 
 // (rows a10-a12): out = [value, dvdx, dvdy, daoerf f, pder0..4, rinter z, dfdx, dfdy] x n (SoA, 12 rows).
 // The "any point off the table" guard of dao_value.py:70-84 is applied by the host wrapper.
 // table_coords != 0: xx, yy are look-up-table coordinates (rinter's own arguments); only the rinter rows are filled.
+// table_coords > 1 is the length numpy would wrap negative flat indices against (rinter.py:117-157).
 __global__ void psfmodel_kernel(const double* xx, const double* yy, long long n, const double* gauss5,
                                 const double* psf, int npsf, int table_coords, double* out) {
     double g[5];
@@ -613,9 +614,11 @@ __global__ void psfmodel_kernel(const double* xx, const double* yy, long long n,
         double z = 0.;
         dfdx = 0.; dfdy = 0.; dvx = 0.; dvy = 0.;
         double val = 0.;
-        if (tx >= 1. && tx <= npsf - 2. && ty >= 1. && ty <= npsf - 2.) {
+        if (table_coords) {  // rinter.rinter's own flat-index semantics: any point, table_coords > 1 = numpy wrap length
+            z = rinter(psf, npsf, npsf, tx, ty, &dfdx, &dfdy, table_coords > 1 ? (long)table_coords : 0L);
+        } else if (tx >= 1. && tx <= npsf - 2. && ty >= 1. && ty <= npsf - 2.) {
             z = rinter(psf, npsf, npsf, tx, ty, &dfdx, &dfdy);
-            if (!table_coords) val = psf_value(xx[i], yy[i], g, psf, npsf, &dvx, &dvy);
+            val = psf_value(xx[i], yy[i], g, psf, npsf, &dvx, &dvy);
         }
         out[0 * n + i] = val; out[1 * n + i] = dvx; out[2 * n + i] = dvy;
         out[3 * n + i] = f;

@@ -128,3 +128,17 @@ def test_rdpsf_gpu_roundtrip(tmp_path):
     want = dao_value.dao_value(dx.ravel(), dy.ravel(), gauss, psf).reshape(17, 17)
     assert np.array_equal(full, want)
     assert np.unravel_index(np.argmax(full), full.shape) == (8, 8)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["past_end", "above_first_row", "both"])
+def test_rinter_gpu_flat_index_semantics_at_the_table_edges(case):
+    """rinter.py indexes the flattened table: rows wrap into each other, indices past the end read the padded last
+    element, negative ones wrap numpy-style.  Golden: the unmodified reference on points in and around a 24x24 table
+    (generated with oracle/refloader.py, see tests/golden/golden_rinter_edge.npz)."""
+    from pythonphot_b200 import rinter
+    g = load_golden("golden_rinter_edge.npz")
+    z, dx, dy = rinter.rinter(g["table"], g[case + "__x"], g[case + "__y"], deriv=True)
+    assert_close(z, g[case + "__z"], rtol=1e-9, atol=1e-12, what=case + " z")
+    assert_close(dx, g[case + "__dfdx"], rtol=1e-9, atol=1e-12, what=case + " dfdx")
+    assert_close(dy, g[case + "__dfdy"], rtol=1e-9, atol=1e-12, what=case + " dfdy")
