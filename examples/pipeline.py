@@ -17,7 +17,7 @@ from pythonphot_b200 import aper, cntrd, find, getpsf, pkfit_noise, synth  # noq
 
 
 def run(size=2048, nstars=6000, seed=1001, verbose=True):
-    f = synth.make_field(size, size, nstars, seed=seed, dtype=np.float32, margin=30.0, edge_frac=0.0, nan_frac=1e-5)
+    f = synth.make_field(size, size, nstars, seed=seed, dtype=np.float32, margin=30.0, edge_frac=0.0, nan_frac=0.0, sat_frac=0.0)
     image, t = f["image"], {}
     say = print if verbose else (lambda *a, **k: None)
     t0 = time.perf_counter()

@@ -281,6 +281,17 @@ void find_constants(double fwhm, bphot::FindConsts* K) {
     for (int i = 0; i < nn; i++) K->ring[i] = mask[i];
     K->ring[nhalf * nbox + nhalf] = 0;  // find.py:199-200
     K->pixels = pixels - 1;
+    {   // footprint offsets, nearest first: the local-maximum test usually fails on a close neighbour
+        int m = 0;
+        for (int d2 = 1; d2 <= 2 * nhalf * nhalf; d2++)
+            for (int r = 0; r < nbox; r++)
+                for (int c = 0; c < nbox; c++)
+                    if (K->ring[r * nbox + c] && (r - nhalf) * (r - nhalf) + (c - nhalf) * (c - nhalf) == d2) {
+                        K->rdy[m] = (signed char)(r - nhalf);
+                        K->rdx[m] = (signed char)(c - nhalf);
+                        m++;
+                    }
+    }
 }
 
 // one non-blocking side stream per device, created on first use and kept for the life of the process
@@ -688,11 +699,15 @@ int bphot_find_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     P.counts = reinterpret_cast<int*>(base + o_cnt); P.flags = reinterpret_cast<unsigned char*>(base + o_fl);
     CU_TRY_F(cudaMemcpyAsync(base + o_K, &hK, sizeof(FindConsts), cudaMemcpyHostToDevice, st));
     const size_t tile_bytes = (size_t)(FIND_TX + 2 * hK.nhalf) * (FIND_TY + 2 * hK.nhalf) * 8;
-    if (image_dtype == BPHOT_F32) find_convolve_kernel<float><<<tiles, FIND_THREADS, tile_bytes, st>>>(P);
-    else find_convolve_kernel<double><<<tiles, FIND_THREADS, tile_bytes, st>>>(P);
+    DevInfo di;
+    if (dev_info(&di)) { cleanup(); return BPHOT_ERR_CUDA; }
+    int cgrid = tiles < di.sms * 8 ? tiles : di.sms * 8;  // persistent: 8 CTAs of 256 threads per SM
+    P.ngrid = cgrid;
+    if (image_dtype == BPHOT_F32) find_convolve_kernel<float><<<cgrid, FIND_THREADS, tile_bytes, st>>>(P);
+    else find_convolve_kernel<double><<<cgrid, FIND_THREADS, tile_bytes, st>>>(P);
     find_min_kernel<<<1, FIND_THREADS, 0, st>>>(P);
     long long cb = (npix + FIND_THREADS - 1) / FIND_THREADS;
-    if (cb > 148 * 16) cb = 148 * 16;
+    if (cb > di.sms * 8) cb = di.sms * 8;
     find_candidate_kernel<<<(int)cb, FIND_THREADS, 0, st>>>(P);
     g_launches += 3;
     int hc[6] = {0, 0, 0, 0, 0, 0};

@@ -17,13 +17,14 @@
 namespace bphot {
 
 constexpr int FIND_MAXBOX = 13;  // find.py:93
-constexpr int FIND_TX = 32, FIND_TY = 16, FIND_THREADS = 256;
+constexpr int FIND_TX = 64, FIND_TY = 32, FIND_THREADS = 256;  // output tile of the convolution
 
 struct FindConsts {  // everything find.py:106-183 derives from fwhm alone; filled on the host (bphot_capi.cu)
     int nhalf, nbox, pixels;  // pixels: footprint size without the centre (find.py:200)
     double sigsq, p;
     double c[FIND_MAXBOX * FIND_MAXBOX];            // convolution kernel, 0 outside the footprint
     unsigned char ring[FIND_MAXBOX * FIND_MAXBOX];  // footprint minus centre
+    signed char rdy[FIND_MAXBOX * FIND_MAXBOX], rdx[FIND_MAXBOX * FIND_MAXBOX];  // its offsets, nearest first (`pixels` of them)
     double c1[FIND_MAXBOX], wt[FIND_MAXBOX], sgx[FIND_MAXBOX], sgy[FIND_MAXBOX], dgdx[FIND_MAXBOX], dgdy[FIND_MAXBOX];
     double sumgx, sumgy, sumgsqx, sumgsqy, sdgdxs, sdgdx, sdgdys, sdgdy, sgdgdx, sgdgdy;
 };
@@ -35,7 +36,8 @@ struct FindParams {
     const FindConsts* K;  // device copy
     double* h;            // [nrow, ncol] convolved image
     double* blockmin;     // [grid of K1]
-    int nblocks;
+    int nblocks;          // tiles of K1
+    int ngrid;            // CTAs of K1 (= entries of blockmin)
     double* minh;         // [1]
     double hmin, round_lo, round_hi, sharp_lo, sharp_hi;
     unsigned char* flags; // [nrow*ncol] candidate flags
@@ -54,6 +56,7 @@ BP_D double nanmin(double a, double b) { return (a != a) ? a : ((b != b) ? b : f
 
 // scipy.ndimage 'reflect' extension (d c b a | a b c d | d c b a)
 BP_D int reflect_index(int i, int n) {
+    if ((unsigned)i < (unsigned)n) return i;
     if (n == 1) return 0;
     const int period = 2 * n;
     i %= period;
@@ -77,23 +80,27 @@ __global__ void __launch_bounds__(FIND_THREADS) find_convolve_kernel(const FindP
     const int nhalf = sK.nhalf, nbox = sK.nbox;
     const int tw = FIND_TX + 2 * nhalf, th = FIND_TY + 2 * nhalf;
     const int tiles_x = (P.ncol + FIND_TX - 1) / FIND_TX;
-    const int x0 = (blockIdx.x % tiles_x) * FIND_TX, y0 = (blockIdx.x / tiles_x) * FIND_TY;
     const T* __restrict__ img = reinterpret_cast<const T*>(P.img);
-    for (int i = tid; i < tw * th; i += FIND_THREADS) {
-        const int ty = i / tw, tx = i - ty * tw;
-        const int gy = reflect_index(y0 + ty - nhalf, P.nrow), gx = reflect_index(x0 + tx - nhalf, P.ncol);
-        tile[i] = (double)img[(size_t)gy * P.pitch + gx];
-    }
-    __syncthreads();
     double mn = __longlong_as_double(0x7ff0000000000000LL);  // +inf
     const int lx = tid & 31;
-    for (int ly = tid >> 5; ly < FIND_TY; ly += FIND_THREADS / 32) {
-        const int gx = x0 + lx, gy = y0 + ly;
+    // persistent CTAs: the constants are staged once, then the CTA walks tiles (neighbouring CTAs take neighbouring
+    // tiles of a tile row, so their halos overlap in L2)
+    for (int tl = blockIdx.x; tl < P.nblocks; tl += gridDim.x) {
+    const int x0 = (tl % tiles_x) * FIND_TX, y0 = (tl / tiles_x) * FIND_TY;
+    __syncthreads();  // the previous tile's readers are done
+    for (int ty = tid >> 5; ty < th; ty += FIND_THREADS / 32) {
+        const T* __restrict__ grow = img + (size_t)reflect_index(y0 + ty - nhalf, P.nrow) * P.pitch;
+        for (int tx = lx; tx < tw; tx += 32) tile[ty * tw + tx] = (double)grow[reflect_index(x0 + tx - nhalf, P.ncol)];
+    }
+    __syncthreads();
+    for (int l = tid; l < FIND_TX * FIND_TY; l += FIND_THREADS) {
+        const int ly = l / FIND_TX, lxx = l % FIND_TX;  // powers of two
+        const int gx = x0 + lxx, gy = y0 + ly;
         if (gx < P.ncol && gy < P.nrow) {
             // scipy accumulates over the footprint (non-zero weights) in row-major order, find.py:188
             double acc = 0.0;
             for (int ky = 0; ky < nbox; ky++) {
-                const double* trow = tile + (ly + ky) * tw + lx;
+                const double* trow = tile + (ly + ky) * tw + lxx;
                 const double* crow = sK.c + ky * nbox;
                 for (int kx = 0; kx < nbox; kx++) {
                     const double w = crow[kx];
@@ -104,6 +111,7 @@ __global__ void __launch_bounds__(FIND_THREADS) find_convolve_kernel(const FindP
             mn = nanmin(mn, acc);
         }
     }
+    }  // tiles
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mn = nanmin(mn, __shfl_xor_sync(FULL, mn, o));
     if ((tid & 31) == 0) s_min[tid >> 5] = mn;
@@ -117,7 +125,7 @@ __global__ void __launch_bounds__(FIND_THREADS) find_convolve_kernel(const FindP
 __global__ void __launch_bounds__(FIND_THREADS) find_min_kernel(const FindParams P) {
     __shared__ double s_min[FIND_THREADS / 32];
     double mn = __longlong_as_double(0x7ff0000000000000LL);
-    for (int i = threadIdx.x; i < P.nblocks; i += FIND_THREADS) mn = nanmin(mn, P.blockmin[i]);
+    for (int i = threadIdx.x; i < P.ngrid; i += FIND_THREADS) mn = nanmin(mn, P.blockmin[i]);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mn = nanmin(mn, __shfl_xor_sync(FULL, mn, o));
     if ((threadIdx.x & 31) == 0) s_min[threadIdx.x >> 5] = mn;
@@ -145,24 +153,29 @@ __global__ void __launch_bounds__(FIND_THREADS) find_candidate_kernel(const Find
         for (int i = threadIdx.x; i < (int)(sizeof(FindConsts) / 4); i += FIND_THREADS) dst[i] = src[i];
     }
     __syncthreads();
-    const int nhalf = sK.nhalf, nbox = sK.nbox;
+    const int nhalf = sK.nhalf;
     const double minh = P.minh[0];
-    const long long npix = (long long)P.nrow * P.ncol;
-    for (long long i = blockIdx.x * (long long)FIND_THREADS + threadIdx.x; i < npix; i += (long long)gridDim.x * FIND_THREADS) {
-        const int y = (int)(i / P.ncol), x = (int)(i - (long long)y * P.ncol);
+    // one warp per 32-pixel row segment: coalesced reads of h, no 64-bit division per pixel
+    const int segs_x = (P.ncol + 31) / 32;
+    const long long nseg = (long long)segs_x * P.nrow;
+    const int lane = threadIdx.x & 31;
+    int found = 0;
+    for (long long sg = blockIdx.x * (long long)(FIND_THREADS / 32) + (threadIdx.x >> 5); sg < nseg; sg += (long long)gridDim.x * (FIND_THREADS / 32)) {
+        const int y = (int)(sg / segs_x), x = (int)(sg - (long long)y * segs_x) * 32 + lane;
+        if (x >= P.ncol) continue;
         const double v = h_bordered(P, nhalf, minh, y, x);
         bool cand = v >= P.hmin;
         if (cand) {
-            for (int k = 0; k < nbox * nbox && cand; k++) {
-                if (!sK.ring[k]) continue;
-                const int ny = y + k / nbox - nhalf, nx = x + k % nbox - nhalf;
+            for (int k = 0; k < sK.pixels && cand; k++) {
+                const int ny = y + sK.rdy[k], nx = x + sK.rdx[k];
                 if (ny < 0 || ny >= P.nrow || nx < 0 || nx >= P.ncol) cand = false;
                 else cand = v >= h_bordered(P, nhalf, minh, ny, nx);
             }
         }
-        P.flags[i] = cand ? 1 : 0;
-        if (cand) atomicAdd(&P.counts[0], 1);
+        P.flags[(size_t)y * P.ncol + x] = cand ? 1 : 0;
+        found += cand;
     }
+    if (found) atomicAdd(&P.counts[0], found);
 }
 
 // numpy's pairwise add-reduce of n <= 13*13 contiguous float64 values (loops_utils.h.src: blocks of 128,
