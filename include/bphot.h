@@ -38,6 +38,9 @@ extern "C" {
 
 #define BPHOT_MAX_APERTURES 16
 
+#define BPHOT_APER_PY2 1       /* bphot_aper_*: `flags` bits */
+#define BPHOT_APER_SIGMACLIP 2
+
 #define BPHOT_OK 0
 #define BPHOT_ERR_ARG (-1)      /* bad argument (NULL pointer, naper out of range, ...) */
 #define BPHOT_ERR_CUDA (-2)     /* CUDA runtime error, see bphot_last_error() */
@@ -68,8 +71,11 @@ int bphot_kernel_times(double* ms, long long* launches);
  *   use_setsky        1 = setskyval given; setsky[3] = (sky, sigma, nsky) (aper.py:156-160, 302-308)
  *   minsky            20 when the reference default [] is used (aper.py:148)
  *   exact             1 = pixwt exact overlap (aper.py:313-333), 0 = polygon approximation
- *   compat_py2        0 = Python-3 semantics of aper.py:246-248 (yy = row + col/nx), 1 = Python-2
+ *   flags             bit 0 (BPHOT_APER_PY2): 0 = Python-3 semantics of aper.py:246-248 (yy = row + col/nx), 1 = Python-2
  *                     integer row (what the reference was written for); only matters when exact=1
+ *                     bit 1 (BPHOT_APER_SIGMACLIP): skyalgorithm='sigmaclipping' -- sky = mean, skyerr = std of the
+ *                     annulus after scipy.stats.sigmaclip(low=4, high=4) (aper.py:275-282) instead of mmm;
+ *                     mmm_iter then counts clipping passes
  * Outputs (fp64 unless noted): mag, magerr, flux, fluxerr [nstars*naper]; sky, skyerr [nstars];
  * badflag uint8 [nstars*naper]; nsky int32 [nstars] (annulus pixels handed to mmm, aper.py:267);
  * mmm_iter int32 [nstars] (clipping iterations mmm ran).
@@ -79,7 +85,7 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
                       double phpadu, const double* apr, int naper, double zeropoint,
                       double skyrad_in, double skyrad_out, double badlo, double badhi,
                       int use_setsky, const double* setsky, int minsky, int exact,
-                      double readnoise, int compat_py2,
+                      double readnoise, int flags,
                       double* d_mag, double* d_magerr, double* d_flux, double* d_fluxerr,
                       double* d_sky, double* d_skyerr, unsigned char* d_badflag,
                       int* d_nsky, int* d_mmm_iter, void* stream);
@@ -89,7 +95,7 @@ int bphot_aper_host(const void* image, int image_dtype, int nrow, int ncol,
                     double phpadu, const double* apr, int naper, double zeropoint,
                     double skyrad_in, double skyrad_out, double badlo, double badhi,
                     int use_setsky, const double* setsky, int minsky, int exact,
-                    double readnoise, int compat_py2,
+                    double readnoise, int flags,
                     double* mag, double* magerr, double* flux, double* fluxerr,
                     double* sky, double* skyerr, unsigned char* badflag,
                     int* nsky, int* mmm_iter, int device);

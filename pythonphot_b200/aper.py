@@ -41,7 +41,7 @@ def _minsky_value(minsky):
 
 
 def aper_device(image_t, xc_t, yc_t, phpadu=1, apr=5, zeropoint=25, skyrad=(40, 50), badpix=(0, 0),
-                setskyval=None, minsky=20, exact=False, readnoise=0, compat='py3', out=None):
+                setskyval=None, minsky=20, exact=False, readnoise=0, compat='py3', out=None, skyalgorithm='mmm'):
     """Device-resident core: ``image_t`` [nrow, ncol] and ``xc_t``/``yc_t`` [nstars] are CUDA tensors.
 
     Enqueues one kernel on the current stream and returns a dict of CUDA tensors
@@ -81,7 +81,8 @@ def aper_device(image_t, xc_t, yc_t, phpadu=1, apr=5, zeropoint=25, skyrad=(40, 
             _lib.ptr(image_t), _lib.dtype_code(image_t), image_t.shape[0], image_t.shape[1], image_t.stride(0),
             _lib.ptr(xc_t), _lib.ptr(yc_t), n, float(phpadu), _lib.nptr(apr_h), naper, float(zeropoint),
             float(skyrad[0]), float(skyrad[1]), float(badpix[0]), float(badpix[1]), use_setsky, _lib.nptr(ssv),
-            int(minsky), int(bool(exact)), float(readnoise or 0), 1 if compat == 'py2' else 0,
+            int(minsky), int(bool(exact)), float(readnoise or 0),
+            (1 if compat == 'py2' else 0) | (2 if str(skyalgorithm).startswith('sigmaclip') else 0),
             _lib.ptr(out['mag']), _lib.ptr(out['magerr']), _lib.ptr(out['flux']), _lib.ptr(out['fluxerr']),
             _lib.ptr(out['sky']), _lib.ptr(out['skyerr']), _lib.ptr(out['badflag']), _lib.ptr(out['nsky']),
             _lib.ptr(out['mmm_iter']), _lib.stream_ptr(dev))
@@ -103,8 +104,8 @@ def aper(image, xc, yc, phpadu=1, apr=5, zeropoint=25,
     float32 image is widened per pixel on the GPU, i.e. results equal the reference called with
     ``image.astype(float64)``.  ``apr`` may also be a list (the reference needs scalar/ndarray).
     """
-    if skyalgorithm != 'mmm':
-        raise NotImplementedError("skyalgorithm=%r: only the 'mmm' sky estimator runs on the GPU" % (skyalgorithm,))
+    if skyalgorithm != 'mmm' and not str(skyalgorithm).startswith('sigmaclip'):  # aper.py:275: anything else means mmm
+        skyalgorithm = 'mmm'
     torch = _lib.torch_cuda()
     dev = _lib.device_of(device if device is not None else (image.device if isinstance(image, torch.Tensor) and image.is_cuda else None))
     # aper.py:134-148
@@ -117,7 +118,7 @@ def aper(image, xc, yc, phpadu=1, apr=5, zeropoint=25,
     yc_t = _lib.to_device_f64(yc, dev)
     o = aper_device(img_t, xc_t, yc_t, phpadu=phpadu, apr=apr, zeropoint=zeropoint, skyrad=skyrad, badpix=badpix,
                     setskyval=setskyval, minsky=_minsky_value(minsky), exact=exact, readnoise=readnoise,
-                    compat=compat)
+                    compat=compat, skyalgorithm=skyalgorithm)
     with torch.cuda.device(dev):
         h = dict(zip(o.keys(), _lib.to_host(list(o.values()))))
     mag, magerr, flux, fluxerr = h['mag'], h['magerr'], h['flux'], h['fluxerr']

@@ -203,6 +203,36 @@ BP_D MmmResult mmm_warp(const View at, int nsky, double readnoise, int minsky, i
     return mmm_sorted(at, delta_sums, plain_sum, first, nsky, readnoise, minsky, mxiter);
 }
 
+// scipy.stats.sigmaclip(skybuf, low, high) followed by np.mean / np.std of the survivors (aper.py:275-282), by one
+// warp on the SORTED annulus: the survivors of every pass are a contiguous index range, found with the same 32-way
+// searches as mmm's brackets; mean and the two-pass variance are lane-strided fp64 sums + butterfly.
+template <typename View>
+BP_D MmmResult sigclip_warp(const View at, int n, double low, double high, int lane) {
+    MmmResult R;
+    R.skymod = nan64(); R.sigma = nan64(); R.skew = 0.0; R.iters = 0;
+    int lo = 0, hi = n;  // survivors: [lo, hi)
+    while (hi > lo) {
+        R.iters++;
+        const int cnt = hi - lo;
+        double a = 0.0;
+        for (int i = lo + lane; i < hi; i += 32) a = a + at(i);
+        const double mean = warp_sum(a) / cnt;
+        double q = 0.0;
+        for (int i = lo + lane; i < hi; i += 32) { const double d = at(i) - mean; q = q + d * d; }
+        const double sd = sqrt(warp_sum(q) / cnt);
+        R.skymod = mean; R.sigma = sd;
+        const double critlo = mean - sd * low, crithi = mean + sd * high;
+        // first index with x >= critlo, first index with x > crithi, both inside [lo, hi)
+        const int nlo = lo + warp_first_true([&](int i) { return at(lo + i) >= critlo; }, cnt, lane);
+        const int nhi = lo + warp_first_true([&](int i) { return at(lo + i) > crithi; }, cnt, lane);
+        const int delta = cnt - (nhi - nlo);
+        lo = nlo; hi = nhi;
+        if (delta == 0) break;
+        if (hi <= lo) { R.skymod = nan64(); R.sigma = nan64(); }  // nothing survived: mean of an empty array
+    }
+    return R;
+}
+
 // ----------------------------------------------------------------- aper
 struct ApPartial {  // one worker warp's share of one aperture
     double sfull;   // sum of pixel values with weight exactly 1 (approx mode) / sum v*w (exact mode)
@@ -616,7 +646,10 @@ __global__ void __launch_bounds__(AP_THREADS, AP_S2_MINB) aper_stage2_kernel(con
         else if (!P.use_setsky) {
             GlobalView<T> view;
             view.p = skeys + (size_t)(i - P.s0) * P.sstride;
-            const MmmResult R = mmm_warp(view, status, P.readnoise, P.minsky, P.mxiter, lane);
+            MmmResult R;
+            if (!P.sky_sigclip) R = mmm_warp(view, status, P.readnoise, P.minsky, P.mxiter, lane);
+            else if (status != nsky_all) { R.skymod = nan64(); R.sigma = nan64(); R.iters = 0; }  // a NaN in the annulus: scipy propagates it
+            else R = sigclip_warp(view, status, 4.0, 4.0, lane);  // aper.py:275-282
             skymod = R.skymod; skysig = R.sigma; iters = R.iters;
         } else {  // aper.py:302-308
             skymod = P.setsky[0]; skysig = P.setsky[1];

@@ -363,7 +363,7 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
                       double phpadu, const double* apr, int naper, double zeropoint,
                       double skyrad_in, double skyrad_out, double badlo, double badhi,
                       int use_setsky, const double* setsky, int minsky, int exact,
-                      double readnoise, int compat_py2,
+                      double readnoise, int flags,
                       double* d_mag, double* d_magerr, double* d_flux, double* d_fluxerr,
                       double* d_sky, double* d_skyerr, unsigned char* d_badflag,
                       int* d_nsky, int* d_mmm_iter, void* stream) {
@@ -389,7 +389,8 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     }
     if (!(skyrad_out >= 0.) || !(skyrad_in >= 0.) || !(skyrad_out < 1e4)) return fail(BPHOT_ERR_ARG, "bphot_aper: skyrad out of range");
     P.skyrad_in = skyrad_in; P.skyrad_out = skyrad_out; P.badlo = badlo; P.badhi = badhi;
-    P.minsky = minsky; P.exact = exact ? 1 : 0; P.compat_py2 = compat_py2 ? 1 : 0; P.mxiter = 50;
+    P.minsky = minsky; P.exact = exact ? 1 : 0; P.compat_py2 = (flags & BPHOT_APER_PY2) ? 1 : 0; P.mxiter = 50;
+    P.sky_sigclip = (flags & BPHOT_APER_SIGMACLIP) ? 1 : 0;
     P.readnoise = readnoise;
     // register-sort variants hold 128*K keys; larger annuli fall back to the shared-memory sort (K = 0)
     const long long bound = use_setsky ? 4 : annulus_bound(skyrad_in, skyrad_out);
@@ -851,7 +852,7 @@ int bphot_aper_host(const void* image, int image_dtype, int nrow, int ncol,
                     double phpadu, const double* apr, int naper, double zeropoint,
                     double skyrad_in, double skyrad_out, double badlo, double badhi,
                     int use_setsky, const double* setsky, int minsky, int exact,
-                    double readnoise, int compat_py2,
+                    double readnoise, int flags,
                     double* mag, double* magerr, double* flux, double* fluxerr,
                     double* sky, double* skyerr, unsigned char* badflag,
                     int* nsky, int* mmm_iter, int device) {
@@ -870,7 +871,7 @@ int bphot_aper_host(const void* image, int image_dtype, int nrow, int ncol,
     CU_TRY(dnsky.alloc((size_t)nstars * 4)); CU_TRY(dit.alloc((size_t)nstars * 4));
     int rc = bphot_aper_device(dimg.p, image_dtype, nrow, ncol, ncol, dx.as<double>(), dy.as<double>(), nstars, phpadu, apr, naper,
                                zeropoint, skyrad_in, skyrad_out, badlo, badhi, use_setsky, setsky, minsky, exact, readnoise,
-                               compat_py2, dmag.as<double>(), dmagerr.as<double>(), dflux.as<double>(), dfluxerr.as<double>(),
+                               flags, dmag.as<double>(), dmagerr.as<double>(), dflux.as<double>(), dfluxerr.as<double>(),
                                dsky.as<double>(), dskyerr.as<double>(), dbad.as<unsigned char>(), dnsky.as<int>(), dit.as<int>(), 0);
     if (rc) return rc;
     DOWN(mag, dmag, na); DOWN(magerr, dmagerr, na); DOWN(flux, dflux, na); DOWN(fluxerr, dfluxerr, na);

@@ -24,6 +24,7 @@ struct AperParams {
     int use_setsky;
     double setsky[3];
     int minsky, exact, compat_py2, mxiter;
+    int sky_sigclip;  // 1: sigma-clipped mean sky (aper.py:275-282) instead of mmm
     double readnoise;
     int sort_cap;  // power of two >= the largest possible annulus pixel count
     // stage-1 -> stage-2 hand-over: sorted annulus keys of stars [s0, s0 + scount), `sstride` keys per star

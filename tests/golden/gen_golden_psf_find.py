@@ -142,17 +142,40 @@ def gen_cntrd():
 
 
 
-def main(which=("getpsf", "find", "cntrd")):
+SIGCLIP_CASES = [  # name, aper keywords; inputs are golden_aper.npz's image and star list
+    ("exact_4050", dict(apr=np.array([3.0, 5.0, 8.0]), skyrad=[40, 50], badpix=[-12000, 60000], exact=True)),
+    ("approx_1220_nobadpix", dict(apr=np.array([2.5, 6.0]), skyrad=[12, 20], badpix=[0, 0], exact=False)),
+]
+
+
+def gen_aper_sigclip():
+    """aper.aper(skyalgorithm='sigmaclipping') (aper.py:275-282) on the frame of golden_aper.npz (fp64 copy)."""
+    aper = refloader.load("aper")
+    g = np.load(os.path.join(HERE, "golden_aper.npz"))
+    img64, x, y = g["image"].astype(np.float64), g["x"], g["y"]
+    out = {}
+    for name, kw in SIGCLIP_CASES:
+        with refloader.quiet(), np.errstate(all="ignore"):
+            r = aper.aper(img64, x, y, phpadu=float(g["phpadu"]), zeropoint=25.0, verbose=False, skyalgorithm="sigmaclipping", **kw)
+        for nm, a in zip(("mag", "magerr", "flux", "fluxerr", "sky", "skyerr", "badflag"), r[:7]):
+            a = np.asarray(a, dtype=np.float64)
+            out["%s__%s" % (name, nm)] = a.reshape(-1) if nm in ("sky", "skyerr") else a.reshape(x.size, -1)
+    return out
+
+
+def main(which=("getpsf", "find", "cntrd", "sigclip")):
     if "getpsf" in which:
         np.savez_compressed(os.path.join(HERE, "golden_getpsf.npz"), **gen_getpsf())
     if "find" in which:
         np.savez_compressed(os.path.join(HERE, "golden_find.npz"), **gen_find())
     if "cntrd" in which:
         np.savez_compressed(os.path.join(HERE, "golden_cntrd.npz"), **gen_cntrd())
+    if "sigclip" in which:
+        np.savez_compressed(os.path.join(HERE, "golden_aper_sigclip.npz"), **gen_aper_sigclip())
     for fn in sorted(os.listdir(HERE)):
         if fn.endswith(".npz"):
             print(fn, os.path.getsize(os.path.join(HERE, fn)))
 
 
 if __name__ == "__main__":
-    main(sys.argv[1:] or ("getpsf", "find", "cntrd"))
+    main(sys.argv[1:] or ("getpsf", "find", "cntrd", "sigclip"))
