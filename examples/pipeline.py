@@ -33,7 +33,10 @@ def run(size=2048, nstars=6000, seed=1001, verbose=True):
     mag, magerr, fl, flerr, sky, skyerr, bad, _ = aper.aper(image, xc, yc, phpadu=f["phpadu"], apr=5, zeropoint=25, skyrad=[40, 50],
                                                             badpix=[-12000, 60000], exact=True, verbose=False)
     t["aper"] = time.perf_counter() - t0
-    good = np.flatnonzero((bad.reshape(xc.size, -1)[:, 0] == 0) & np.isfinite(mag.reshape(xc.size, -1)[:, 0]))
+    # PSF stars: unflagged, with no other detection within 15 px (a blend as first star would set the Gaussian widths)
+    from scipy.spatial import cKDTree
+    dnn = cKDTree(np.column_stack([xc, yc])).query(np.column_stack([xc, yc]), k=2)[0][:, 1]
+    good = np.flatnonzero((bad.reshape(xc.size, -1)[:, 0] == 0) & np.isfinite(mag.reshape(xc.size, -1)[:, 0]) & (dnn > 15.0))
     order = good[np.argsort(mag.reshape(xc.size, -1)[good, 0])]
     t0 = time.perf_counter()
     with contextlib.redirect_stdout(io.StringIO()):

@@ -30,10 +30,19 @@ def test_aper_sigclip_gpu_matches_reference_golden(name):
     r = aper.aper(a["image"].astype(np.float64), a["x"], a["y"], phpadu=float(a["phpadu"]), zeropoint=25.0, verbose=False,
                   skyalgorithm="sigmaclipping", **CASES[name])
     n = a["x"].size
-    assert np.array_equal(np.asarray(r[6]).reshape(n, -1), g[name + "__badflag"])
+    # apertures whose flag hinges on the rounding of one atan (a NaN pixel with overlap weight 0 +- 1e-9) are
+    # identified by the oracle from the geometry alone and left out, as in tests/test_gpu_parity.py
+    from oracle import oracle
+    fragile = oracle.aper(a["image"].astype(np.float64), a["x"], a["y"], phpadu=float(a["phpadu"]), zeropoint=25.0,
+                          return_extra=True, **CASES[name])[-1]
+    ok = ~fragile
+    assert np.array_equal(np.asarray(r[6]).reshape(n, -1)[ok], g[name + "__badflag"][ok])
     for nm, got in zip(("mag", "magerr", "flux", "fluxerr", "sky", "skyerr"), r[:6]):
         want = g["%s__%s" % (name, nm)]
-        assert_close(np.asarray(got).reshape(want.shape), want, rtol=1e-9, atol=1e-7 if nm in ("flux", "fluxerr") else 0.0, what=nm)
+        got = np.asarray(got).reshape(want.shape)
+        if want.ndim == 2:
+            got, want = got[ok], want[ok]
+        assert_close(got, want, rtol=1e-9, atol=1e-7 if nm in ("flux", "fluxerr") else 0.0, what=nm)
 
 
 @pytest.mark.gpu
