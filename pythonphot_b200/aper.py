@@ -96,7 +96,8 @@ def aper(image, xc, yc, phpadu=1, apr=5, zeropoint=25,
          verbose=True, debug=False, compat='py3', device=None, return_info=False):
     """Compute concentric aperture photometry on one or more stars (reference: aper.py:26-433).
 
-    Same positional/keyword arguments and the same return tuple as the reference.  Extras
+    Same positional/keyword arguments and the same return tuple as the reference (``skyalgorithm`` = 'mmm' or
+    'sigmaclipping', aper.py:275-288).  Extras
     (keyword only in spirit): ``compat`` selects how aper.py:246-248 is read -- 'py3' = as the
     reference runs today (pixel y-centre = row + col/nx when exact=True), 'py2' = the Python-2
     integer row it was written for; ``device`` picks the CUDA device; ``return_info`` appends a dict
