@@ -87,38 +87,49 @@ BP_D void shfl_mirror(T (&r)[K], int m, bool keepmin) {
     }
 }
 // partner thread in another warp: through shared memory, row stride K+1 keeps both the writes and
-// the partner reads conflict-free
+// the partner reads conflict-free.  `doit` is warp-uniform: false for warps that hold only padding, or whose
+// partner warp does (then the exchange cannot change anything); every thread still reaches the barriers.
 template <typename T, int K>
-BP_D void smem_stage(T (&r)[K], int m, bool mirror, bool keepmin, T* xbuf, int tid) {
+BP_D void smem_stage(T (&r)[K], int m, bool mirror, bool keepmin, T* xbuf, int tid, bool doit) {
     T* mine = xbuf + tid * (K + 1);
+    if (doit) {
 #pragma unroll
-    for (int q = 0; q < K; q++) mine[q] = r[q];
+        for (int q = 0; q < K; q++) mine[q] = r[q];
+    }
     __syncthreads();
-    const T* theirs = xbuf + (tid ^ m) * (K + 1);
+    if (doit) {
+        const T* theirs = xbuf + (tid ^ m) * (K + 1);
 #pragma unroll
-    for (int q = 0; q < K; q++) {
-        const T o = theirs[mirror ? K - 1 - q : q];
-        r[q] = keepmin ? kmin(r[q], o) : kmax(r[q], o);
+        for (int q = 0; q < K; q++) {
+            const T o = theirs[mirror ? K - 1 - q : q];
+            r[q] = keepmin ? kmin(r[q], o) : kmax(r[q], o);
+        }
     }
     __syncthreads();
 }
+// `nwarps` = warps that hold real keys.  The network is standard (every comparator leaves the minimum at the lower
+// index), so threads above them, which start with +inf in every register, can never receive anything else: their
+// warps skip the whole network and their partners skip the exchanges with them.  With skyrad=[40,50] the annulus
+// has <= 2840 pixels = 89 threads x 32 keys: three warps sort, the fourth only keeps the barriers.
 template <typename T, int K>
-BP_D void cta_sort_regs(T (&r)[K], T* xbuf, int tid) {
-    local_phases<T, K, 2>(r);
+BP_D void cta_sort_regs(T (&r)[K], T* xbuf, int tid, int nwarps) {
+    const int warp = tid >> 5;
+    const bool wact = warp < nwarps;
+    if (wact) local_phases<T, K, 2>(r);
 #pragma unroll 1
     for (int k = 2 * K; k <= AP_THREADS * K; k <<= 1) {
         const int m = k / K - 1;
         const bool keepmin = (tid & (k / (2 * K))) == 0;
-        if (m < 32) shfl_mirror<T, K>(r, m, keepmin);
-        else smem_stage<T, K>(r, m, true, keepmin, xbuf, tid);
+        if (m < 32) { if (wact) shfl_mirror<T, K>(r, m, keepmin); }
+        else smem_stage<T, K>(r, m, true, keepmin, xbuf, tid, wact && (warp ^ (m >> 5)) < nwarps);
 #pragma unroll 1
         for (int j = k >> 2; j >= K; j >>= 1) {
             const int mm = j / K;
             const bool km = (tid & mm) == 0;
-            if (mm < 32) shfl_stage<T, K>(r, mm, km);
-            else smem_stage<T, K>(r, mm, false, km, xbuf, tid);
+            if (mm < 32) { if (wact) shfl_stage<T, K>(r, mm, km); }
+            else smem_stage<T, K>(r, mm, false, km, xbuf, tid, wact && (warp ^ (mm >> 5)) < nwarps);
         }
-        half_clean<T, K, K / 2>(r);
+        if (wact) half_clean<T, K, K / 2>(r);
     }
 }
 
@@ -127,7 +138,7 @@ template <typename T>
 BP_D void cta_bitonic_sort(T* keys, int m, int tid) {
     for (int k = 2; k <= m; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int t = tid; t < (m >> 1); t += AP_THREADS) {
+            for (int t = tid; t < (m >> 1); t += (int)blockDim.x) {
                 const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));  // lower index of the pair
                 const int p = i | j;
                 const bool up = (i & k) == 0;
@@ -275,7 +286,7 @@ BP_D StarGeom star_geom(const AperParams& P, double x, double y) {
 // The annulus pixels of the row are [a0, b0) and (b1, a1]; span[4r..4r+3] = a0, b0, b1, a1 and rowoff[r] = number of
 // annulus pixels in the rows above (filled by row_offsets), so pixel t of row r owns key slot rowoff[r] + t.
 BP_D void row_spans(const StarGeom& g, double rinsq, double routsq, int* span, int* rowoff, int tid) {
-    for (int r = tid; r < g.ny; r += AP_THREADS) {
+    for (int r = tid; r < g.ny; r += (int)blockDim.x) {
         const double dyv = (double)r - g.dy, dysq = dyv * dyv;
         auto rsq_at = [&](int c) { const double dxv = (double)c - g.dx; return dxv * dxv + dysq; };
         int a0 = 0, a1 = -1, b0 = 0, b1 = -1;
@@ -336,14 +347,15 @@ BP_D int2 gather_rows(const AperParams& P, const T* __restrict__ stamp, const St
                       T* __restrict__ keys, int warp, int lane) {
     int nrej = 0, nnan = 0;
     const bool window = P.badlo != P.badhi;
+    const int nw = (int)(blockDim.x >> 5);  // 4 warps, or 3 when the annulus fits 96 threads x K keys
     constexpr int U = 4;  // rows in flight per warp: U independent loads per lane before the first use
-    for (int r0 = warp; r0 < g.ny; r0 += U * AP_WARPS) {
+    for (int r0 = warp; r0 < g.ny; r0 += U * nw) {
         int a0[U], nl[U], skip[U], tot[U], off[U];
         const T* __restrict__ row[U];
         int maxtot = 0;
 #pragma unroll
         for (int u = 0; u < U; u++) {
-            const int r = r0 + u * AP_WARPS;
+            const int r = r0 + u * nw;
             tot[u] = 0;
             if (r < g.ny) {
                 const int4 sp = *reinterpret_cast<const int4*>(span + 4 * r);
@@ -514,13 +526,14 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S
     __shared__ int s_ntot;
     __shared__ int s_nrej[AP_WARPS], s_nnan[AP_WARPS];
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = (int)(blockDim.x >> 5);
     const T* __restrict__ img = reinterpret_cast<const T*>(P.img);
     T* __restrict__ skeys = reinterpret_cast<T*>(P.skeys);
     const double rinsq = P.skyrad_in * P.skyrad_in, routsq = P.skyrad_out * P.skyrad_out;
 
     for (int i = P.s0 + blockIdx.x; i < P.s0 + P.scount; i += gridDim.x) {
         const int s = P.order ? P.order[i] : i;  // stars are visited in image-tile order, results land at s
+        if (P.retry_wide && P.mmm_iter[s] != -3) continue;  // CTA-uniform
         const double x = P.xc[s], y = P.yc[s];
         // aper.py:209-210 (a NaN position crashes the reference; it is flagged bad here)
         const bool badstar = !(x >= 0.5) || !(x <= P.ncol - 1.5) || !(y >= 0.5) || !(y <= P.nrow - 1.5);
@@ -541,13 +554,18 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S
                 if (lane == 0) s_ntot = tot;
             }
             __syncthreads();
+            if (K > 0 && (int)blockDim.x * K < s_ntot && s_ntot <= P.sort_cap) {
+                // the annulus needs the fourth warp of the network: left to the 128-thread pass that follows
+                if (tid == 0) P.mmm_iter[s] = -3;
+                __syncthreads();
+                continue;
+            }
             const int2 cnt = gather_rows<T>(P, stamp, g, span, rowoff, keys, warp, lane);
             const int wrej = warp_sum_int(cnt.x), wnan = warp_sum_int(cnt.y);
             if (lane == 0) { s_nrej[warp] = wrej; s_nnan[warp] = wnan; }
             __syncthreads();
             int nrej = 0, nnan = 0;
-#pragma unroll
-            for (int w = 0; w < AP_WARPS; w++) { nrej += s_nrej[w]; nnan += s_nnan[w]; }
+            for (int w = 0; w < nw; w++) { nrej += s_nrej[w]; nnan += s_nnan[w]; }
             int nslots = s_ntot < P.sort_cap ? s_ntot : P.sort_cap;  // key slots in use (some hold +inf)
             if (nslots > (int)P.sstride) nslots = (int)P.sstride;
             nsky_all = s_ntot - nrej;       // aper.py:267 counts NaNs
@@ -562,13 +580,14 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S
             T* __restrict__ dst = skeys + (size_t)(i - P.s0) * P.sstride;
             if constexpr (K > 0) {
                 T r[K];
+                const int nwarps = ((nslots + K - 1) / K + 31) >> 5, nthr = nwarps * 32;  // warps / threads that get real keys
 #pragma unroll
                 for (int q = 0; q < K; q++) {
-                    const int idx = q * AP_THREADS + tid;  // any bijection will do before sorting
-                    r[q] = idx < nslots ? keys[idx] : KeyTraits<T>::inf();
+                    const int idx = q * nthr + tid;  // any bijection onto the active threads will do before sorting
+                    r[q] = (tid < nthr && idx < nslots) ? keys[idx] : KeyTraits<T>::inf();
                 }
                 __syncthreads();
-                cta_sort_regs<T, K>(r, keys, tid);
+                cta_sort_regs<T, K>(r, keys, tid, nwarps);
                 constexpr int VEC = 16 / sizeof(T);  // sstride is a multiple of VEC, rows are 16-byte aligned
 #pragma unroll
                 for (int q = 0; q < K; q += VEC) {
@@ -581,10 +600,10 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S
             } else {
                 int m = 2;
                 while (m < nslots) m <<= 1;
-                for (int i = nslots + tid; i < m; i += AP_THREADS) keys[i] = KeyTraits<T>::inf();
+                for (int i = nslots + tid; i < m; i += (int)blockDim.x) keys[i] = KeyTraits<T>::inf();
                 __syncthreads();
                 cta_bitonic_sort(keys, m, tid);
-                for (int i = tid; i < nvalid; i += AP_THREADS) dst[i] = keys[i];
+                for (int i = tid; i < nvalid; i += (int)blockDim.x) dst[i] = keys[i];
             }
         }
 
@@ -753,7 +772,7 @@ __global__ void __launch_bounds__(AP_THREADS) mmm_kernel(const T* vec, const lon
                 r[q] = idx < n ? keys[idx] : KeyTraits<T>::inf();
             }
             __syncthreads();
-            cta_sort_regs<T, K>(r, keys, tid);
+            cta_sort_regs<T, K>(r, keys, tid, AP_WARPS);
 #pragma unroll
             for (int q = 0; q < K; q++) keys[tid * (K + 1) + q] = r[q];
             view.shift = __ffs(K) - 1;

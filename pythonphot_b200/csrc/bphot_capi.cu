@@ -423,11 +423,24 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     if (rc) return rc;
     P.order = ord.order;
     int grid1 = 0, grid2 = 0;
+    // stage-1 CTA: 4 warps, or 3 when every annulus fits 96 threads x K keys (the 4th warp of the network would hold
+    // only padding; without it 8 CTAs fit an SM instead of 6)
+    // `bound` is an analytic upper limit (3 235 for skyrad=[40,50], true maximum 2 840): the narrow pass is chosen on
+    // the expected count (annulus area + 3 %); a star that still exceeds 96 x K is marked and redone by a 128-thread pass
+    const double expect = M_PI * (skyrad_out * skyrad_out - skyrad_in * skyrad_in) * 1.03;
+    const int nt1 = (K > 0 && !use_setsky && expect <= 96.0 * K) ? 96 : AP_THREADS;
     LaunchTimer lt(st);
 #define BP_STAGE1(T, KK)                                                                          \
     do {                                                                                          \
-        rc = persistent_grid(aper_stage1_kernel<T, KK>, AP_THREADS, smem, P.scount, &grid1);      \
-        if (!rc) aper_stage1_kernel<T, KK><<<grid1, AP_THREADS, smem, st>>>(P);                   \
+        rc = persistent_grid(aper_stage1_kernel<T, KK>, nt1, smem, P.scount, &grid1);             \
+        if (!rc) aper_stage1_kernel<T, KK><<<grid1, nt1, smem, st>>>(P);                          \
+        if (!rc && nt1 != AP_THREADS) { /* stars whose annulus did not fit 96 x K keys */         \
+            P.retry_wide = 1;                                                                     \
+            rc = persistent_grid(aper_stage1_kernel<T, KK>, AP_THREADS, smem, P.scount, &grid1);  \
+            if (!rc) aper_stage1_kernel<T, KK><<<grid1, AP_THREADS, smem, st>>>(P);               \
+            P.retry_wide = 0;                                                                     \
+            g_launches += 1;                                                                      \
+        }                                                                                         \
     } while (0)
 #define BP_STAGE1_K(T)                       \
     do {                                     \

@@ -24,6 +24,7 @@ struct AperParams {
     int use_setsky;
     double setsky[3];
     int minsky, exact, compat_py2, mxiter;
+    int retry_wide;   // stage 1, second pass: only stars the 96-thread pass marked -3 (annulus larger than 96 x K keys)
     int sky_sigclip;  // 1: sigma-clipped mean sky (aper.py:275-282) instead of mmm
     double readnoise;
     int sort_cap;  // power of two >= the largest possible annulus pixel count
