@@ -557,7 +557,7 @@ int bphot_pkfit_device(int variant, const void* d_image, int image_dtype,
     {   // pixel centres with (dx^2+dy^2) < radius^2: unit cells lie inside a disc of radius + sqrt(2)/2
         const double rr = radius + 0.70710678118654757;
         long long c = (long long)(M_PI * rr * rr + 8.);
-        P.cap = (int)((c + 31) / 32 * 32);
+        P.cap = (int)((c + 7) / 8 * 8);  // lists are indexed q < ngood, nothing reads a whole 32-slot chunk
     }
     P.errmag = d_errmag; P.chi = d_chi; P.sharp = d_sharp; P.niter = d_niter;
     P.scale_out = d_scale_out; P.x_out = d_x_out; P.y_out = d_y_out; P.chi2 = d_chi2;

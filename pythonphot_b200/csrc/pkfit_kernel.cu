@@ -42,6 +42,9 @@ BP_D double pk_max(double v) { return warp_max(v); }
 #endif
 
 
+#ifndef PK_MINB_FORCED
+#define PK_MINB_FORCED 5  // resident CTAs per SM the forced variant's register budget is compiled for
+#endif
 constexpr int PK_WARPS = 4;
 constexpr int PK_THREADS = PK_WARPS * 32;
 constexpr int PK_NARR_FIT = 10;     // per-warp scratch arrays of `cap` doubles, recentring variants
@@ -571,7 +574,7 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
 
 // Shared memory: [psf table | per-warp W arrays | per-warp AX | per-warp GIDX (variants 0, 1)].
 template <int V, typename TI, typename TN>
-__global__ void __launch_bounds__(PK_THREADS) pkfit_kernel(const PkfitParams P) {
+__global__ void __launch_bounds__(PK_THREADS, V == 2 ? PK_MINB_FORCED : 1) pkfit_kernel(const PkfitParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int NARR = (V == 2) ? PK_NARR_FORCED : PK_NARR_FIT;
     double* psf = reinterpret_cast<double*>(smem_raw);
