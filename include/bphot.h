@@ -40,6 +40,7 @@ extern "C" {
 
 #define BPHOT_APER_PY2 1       /* bphot_aper_*: `flags` bits */
 #define BPHOT_APER_SIGMACLIP 2
+#define BPHOT_APER_NARROW_CTAS 256 /* testing aid, see `flags` below */
 
 #define BPHOT_OK 0
 #define BPHOT_ERR_ARG (-1)      /* bad argument (NULL pointer, naper out of range, ...) */
@@ -76,6 +77,9 @@ int bphot_kernel_times(double* ms, long long* launches);
  *                     bit 1 (BPHOT_APER_SIGMACLIP): skyalgorithm='sigmaclipping' -- sky = mean, skyerr = std of the
  *                     annulus after scipy.stats.sigmaclip(low=4, high=4) (aper.py:275-282) instead of mmm;
  *                     mmm_iter then counts clipping passes
+ *                     bit 8 (BPHOT_APER_NARROW_CTAS): always run the sort stage with 96-thread CTAs first, whatever the
+ *                     expected annulus count; stars that do not fit are redone by the 128-thread pass.  Results do
+ *                     not change; the parity tests use it to reach the retry pass, which default radii never need
  * Outputs (fp64 unless noted): mag, magerr, flux, fluxerr [nstars*naper]; sky, skyerr [nstars];
  * badflag uint8 [nstars*naper]; nsky int32 [nstars] (annulus pixels handed to mmm, aper.py:267);
  * mmm_iter int32 [nstars] (clipping iterations mmm ran).

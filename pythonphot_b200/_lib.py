@@ -15,6 +15,7 @@ CSRC = os.path.join(_HERE, "csrc")
 SO_PATH = os.path.join(CSRC, "libbphot.so")
 F32, F64 = 0, 1
 ERR_CAPACITY = -3
+APER_NARROW_CTAS = 256  # bphot.h BPHOT_APER_NARROW_CTAS (testing aid)
 PKFIT, PKFIT_NOISE, PKFIT_NORECENT = 0, 1, 2
 MAX_APERTURES = 16
 

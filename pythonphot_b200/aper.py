@@ -41,7 +41,8 @@ def _minsky_value(minsky):
 
 
 def aper_device(image_t, xc_t, yc_t, phpadu=1, apr=5, zeropoint=25, skyrad=(40, 50), badpix=(0, 0),
-                setskyval=None, minsky=20, exact=False, readnoise=0, compat='py3', out=None, skyalgorithm='mmm'):
+                setskyval=None, minsky=20, exact=False, readnoise=0, compat='py3', out=None, skyalgorithm='mmm',
+                _narrow_ctas=False):
     """Device-resident core: ``image_t`` [nrow, ncol] and ``xc_t``/``yc_t`` [nstars] are CUDA tensors.
 
     Enqueues one kernel on the current stream and returns a dict of CUDA tensors
@@ -82,7 +83,8 @@ def aper_device(image_t, xc_t, yc_t, phpadu=1, apr=5, zeropoint=25, skyrad=(40, 
             _lib.ptr(xc_t), _lib.ptr(yc_t), n, float(phpadu), _lib.nptr(apr_h), naper, float(zeropoint),
             float(skyrad[0]), float(skyrad[1]), float(badpix[0]), float(badpix[1]), use_setsky, _lib.nptr(ssv),
             int(minsky), int(bool(exact)), float(readnoise or 0),
-            (1 if compat == 'py2' else 0) | (2 if str(skyalgorithm).startswith('sigmaclip') else 0),
+            (1 if compat == 'py2' else 0) | (2 if str(skyalgorithm).startswith('sigmaclip') else 0)
+            | (_lib.APER_NARROW_CTAS if _narrow_ctas else 0),
             _lib.ptr(out['mag']), _lib.ptr(out['magerr']), _lib.ptr(out['flux']), _lib.ptr(out['fluxerr']),
             _lib.ptr(out['sky']), _lib.ptr(out['skyerr']), _lib.ptr(out['badflag']), _lib.ptr(out['nsky']),
             _lib.ptr(out['mmm_iter']), _lib.stream_ptr(dev))

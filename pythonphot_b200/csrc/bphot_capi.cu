@@ -428,7 +428,7 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     // `bound` is an analytic upper limit (3 235 for skyrad=[40,50], true maximum 2 840): the narrow pass is chosen on
     // the expected count (annulus area + 3 %); a star that still exceeds 96 x K is marked and redone by a 128-thread pass
     const double expect = M_PI * (skyrad_out * skyrad_out - skyrad_in * skyrad_in) * 1.03;
-    const int nt1 = (K > 0 && !use_setsky && expect <= 96.0 * K) ? 96 : AP_THREADS;
+    const int nt1 = (K > 0 && !use_setsky && (expect <= 96.0 * K || (flags & BPHOT_APER_NARROW_CTAS))) ? 96 : AP_THREADS;
     LaunchTimer lt(st);
 #define BP_STAGE1(T, KK)                                                                          \
     do {                                                                                          \

@@ -151,6 +151,27 @@ def test_aper_vs_oracle_field(pp, oracle, dtype, exact, compat):
     print("fragile: %d mismatching: %d of %d" % (o[-1].sum(), nm, o[-1].size))
 
 
+@pytest.mark.parametrize("skyrad,fit96", [([12, 19.8], 768), ([40, 51.5], 3072)])
+def test_aper_narrow_ctas_and_wide_retry(pp, skyrad, fit96):
+    """Stage 1 with 96-thread CTAs forced: stars whose annulus exceeds 96 x K keys are redone by the 128-thread pass
+    (default radii never need it).  Every column must equal the default launch bit for bit."""
+    import torch
+    from pythonphot_b200 import synth
+    from pythonphot_b200.aper import aper_device
+    f = synth.make_field(600, 700, 2500, seed=77, dtype=np.float32, with_noise=False, edge_frac=0.05)
+    img, x, y = (torch.from_numpy(np.ascontiguousarray(f[k])).cuda() for k in ("image", "x", "y"))
+    kw = dict(phpadu=f["phpadu"], apr=np.array([3., 5.]), skyrad=skyrad, badpix=[-12000, 60000], exact=True)
+    a = aper_device(img, x, y, **kw)
+    b = aper_device(img, x, y, _narrow_ctas=True, **kw)
+    nsky = a["nsky"].cpu().numpy()
+    assert (nsky > fit96).any(), "no star exercises the retry pass"
+    if fit96 == 768:
+        assert ((nsky > 0) & (nsky <= fit96 - 40)).any(), "no star stays on the narrow pass"
+    for k in a:
+        ta, tb = a[k].cpu().numpy(), b[k].cpu().numpy()
+        assert np.array_equal(ta, tb, equal_nan=ta.dtype.kind == "f"), k
+
+
 def test_aper_edge_matrix(pp, oracle):
     """Branches of aper.py: off-frame, edge < apr, nsky < minsky, NaN in annulus / aperture, all-NaN."""
     rng = np.random.default_rng(3)
