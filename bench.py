@@ -330,22 +330,34 @@ def main():
     if not a.no_e2e:
         if rank == 0:
             np_img, np_noise, np_mask = host["image"].numpy(), host["noise"].numpy(), host["mask"].numpy()
-        else:  # other ranks own pinned host copies too: every rank uploads its exposure like a real caller would
-            host = {"image": img_t.cpu().pin_memory(), "noise": noise_t.cpu().pin_memory(), "mask": mask_t.cpu().pin_memory()}
-            np_img, np_noise, np_mask = host["image"].numpy(), host["noise"].numpy(), host["mask"].numpy()
+        else:  # only rank 0 holds the exposure on the host
+            np_img = np_noise = np_mask = None
         nx, ny, nxf, nyf, none, nsky = (t.numpy() for t in (h_x, h_y, h_xf, h_yf, h_one, h_sky))
 
         def e2e_step():
             h2d = d2h = 0
+            im_a, nz_a, mk_a = np_img, np_noise, np_mask
+            if world > 1:
+                # several GPUs: the exposure crosses PCIe once, on rank 0, and reaches the other GPUs over NVLink
+                # (shard.broadcast_exposure); every rank then calls the public API on its own shard of
+                # the star list with HOST star columns and gets HOST results back
+                if rank == 0:
+                    ex = [_lib.to_device_image(np_img, dev), _lib.to_device_image(np_noise, dev) if do_fit else None,
+                          _lib.to_device_mask(np_mask, dev) if do_fit else None]
+                    h2d += np_img.nbytes + (np_noise.nbytes + np_mask.nbytes if do_fit else 0)
+                else:
+                    ex = [torch.empty_like(img_t), torch.empty_like(noise_t) if do_fit else None,
+                          torch.empty_like(mask_t) if do_fit else None]
+                im_a, nz_a, mk_a = shard.broadcast_exposure(ex, src=0)
             if do_aper:
-                r = pp.aper.aper(np_img, nx, ny, phpadu=field["phpadu"], apr=APR, zeropoint=25.0, skyrad=list(SKYRAD),
+                r = pp.aper.aper(im_a, nx, ny, phpadu=field["phpadu"], apr=APR, zeropoint=25.0, skyrad=list(SKYRAD),
                                  badpix=list(BADPIX), exact=True, verbose=False)
-                h2d += np_img.nbytes + nx.nbytes + ny.nbytes
+                h2d += (np_img.nbytes if world == 1 else 0) + nx.nbytes + ny.nbytes
                 d2h += sum(np.asarray(v).nbytes for v in r[:6]) + r[6].size + 8 * n  # uint8 flags + nsky/mmm_iter
             if do_fit:
-                pkh = pp.pkfit_class(np_img, field["gauss"], field["psf"], field["ronois"], field["phpadu"], np_noise, np_mask)
+                pkh = pp.pkfit_class(im_a, field["gauss"], field["psf"], field["ronois"], field["phpadu"], nz_a, mk_a)
                 r = pkh.pkfit_norecent_noise(none, nxf, nyf, nsky, FIT_RADIUS)
-                h2d += np_img.nbytes + np_noise.nbytes + np_mask.nbytes + 4 * nxf.nbytes + field["psf"].nbytes
+                h2d += (np_img.nbytes + np_noise.nbytes + np_mask.nbytes if world == 1 else 0) + 4 * nxf.nbytes + field["psf"].nbytes
                 d2h += sum(np.asarray(v).nbytes for v in r)
             return h2d, d2h
 
@@ -364,7 +376,10 @@ def main():
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             dt = float(tt.item())
         e2e = {"value": world * n * ksteps / dt, "unit": "stars/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-               "steps": ksteps, "ms_per_step": 1e3 * dt / ksteps}
+               "steps": ksteps, "ms_per_step": 1e3 * dt / ksteps,
+               "path": ("aper.aper + pkfit_class.pkfit_norecent_noise with numpy inputs, numpy results" if world == 1 else
+                        "rank 0 uploads the exposure and NCCL-broadcasts it; every rank calls aper.aper + pkfit_class."
+                        "pkfit_norecent_noise on its shard with numpy star columns, numpy results; byte counts are rank 0's")}
 
     if rank == 0:
         peaks = {}
