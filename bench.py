@@ -395,11 +395,11 @@ def main():
         b_fit = 144 * (4 + 4 + 1) + 68
         stages = {}
         if do_aper:
-            stages["aper"] = {"ms": ms_aper, "stars_per_s": n / (ms_aper * 1e-3), "alg_bytes_per_star": b_aper,
+            stages["aper"] = {"ms": ms_aper, "stars_per_s": n / (ms_aper * 1e-3), "job_stars_per_s": world * n / (ms_aper * 1e-3), "alg_bytes_per_star": b_aper,
                               "achieved_gbs": n * b_aper / (ms_aper * 1e-3) / 1e9}
         if do_fit:
             nit = bufs["fit"]["niter"]
-            stages["pkfit"] = {"ms": ms_fit, "stars_per_s": n / (ms_fit * 1e-3), "alg_bytes_per_star": b_fit,
+            stages["pkfit"] = {"ms": ms_fit, "stars_per_s": n / (ms_fit * 1e-3), "job_stars_per_s": world * n / (ms_fit * 1e-3), "alg_bytes_per_star": b_fit,
                                "achieved_gbs": n * b_fit / (ms_fit * 1e-3) / 1e9,
                                "mean_niter": float(nit.double().mean().item()),
                                "frac_niter_25": float((nit == 25).double().mean().item())}
