@@ -26,6 +26,9 @@ constexpr int AP_WARPS = AP_THREADS / 32;
 #ifndef AP_S1_CTAS
 #define AP_S1_CTAS 6  // resident stage-1 CTAs per SM the register budget is compiled for (K = 32, fp32 keys)
 #endif
+#ifndef AP_DYNAMIC
+#define AP_DYNAMIC 1  // 1 = stage-1 CTAs / stage-2 warps draw stars from an atomic counter; 0 = static grid stride
+#endif
 #ifndef AP_S2_MINB
 #define AP_S2_MINB 9  // minimum resident stage-2 CTAs per SM the register budget is compiled for
 #endif
@@ -531,7 +534,18 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S
     T* __restrict__ skeys = reinterpret_cast<T*>(P.skeys);
     const double rinsq = P.skyrad_in * P.skyrad_in, routsq = P.skyrad_out * P.skyrad_out;
 
+#if AP_DYNAMIC
+    // Stars are drawn from a counter instead of a fixed stride: a launch ends when the last star does, not when the
+    // unluckiest CTA has worked off its share (static stride left ~19 % of the warp slots idle in the tail of a launch).
+    __shared__ int s_next[2];
+    for (int it = 0;; it++) {
+        if (tid == 0) s_next[it & 1] = atomicAdd(P.work_counter, 1);
+        __syncthreads();  // also orders this star's use of keys / tables after the previous star's
+        const int i = P.s0 + s_next[it & 1];
+        if (i >= P.s0 + P.scount) break;
+#else
     for (int i = P.s0 + blockIdx.x; i < P.s0 + P.scount; i += gridDim.x) {
+#endif
         const int s = P.order ? P.order[i] : i;  // stars are visited in image-tile order, results land at s
         if (P.retry_wide && P.mmm_iter[s] != -3) continue;  // CTA-uniform
         const double x = P.xc[s], y = P.yc[s];
@@ -655,7 +669,15 @@ template <typename T>
 __global__ void __launch_bounds__(AP_THREADS, AP_S2_MINB) aper_stage2_kernel(const AperParams P) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const T* __restrict__ skeys = reinterpret_cast<const T*>(P.skeys);
+#if AP_DYNAMIC
+    for (;;) {
+        int i = 0;
+        if (lane == 0) i = atomicAdd(P.work_counter, 1);
+        i = P.s0 + __shfl_sync(FULL, i, 0);
+        if (i >= P.s0 + P.scount) break;
+#else
     for (int i = P.s0 + blockIdx.x * AP_WARPS + warp; i < P.s0 + P.scount; i += gridDim.x * AP_WARPS) {
+#endif
         const int s = P.order ? P.order[i] : i;
         const int status = P.mmm_iter[s], nsky_all = P.nsky[s];
         double skymod = 0.0, skysig = 0.0;

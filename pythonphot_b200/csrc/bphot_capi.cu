@@ -418,9 +418,15 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     void* scratch = nullptr;
     if (!use_setsky) CU_TRY(cudaMallocAsync(&scratch, (size_t)batch * P.sstride * es, st));
     P.skeys = scratch;
+    // one zeroed work counter per stage-1 / retry / stage-2 launch
+    const int nbatch = (nstars + batch - 1) / batch;
+    int* counters = nullptr;
+    CU_TRY(cudaMallocAsync((void**)&counters, (size_t)(3 * nbatch + 1) * sizeof(int), st));
+    CU_TRY(cudaMemsetAsync(counters, 0, (size_t)(3 * nbatch + 1) * sizeof(int), st));
+    int* next_counter = counters;
     StarOrder ord;
     rc = make_star_order(d_xc, d_yc, nstars, nrow, ncol, st, &ord);
-    if (rc) return rc;
+    if (rc) { if (scratch) cudaFreeAsync(scratch, st); cudaFreeAsync(counters, st); return rc; }
     P.order = ord.order;
     int grid1 = 0, grid2 = 0;
     // stage-1 CTA: 4 warps, or 3 when every annulus fits 96 threads x K keys (the 4th warp of the network would hold
@@ -433,9 +439,11 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
 #define BP_STAGE1(T, KK)                                                                          \
     do {                                                                                          \
         rc = persistent_grid(aper_stage1_kernel<T, KK>, nt1, smem, P.scount, &grid1);             \
+        P.work_counter = next_counter++;                                                          \
         if (!rc) aper_stage1_kernel<T, KK><<<grid1, nt1, smem, st>>>(P);                          \
         if (!rc && nt1 != AP_THREADS) { /* stars whose annulus did not fit 96 x K keys */         \
             P.retry_wide = 1;                                                                     \
+            P.work_counter = next_counter++;                                                      \
             rc = persistent_grid(aper_stage1_kernel<T, KK>, AP_THREADS, smem, P.scount, &grid1);  \
             if (!rc) aper_stage1_kernel<T, KK><<<grid1, AP_THREADS, smem, st>>>(P);               \
             P.retry_wide = 0;                                                                     \
@@ -453,6 +461,7 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     do {                                                                                                          \
         rc = persistent_grid(aper_stage2_kernel<T>, AP_THREADS, 0, (P.scount + AP_WARPS - 1) / AP_WARPS, &grid2); \
         if (!rc && AP_S2_CTAS > 0 && grid2 > AP_S2_CTAS * d.sms) grid2 = AP_S2_CTAS * d.sms;                      \
+        P.work_counter = next_counter++;                                                                          \
         if (!rc) aper_stage2_kernel<T><<<grid2, AP_THREADS, 0, st>>>(P);                                          \
     } while (0)
     // Aperture sums of every star (independent of the sky): one launch, warp per star.  The kernel is bound by the
@@ -463,7 +472,7 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     if (AP_SIDE_STREAM && !lt.on && nstars >= ORDER_MIN_STARS) {
         rc = side_stream(&side);
-        if (rc) { if (scratch) cudaFreeAsync(scratch, st); ord.release(st); return rc; }
+        if (rc) { if (scratch) cudaFreeAsync(scratch, st); cudaFreeAsync(counters, st); ord.release(st); return rc; }
         cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming);
         cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming);
         cudaEventRecord(ev_fork, st);
@@ -519,6 +528,7 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     }
     lt.flush();
     if (scratch) cudaFreeAsync(scratch, st);
+    cudaFreeAsync(counters, st);
     ord.release(st);
     if (rc) return rc;
     CU_TRY(cudaGetLastError());

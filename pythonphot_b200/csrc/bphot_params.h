@@ -24,6 +24,7 @@ struct AperParams {
     int use_setsky;
     double setsky[3];
     int minsky, exact, compat_py2, mxiter;
+    int* work_counter;  // stage 1 / stage 2: zeroed counter the CTAs (warps) draw their next star from, one per launch
     int retry_wide;   // stage 1, second pass: only stars the 96-thread pass marked -3 (annulus larger than 96 x K keys)
     int sky_sigclip;  // 1: sigma-clipped mean sky (aper.py:275-282) instead of mmm
     double readnoise;
