@@ -632,9 +632,18 @@ template <typename T>
 __global__ void __launch_bounds__(AP_THREADS, AP_SUMS_CTAS) aper_sums_kernel(const AperParams P) {
     __shared__ CrossList s_list[AP_WARPS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    (void)warp;
     const T* __restrict__ img = reinterpret_cast<const T*>(P.img);
     const int naper = P.naper;
+#if AP_DYNAMIC
+    for (;;) {
+        int i = 0;
+        if (lane == 0) i = atomicAdd(P.work_counter, 1);
+        i = __shfl_sync(FULL, i, 0);
+        if (i >= P.nstars) break;
+#else
     for (int i = blockIdx.x * AP_WARPS + warp; i < P.nstars; i += gridDim.x * AP_WARPS) {
+#endif
         const int s = P.order ? P.order[i] : i;
         const double x = P.xc[s], y = P.yc[s];
         if (!(x >= 0.5) || !(x <= P.ncol - 1.5) || !(y >= 0.5) || !(y <= P.nrow - 1.5)) continue;  // aper.py:209-210, flagged by stage 1
@@ -668,6 +677,7 @@ __global__ void __launch_bounds__(AP_THREADS, AP_SUMS_CTAS) aper_sums_kernel(con
 template <typename T>
 __global__ void __launch_bounds__(AP_THREADS, AP_S2_MINB) aper_stage2_kernel(const AperParams P) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    (void)warp;
     const T* __restrict__ skeys = reinterpret_cast<const T*>(P.skeys);
 #if AP_DYNAMIC
     for (;;) {

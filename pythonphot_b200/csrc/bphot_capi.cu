@@ -421,8 +421,8 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     // one zeroed work counter per stage-1 / retry / stage-2 launch
     const int nbatch = (nstars + batch - 1) / batch;
     int* counters = nullptr;
-    CU_TRY(cudaMallocAsync((void**)&counters, (size_t)(3 * nbatch + 1) * sizeof(int), st));
-    CU_TRY(cudaMemsetAsync(counters, 0, (size_t)(3 * nbatch + 1) * sizeof(int), st));
+    CU_TRY(cudaMallocAsync((void**)&counters, (size_t)(3 * nbatch + 2) * sizeof(int), st));
+    CU_TRY(cudaMemsetAsync(counters, 0, (size_t)(3 * nbatch + 2) * sizeof(int), st));
     int* next_counter = counters;
     StarOrder ord;
     rc = make_star_order(d_xc, d_yc, nstars, nrow, ncol, st, &ord);
@@ -482,6 +482,7 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
         int grida = 0;
         const long long nb = ((long long)nstars + AP_WARPS - 1) / AP_WARPS;
         cudaStream_t sa = side ? side : st;
+        P.work_counter = next_counter++;
         lt.begin(KT_APER_SUMS);
         if (image_dtype == BPHOT_F32) {
             rc = persistent_grid(aper_sums_kernel<float>, AP_THREADS, 0, nb, &grida);
@@ -587,12 +588,18 @@ int bphot_pkfit_device(int variant, const void* d_image, int image_dtype,
     rc = make_star_order(d_x, d_y, nstars, nrow, ncol, st, &ord);
     if (rc) return rc;
     P.order = ord.order;
+    int* counter = nullptr;
+    if (cudaMallocAsync((void**)&counter, sizeof(int), st) != cudaSuccess || cudaMemsetAsync(counter, 0, sizeof(int), st) != cudaSuccess) {
+        ord.release(st);
+        return fail(BPHOT_ERR_CUDA, "bphot_pkfit: work counter: %s", cudaGetErrorString(cudaGetLastError()));
+    }
+    P.work_counter = counter;
     LaunchTimer lt(st);
     lt.begin(KT_PKFIT);
 #define BP_LAUNCH(V, TI, TN)                                                              \
     do {                                                                                  \
         rc = persistent_grid(pkfit_kernel<V, TI, TN>, PK_THREADS, smem, nblocks, &grid);  \
-        if (rc) { ord.release(st); return rc; }                                           \
+        if (rc) { ord.release(st); cudaFreeAsync(counter, st); return rc; }               \
         pkfit_kernel<V, TI, TN><<<grid, PK_THREADS, smem, st>>>(P);                       \
     } while (0)
 #define BP_LAUNCH_T(V)                                                           \
@@ -612,6 +619,7 @@ int bphot_pkfit_device(int variant, const void* d_image, int image_dtype,
     lt.end();
     lt.flush();
     ord.release(st);
+    cudaFreeAsync(counter, st);
     g_launches++;
     CU_TRY(cudaGetLastError());
     return BPHOT_OK;

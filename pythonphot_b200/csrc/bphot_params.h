@@ -64,6 +64,7 @@ struct PkfitParams {
     const double* y;
     const double* sky;
     int nstars;
+    int* work_counter;  // zeroed counter the warps draw their next star from
     const int* order;  // visiting order of the stars (image-tile sorted), or null
     int cap;   // per-star pixel-list capacity
     int acap;  // columns / rows of the fitting box (capacity of the per-axis Gaussian factors)

@@ -585,8 +585,13 @@ __global__ void __launch_bounds__(PK_THREADS, V == 2 ? PK_MINB_FORCED : 1) pkfit
     int* GIDX = reinterpret_cast<int*>(psf + ntab + (size_t)PK_WARPS * (NARR * P.cap + 4 * P.acap)) + (size_t)warp * P.cap;
     for (int i = threadIdx.x; i < ntab; i += PK_THREADS) psf[i] = P.psf[i];
     __syncthreads();
-    const int wstride = gridDim.x * PK_WARPS;
-    for (int i = blockIdx.x * PK_WARPS + warp; i < P.nstars; i += wstride) {
+    // stars are drawn from a counter, not a fixed stride: fits take 3 to 25 iterations, and a launch should end with
+    // its last star, not with the warp that was dealt the most slow ones
+    for (;;) {
+        int i = 0;
+        if (lane == 0) i = atomicAdd(P.work_counter, 1);
+        i = __shfl_sync(FULL, i, 0);
+        if (i >= P.nstars) break;
         const int s = P.order ? P.order[i] : i;  // stars are visited in image-tile order, results land at s
         FitOut o;
         if constexpr (V == 2) o = pkfit_forced_warp<TI, TN>(P, psf, W, AX, P.scale[s], P.x[s], P.y[s], P.sky[s], lane);
