@@ -41,6 +41,26 @@ BP_D float kmax(float a, float b) { return fmaxf(a, b); }
 BP_D double kmin(double a, double b) { return fmin(a, b); }
 BP_D double kmax(double a, double b) { return fmax(a, b); }
 
+// Compare-exchange against a value that came from another thread: the lower index of the pair keeps the minimum.
+// ptxas has no single-instruction form for "min or max by predicate": `p ? fminf : fmaxf` becomes FMNMX into a fresh
+// register, a predicated FMNMX over it and an IMAD.MOV back (ncu, v8: 3 939 of stage 1's 28 800 warp-instructions per
+// star are such moves).  AP_ASM_SELECT=1 writes the two predicated min/max in place (no move).  Off by default until
+// it has been through the GPU parity suite and the bench.
+#ifndef AP_ASM_SELECT
+#define AP_ASM_SELECT 0
+#endif
+#if AP_ASM_SELECT
+BP_D float ksel(float a, float b, bool keepmin) {
+    asm("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %2, 0;\n\t@p min.f32 %0, %0, %1;\n\t@!p max.f32 %0, %0, %1;\n\t}"
+        : "+f"(a) : "f"(b), "r"((int)keepmin));
+    return a;
+}
+BP_D double ksel(double a, double b, bool keepmin) { return keepmin ? kmin(a, b) : kmax(a, b); }
+#define AP_KSEL(dst, other, keepmin) dst = ksel(dst, other, keepmin)
+#else
+#define AP_KSEL(dst, other, keepmin) dst = keepmin ? kmin(dst, other) : kmax(dst, other)
+#endif
+
 // ----------------------------------------------------------------- sort
 // Element e of the 128*K-key vector lives in register e % K of thread e / K.  The network is the
 // all-ascending form of bitonic sort: phase k first pairs e with its mirror e ^ (k-1) inside each
@@ -76,7 +96,7 @@ BP_D void shfl_stage(T (&r)[K], int m, bool keepmin) {
 #pragma unroll
     for (int q = 0; q < K; q++) {
         const T o = __shfl_xor_sync(FULL, r[q], m);
-        r[q] = keepmin ? kmin(r[q], o) : kmax(r[q], o);
+        AP_KSEL(r[q], o, keepmin);
     }
 }
 template <typename T, int K>
@@ -85,8 +105,8 @@ BP_D void shfl_mirror(T (&r)[K], int m, bool keepmin) {
     for (int q = 0; q < K / 2; q++) {
         const T oa = __shfl_xor_sync(FULL, r[K - 1 - q], m);
         const T ob = __shfl_xor_sync(FULL, r[q], m);
-        r[q] = keepmin ? kmin(r[q], oa) : kmax(r[q], oa);
-        r[K - 1 - q] = keepmin ? kmin(r[K - 1 - q], ob) : kmax(r[K - 1 - q], ob);
+        AP_KSEL(r[q], oa, keepmin);
+        AP_KSEL(r[K - 1 - q], ob, keepmin);
     }
 }
 // partner thread in another warp: through shared memory, row stride K+1 keeps both the writes and
@@ -105,7 +125,7 @@ BP_D void smem_stage(T (&r)[K], int m, bool mirror, bool keepmin, T* xbuf, int t
 #pragma unroll
         for (int q = 0; q < K; q++) {
             const T o = theirs[mirror ? K - 1 - q : q];
-            r[q] = keepmin ? kmin(r[q], o) : kmax(r[q], o);
+            AP_KSEL(r[q], o, keepmin);
         }
     }
     __syncthreads();
