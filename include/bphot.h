@@ -49,6 +49,8 @@ extern "C" {
 #define BPHOT_ERR_NODEVICE (-4) /* no CUDA device: there is no CPU fallback */
 
 int bphot_version(void);
+/* the build knobs this library was compiled with ("AP_ASM_SELECT=1 AP_BATCH=65536 ..."), for A/B logs */
+const char* bphot_build_flags(void);
 const char* bphot_last_error(void);
 int bphot_device_count(void);
 /* number of kernels this library has launched in this process (bench.py's gpu_launches) */

@@ -25,6 +25,7 @@ _vp, _i, _d, _ll = C.c_void_p, C.c_int, C.c_double, C.c_longlong
 
 _SIGNATURES = {
     "bphot_version": (C.c_int, []),
+    "bphot_build_flags": (C.c_char_p, []),
     "bphot_last_error": (C.c_char_p, []),
     "bphot_device_count": (C.c_int, []),
     "bphot_launch_count": (C.c_longlong, []),
@@ -82,6 +83,10 @@ def lib():
 def check(rc):
     if rc != 0:
         raise BphotError("libbphot error %d: %s" % (rc, lib().bphot_last_error().decode("utf-8", "replace")))
+
+
+def build_flags():
+    return lib().bphot_build_flags().decode("ascii", "replace")
 
 
 def launch_count():
