@@ -44,10 +44,10 @@ BP_D double kmax(double a, double b) { return fmax(a, b); }
 // Compare-exchange against a value that came from another thread: the lower index of the pair keeps the minimum.
 // ptxas has no single-instruction form for "min or max by predicate": `p ? fminf : fmaxf` becomes FMNMX into a fresh
 // register, a predicated FMNMX over it and an IMAD.MOV back (ncu, v8: 3 939 of stage 1's 28 800 warp-instructions per
-// star are such moves).  AP_ASM_SELECT=1 writes the two predicated min/max in place (no move).  Off by default until
-// it has been through the GPU parity suite and the bench.
+// star are such moves).  AP_ASM_SELECT=1 (default) writes the two predicated min/max in place (no move): stage 1
+// 37.45 -> 33.59 ms per 1 M stars, parity suite green (profiles/r02_asmselect_ab.txt).
 #ifndef AP_ASM_SELECT
-#define AP_ASM_SELECT 0
+#define AP_ASM_SELECT 1
 #endif
 #if AP_ASM_SELECT
 BP_D float ksel(float a, float b, bool keepmin) {
