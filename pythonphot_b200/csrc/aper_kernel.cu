@@ -525,6 +525,62 @@ BP_D ApPartial aperture_warp(const AperParams& P, const T* __restrict__ stamp, c
     return A;
 }
 
+// ------------------------------------------------- index of the sorted row
+// What mmm reads from the sorted annulus is (a) single keys by rank, (b) rank queries "first key > / >= v" and
+// (c) sums of (key - skymid) and (key - skymid)^2 over rank ranges (mmm.py:140-145, 217-220, 244-247) plus the
+// plain sum of the central 20 % (mmm.py:288).  Stage 1 holds the sorted keys in registers, K consecutive ones per
+// thread, so it leaves a small index next to the sorted row: per thread t the first key of its block
+// (bmin[t] = key[t*K]) and the EXCLUSIVE prefix sums P[t] = sum over keys [0, t*K) of (d, d^2), d = key - skymid,
+// skymid = mmm.py:121's median.  With it every range sum is two table reads plus at most K/2 keys per end point
+// and every rank query a 7-step search of bmin plus a log2(K)-step search inside one block, so mmm becomes
+// scalar work: aper_mmm_kernel runs it with one THREAD per star (32 stars per warp) instead of one warp.
+// Index layout per star (idx_stride bytes): double2 P[AP_THREADS + 1] | T bmin[AP_THREADS].
+constexpr size_t sort_index_bytes(size_t key_size) { return ((size_t)(AP_THREADS + 1) * 16 + (size_t)AP_THREADS * key_size + 15) & ~(size_t)15; }
+
+template <typename T, int K>
+BP_D void sort_index(const AperParams& P, const T (&r)[K], int nvalid, size_t row, int tid, T* s_med, double (*s_wsum)[2]) {
+    const int lane = tid & 31, warp = tid >> 5, nthr = (int)blockDim.x;
+    unsigned char* base = reinterpret_cast<unsigned char*>(P.sidx) + row * (size_t)P.idx_stride;
+    double2* __restrict__ PT = reinterpret_cast<double2*>(base);
+    T* __restrict__ bmin = reinterpret_cast<T*>(base + (size_t)(AP_THREADS + 1) * 16);
+    // the two median keys (ranks (n-1)/2 and n/2) sit in some thread's registers: static register indices only
+    const int ia = (nvalid - 1) / 2, ib = nvalid / 2, e0 = tid * K;
+    if (nvalid > 0) {
+#pragma unroll
+        for (int q = 0; q < K; q++) {
+            if (e0 + q == ia) s_med[0] = r[q];
+            if (e0 + q == ib) s_med[1] = r[q];
+        }
+    }
+    __syncthreads();
+    const double skymid = nvalid > 0 ? 0.5 * (double)s_med[0] + 0.5 * (double)s_med[1] : 0.0;  // mmm.py:121
+    double a = 0.0, qq = 0.0;
+#pragma unroll
+    for (int q = 0; q < K; q++) {
+        if (e0 + q < nvalid) {
+            const double d = (double)r[q] - skymid;
+            a = a + d;
+            qq = qq + d * d;
+        }
+    }
+    // inclusive scan over the threads of the warp, then over the warps
+    double ia_ = a, iq_ = qq;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const double ua = __shfl_up_sync(FULL, ia_, o), uq = __shfl_up_sync(FULL, iq_, o);
+        if (lane >= o) { ia_ = ua + ia_; iq_ = uq + iq_; }
+    }
+    if (lane == 31) { s_wsum[warp][0] = ia_; s_wsum[warp][1] = iq_; }
+    double xa = __shfl_up_sync(FULL, ia_, 1), xq = __shfl_up_sync(FULL, iq_, 1);  // exclusive within the warp
+    if (lane == 0) { xa = 0.0; xq = 0.0; }
+    __syncthreads();
+    double ba = 0.0, bq = 0.0;
+    for (int w = 0; w < warp; w++) { ba = ba + s_wsum[w][0]; bq = bq + s_wsum[w][1]; }
+    PT[tid] = make_double2(ba + xa, bq + xq);
+    bmin[tid] = r[0];
+    if (tid == nthr - 1) PT[nthr] = make_double2(ba + ia_, bq + iq_);
+}
+
 // ------------------------------------------------------------ the two stages
 // The per-star work splits into a wide part (gather, sort, aperture sums: thousands of independent
 // pixels) and a narrow one (mmm: ~20 dependent clipping iterations on the sorted vector, enough work for
@@ -548,6 +604,8 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S
     int* rowoff = span + 4 * P.span_rows;
     __shared__ int s_ntot;
     __shared__ int s_nrej[AP_WARPS], s_nnan[AP_WARPS];
+    __shared__ T s_med[2];
+    __shared__ double s_wsum[AP_WARPS][2];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = (int)(blockDim.x >> 5);
     const T* __restrict__ img = reinterpret_cast<const T*>(P.img);
@@ -631,6 +689,7 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S
                         else *reinterpret_cast<double2*>(dst + e) = make_double2(r[q], r[q + 1]);
                     }
                 }
+                if (P.sidx) sort_index<T, K>(P, r, nvalid, (size_t)(i - P.s0), tid, s_med, s_wsum);
             } else {
                 int m = 2;
                 while (m < nslots) m <<= 1;
@@ -727,6 +786,40 @@ __global__ void __launch_bounds__(AP_THREADS, AP_S2_MINB) aper_stage2_kernel(con
             nsky_out = (int)P.setsky[2];
         }
         if (lane == 0) { P.sky[s] = skymod; P.skyerr[s] = skysig; P.nsky[s] = nsky_out; P.mmm_iter[s] = iters; }
+    }
+}
+
+// Stage 2, indexed flavour: one THREAD per star runs mmm (mmm.py:121-314) on the sorted row through its index
+// (IndexedView).  32 stars per warp: ~1.5 k warp-instructions per star instead of the warp-per-star kernel's 14 k.
+// Range sums come from prefix differences, so their last bits differ from a direct sum (1e-13 relative); counts and
+// iteration numbers are decided by the same comparisons on the same keys.
+template <typename T>
+__global__ void __launch_bounds__(AP_THREADS) aper_mmm_kernel(const AperParams P) {
+    const T* __restrict__ skeys = reinterpret_cast<const T*>(P.skeys);
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < P.scount; j += gridDim.x * blockDim.x) {
+        const int i = P.s0 + j;
+        const int s = P.order ? P.order[i] : i;
+        const int status = P.mmm_iter[s], nsky_all = P.nsky[s];
+        double skymod = 0.0, skysig = 0.0;
+        int iters = 0, nsky_out = nsky_all;
+        if (status == -1) nsky_out = 0;   // star off the frame, aper.py:221-233: sky = skyerr = 0
+        else if (status == -2) {}         // nsky < minsky, aper.py:269-272: sky = skyerr = 0
+        else {
+            IndexedView<T> V;
+            const unsigned char* base = reinterpret_cast<const unsigned char*>(P.sidx) + (size_t)j * (size_t)P.idx_stride;
+            V.k = skeys + (size_t)j * P.sstride;
+            V.PT = reinterpret_cast<const double*>(base);
+            V.bmin = reinterpret_cast<const T*>(base + (size_t)(AP_THREADS + 1) * 16);
+            V.gs = P.idx_gs;
+            V.n = status;
+            V.skymid = status > 0 ? 0.5 * V((status - 1) / 2) + 0.5 * V(status / 2) : 0.0;
+            const MmmResult R = mmm_sorted(
+                V, [&](int lo, int hi, double, double* s1, double* s2) { V.delta_sums(lo, hi, s1, s2); },
+                [&](int lo, int hi) { return V.plain_sum(lo, hi); }, [&](double v, bool strict) { return V.first(v, strict); },
+                status, P.readnoise, P.minsky, P.mxiter);
+            skymod = R.skymod; skysig = R.sigma; iters = R.iters;
+        }
+        P.sky[s] = skymod; P.skyerr[s] = skysig; P.nsky[s] = nsky_out; P.mmm_iter[s] = iters;
     }
 }
 

@@ -83,6 +83,9 @@ int next_pow2(long long v) {
 #ifndef AP_BATCH
 #define AP_BATCH 65536
 #endif
+#ifndef AP_MMM_INDEXED
+#define AP_MMM_INDEXED 1  // 1 = mmm by one thread per star on the indexed sorted row; 0 = one warp per star on the plain row
+#endif
 #ifndef AP_SIDE_STREAM
 #define AP_SIDE_STREAM 0  // measured: co-running aper_sums with stage 1/2 does not pay; kept as a build knob
 #endif
@@ -341,7 +344,7 @@ int bphot_version(void) { return BPHOT_VERSION; }
 #define BP_STR2(x) #x
 #define BP_STR(x) BP_STR2(x)
 const char* bphot_build_flags(void) {
-    return "AP_ASM_SELECT=" BP_STR(AP_ASM_SELECT) " AP_BATCH=" BP_STR(AP_BATCH) " AP_S1_CTAS=" BP_STR(AP_S1_CTAS)
+    return "AP_ASM_SELECT=" BP_STR(AP_ASM_SELECT) " AP_BATCH=" BP_STR(AP_BATCH) " AP_S1_CTAS=" BP_STR(AP_S1_CTAS) " AP_MMM_INDEXED=" BP_STR(AP_MMM_INDEXED)
            " AP_S2_MINB=" BP_STR(AP_S2_MINB) " AP_SUMS_CTAS=" BP_STR(AP_SUMS_CTAS) " AP_DYNAMIC=" BP_STR(AP_DYNAMIC)
            " PK_MINB_FORCED=" BP_STR(PK_MINB_FORCED) " PK_U=" BP_STR(PK_U);
 }
@@ -423,8 +426,14 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     rc = ensure_log10_table(st);
     if (rc) return rc;
     void* scratch = nullptr;
-    if (!use_setsky) CU_TRY(cudaMallocAsync(&scratch, (size_t)batch * P.sstride * es, st));
+    // thread-per-star mmm on an index of the sorted row (aper_kernel.cu sort_index): register-sort variants, mmm sky
+    const bool indexed = AP_MMM_INDEXED && K > 0 && !use_setsky && !P.sky_sigclip;
+    const size_t keys_bytes = ((size_t)batch * P.sstride * es + 255) & ~(size_t)255;
+    P.idx_stride = indexed ? (long long)sort_index_bytes(es) : 0;
+    P.idx_gs = K == 8 ? 3 : K == 16 ? 4 : 5;
+    if (!use_setsky) CU_TRY(cudaMallocAsync(&scratch, keys_bytes + (size_t)batch * (size_t)P.idx_stride, st));
     P.skeys = scratch;
+    P.sidx = indexed ? (void*)(reinterpret_cast<char*>(scratch) + keys_bytes) : nullptr;
     // one zeroed work counter per stage-1 / retry / stage-2 launch
     const int nbatch = (nstars + batch - 1) / batch;
     int* counters = nullptr;
@@ -466,6 +475,10 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     } while (0)
 #define BP_STAGE2(T)                                                                                              \
     do {                                                                                                          \
+        if (indexed) {                                                                                            \
+            aper_mmm_kernel<T><<<(P.scount + AP_THREADS - 1) / AP_THREADS, AP_THREADS, 0, st>>>(P);               \
+            break;                                                                                                \
+        }                                                                                                         \
         rc = persistent_grid(aper_stage2_kernel<T>, AP_THREADS, 0, (P.scount + AP_WARPS - 1) / AP_WARPS, &grid2); \
         if (!rc && AP_S2_CTAS > 0 && grid2 > AP_S2_CTAS * d.sms) grid2 = AP_S2_CTAS * d.sms;                      \
         P.work_counter = next_counter++;                                                                          \

@@ -20,8 +20,10 @@
 #if defined(__CUDACC__)
 #define BP_HD __host__ __device__ __forceinline__
 #define BP_D __device__ __forceinline__
+#define BP_HDM __host__ __device__ __forceinline__  // member functions
 #else
 #define BP_HD static inline
+#define BP_HDM inline
 #endif
 
 namespace bphot {
@@ -398,6 +400,95 @@ BP_HD double mmm_log10n(int n) {
 #endif
     return log10((double)n);
 }
+
+// ------------------------------------------------ indexed sorted vector
+// read-only loads: __ldg on the device, plain on the host (tests/hostcheck)
+template <typename T>
+BP_HD T bp_ld(const T* p) {
+#if defined(__CUDA_ARCH__)
+    return __ldg(p);
+#else
+    return *p;
+#endif
+}
+BP_HD void bp_ld2(const double* p, double* x, double* y) {  // p is 16-byte aligned
+#if defined(__CUDA_ARCH__)
+    const double2 v = __ldg(reinterpret_cast<const double2*>(p));
+    *x = v.x; *y = v.y;
+#else
+    *x = p[0]; *y = p[1];
+#endif
+}
+
+// Sorted vector + its block index (aper_kernel.cu sort_index builds it), read by ONE thread: keys k[0..n), per block b of
+// 1 << gs keys the first key bmin[b] and the exclusive prefix sums PT[2b], PT[2b+1] of d = key - skymid and d^2.
+template <typename T>
+struct IndexedView {
+    const T* __restrict__ k;
+    const double* __restrict__ PT;  // (sum d, sum d^2) pairs
+    const T* __restrict__ bmin;
+    int gs, n;  // block size = 1 << gs keys; n valid keys
+    double skymid;
+    BP_HDM double operator()(int i) const { return (double)bp_ld(k + i); }
+    // sums of d and d^2 over keys [0, i): the nearer block boundary's prefix, then at most K/2 keys
+    BP_HDM void prefix(int i, double* s1, double* s2) const {
+        const int b = i >> gs, start = b << gs, G = 1 << gs;
+        if (2 * (i - start) <= G) {
+            double a, q;
+            bp_ld2(PT + 2 * b, &a, &q);
+            for (int j = start; j < i; j++) { const double d = (double)bp_ld(k + j) - skymid; a = a + d; q = q + d * d; }
+            *s1 = a; *s2 = q;
+        } else {
+            double a, q;
+            bp_ld2(PT + 2 * (b + 1), &a, &q);
+            const int end = (start + G) < n ? (start + G) : n;
+            for (int j = i; j < end; j++) { const double d = (double)bp_ld(k + j) - skymid; a = a - d; q = q - d * d; }
+            *s1 = a; *s2 = q;
+        }
+    }
+    BP_HDM void delta_sums(int lo, int hi, double* s1, double* s2) const {
+        if (hi - lo <= (1 << gs)) {
+            double a = 0.0, q = 0.0;
+            for (int j = lo; j < hi; j++) { const double d = (double)bp_ld(k + j) - skymid; a = a + d; q = q + d * d; }
+            *s1 = a; *s2 = q;
+        } else {
+            double a1, q1, a0, q0;
+            prefix(hi, &a1, &q1);
+            prefix(lo, &a0, &q0);
+            *s1 = a1 - a0; *s2 = q1 - q0;
+        }
+    }
+    BP_HDM double plain_sum(int lo, int hi) const {
+        if (hi <= lo) return 0.0;
+        if (hi - lo <= (1 << gs)) {
+            double a = 0.0;
+            for (int j = lo; j < hi; j++) a = a + (double)bp_ld(k + j);
+            return a;
+        }
+        double a1, q1, a0, q0;
+        prefix(hi, &a1, &q1);
+        prefix(lo, &a0, &q0);
+        return (a1 - a0) + (double)(hi - lo) * skymid;
+    }
+    // first index with key > v (strict) or key >= v, n if none: bmin picks the block, then a search inside it
+    BP_HDM int first(double v, bool strict) const {
+        const int G = 1 << gs, nb = (n + G - 1) >> gs;
+        int lo = 0, hi = nb;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            const double a = (double)bp_ld(bmin + mid);
+            if (strict ? a > v : a >= v) hi = mid; else lo = mid + 1;
+        }
+        if (lo == 0) return 0;
+        int l = ((lo - 1) << gs) + 1, h = (lo << gs) < n ? (lo << gs) : n;  // key[(lo-1)*G] fails, key[lo*G] passes
+        while (l < h) {
+            const int mid = (l + h) >> 1;
+            const double a = (double)bp_ld(k + mid);
+            if (strict ? a > v : a >= v) h = mid; else l = mid + 1;
+        }
+        return l;
+    }
+};
 
 struct MmmResult {
     double skymod, sigma, skew;
