@@ -212,6 +212,23 @@ def to_host(tensors):
     return [h.numpy() for h in hosts]
 
 
+def alloc_out(spec, n, device, out=None):
+    """Result tensors for a launch: ``spec`` = [(name, torch dtype, tail shape)].  A caller-supplied ``out`` dict is
+    checked column by column (shape, dtype, device, contiguity) before its pointers go to the C ABI: the kernels write
+    n x tail elements per column without knowing how large the buffer behind the pointer is."""
+    torch = torch_cuda()
+    if out is None:
+        return {name: torch.empty((n,) + tuple(tail), dtype=dt, device=device) for name, dt, tail in spec}
+    for name, dt, tail in spec:
+        t = out.get(name)
+        if t is None:
+            raise ValueError("out= is missing column %r" % name)
+        if tuple(t.shape) != (n,) + tuple(tail) or t.dtype != dt or t.device != device or not t.is_contiguous():
+            raise ValueError("out[%r] is %s %s on %s (contiguous=%s); this call needs %s %s on %s" % (
+                name, tuple(t.shape), t.dtype, t.device, t.is_contiguous(), (n,) + tuple(tail), dt, device))
+    return out
+
+
 def host_f64(a):
     return np.ascontiguousarray(np.atleast_1d(np.asarray(a, dtype=np.float64)).reshape(-1))
 

@@ -46,10 +46,8 @@ class PkfitEngine(object):
         dev = self.device
         if variant != _lib.PKFIT and (self._noise_t is None or self._mask_t is None):
             raise ValueError("this fit needs the noise and mask images given to pkfit_class(...)")
-        if out is None:
-            out = {k: torch.empty(n, dtype=torch.float64, device=dev)
-                   for k in ("errmag", "chi", "sharp", "scale", "x", "y", "chi2")}
-            out["niter"] = torch.empty(n, dtype=torch.int32, device=dev)
+        out = _lib.alloc_out([(k, torch.float64, ()) for k in ("errmag", "chi", "sharp", "scale", "x", "y", "chi2")] +
+                             [("niter", torch.int32, ())], n, dev, out)
         img, nz, mk = self._img_t, self._noise_t, self._mask_t
         with torch.cuda.device(dev):
             rc = _lib.lib().bphot_pkfit_device(

@@ -48,7 +48,7 @@ def aper_device(image_t, xc_t, yc_t, phpadu=1, apr=5, zeropoint=25, skyrad=(40, 
     Enqueues one kernel on the current stream and returns a dict of CUDA tensors
     (mag, magerr, flux, fluxerr [nstars, naper] fp64; sky, skyerr [nstars] fp64; badflag uint8
     [nstars, naper]; nsky, mmm_iter int32 [nstars]) without synchronising.  ``out`` may carry a
-    dict from a previous call with the same shapes to reuse its buffers."""
+    dict from a previous call with the same shapes to reuse its buffers (checked: shape, dtype, device)."""
     torch = _lib.torch_cuda()
     if compat not in ('py3', 'py2'):
         raise ValueError("compat must be 'py3' or 'py2'")
@@ -68,15 +68,10 @@ def aper_device(image_t, xc_t, yc_t, phpadu=1, apr=5, zeropoint=25, skyrad=(40, 
         ssv, use_setsky = np.zeros(3), 0
     skyrad = np.asarray(skyrad, dtype=np.float64).reshape(-1)
     badpix = np.asarray(badpix, dtype=np.float64).reshape(-1)
-    if out is None:
-        out = {}
-        for k in ('mag', 'magerr', 'flux', 'fluxerr'):
-            out[k] = torch.empty((n, naper), dtype=torch.float64, device=dev)
-        out['sky'] = torch.empty(n, dtype=torch.float64, device=dev)
-        out['skyerr'] = torch.empty(n, dtype=torch.float64, device=dev)
-        out['badflag'] = torch.empty((n, naper), dtype=torch.uint8, device=dev)
-        out['nsky'] = torch.empty(n, dtype=torch.int32, device=dev)
-        out['mmm_iter'] = torch.empty(n, dtype=torch.int32, device=dev)
+    f64, na = torch.float64, (naper,)
+    out = _lib.alloc_out([('mag', f64, na), ('magerr', f64, na), ('flux', f64, na), ('fluxerr', f64, na), ('sky', f64, ()),
+                          ('skyerr', f64, ()), ('badflag', torch.uint8, na), ('nsky', torch.int32, ()),
+                          ('mmm_iter', torch.int32, ())], n, dev, out)
     with torch.cuda.device(dev):
         rc = _lib.lib().bphot_aper_device(
             _lib.ptr(image_t), _lib.dtype_code(image_t), image_t.shape[0], image_t.shape[1], image_t.stride(0),

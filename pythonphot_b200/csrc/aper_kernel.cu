@@ -234,7 +234,11 @@ BP_D MmmResult mmm_warp(const View at, int nsky, double readnoise, int minsky, i
     auto first = [&](double v, bool strict) -> int {
         return warp_first_true([&](int i) { const double a = at(i); return strict ? a > v : a >= v; }, nsky, lane);
     };
-    return mmm_sorted(at, delta_sums, plain_sum, first, nsky, readnoise, minsky, mxiter);
+    auto first2 = [&](double v1, bool st1, bool need1, double v2, bool st2, bool need2, int* r1, int* r2) {
+        if (need1) *r1 = first(v1, st1);  // need* are warp-uniform
+        if (need2) *r2 = first(v2, st2);
+    };
+    return mmm_sorted(at, delta_sums, plain_sum, first2, nsky, readnoise, minsky, mxiter);
 }
 
 // scipy.stats.sigmaclip(skybuf, low, high) followed by np.mean / np.std of the survivors (aper.py:275-282), by one
@@ -529,38 +533,37 @@ BP_D ApPartial aperture_warp(const AperParams& P, const T* __restrict__ stamp, c
 // What mmm reads from the sorted annulus is (a) single keys by rank, (b) rank queries "first key > / >= v" and
 // (c) sums of (key - skymid) and (key - skymid)^2 over rank ranges (mmm.py:140-145, 217-220, 244-247) plus the
 // plain sum of the central 20 % (mmm.py:288).  Stage 1 holds the sorted keys in registers, K consecutive ones per
-// thread, so it leaves a small index next to the sorted row: per thread t the first key of its block
-// (bmin[t] = key[t*K]) and the EXCLUSIVE prefix sums P[t] = sum over keys [0, t*K) of (d, d^2), d = key - skymid,
-// skymid = mmm.py:121's median.  With it every range sum is two table reads plus at most K/2 keys per end point
-// and every rank query a 7-step search of bmin plus a log2(K)-step search inside one block, so mmm becomes
-// scalar work: aper_mmm_kernel runs it with one THREAD per star (32 stars per warp) instead of one warp.
-// Index layout per star (idx_stride bytes): double2 P[AP_THREADS + 1] | T bmin[AP_THREADS].
-constexpr size_t sort_index_bytes(size_t key_size) { return ((size_t)(AP_THREADS + 1) * 16 + (size_t)AP_THREADS * key_size + 15) & ~(size_t)15; }
+// thread, so it leaves a small index next to the sorted row (bphot_math.cuh IndexedView): a 16-ary search tree
+// (L1[i] = key[256 i], L2[j] = key[16 j]) and, for every group of 16 keys, the EXCLUSIVE prefix sums
+// PT[g] = sum over keys [0, 16 g) of (d, d^2), d = key - skymid, skymid = mmm.py:121's median.  With it a range sum is
+// two table reads plus two 16-key groups and a rank query three 16-key groups, all independent loads, so mmm becomes
+// scalar work that waits for memory a few times per clipping pass: aper_mmm_kernel runs it with one THREAD per
+// star (32 stars per warp) instead of one warp per star.
+// Index layout per star (idx_stride bytes, 64-byte aligned): T L1[16] | T L2[256] | double2 PT[257].
+constexpr size_t sort_index_bytes(size_t key_size) { return ((size_t)(16 + 256) * key_size + (size_t)257 * 16 + 63) & ~(size_t)63; }
 
 template <typename T, int K>
-BP_D void sort_index(const AperParams& P, const T (&r)[K], int nvalid, size_t row, int tid, T* s_med, double (*s_wsum)[2]) {
+BP_D void sort_index(const AperParams& P, const T (&r)[K], const T* __restrict__ dst, int nvalid, size_t row, int tid, double (*s_wsum)[2]) {
+    static_assert(K == 8 || K == 16 || K == 32, "index groups are 16 keys");
     const int lane = tid & 31, warp = tid >> 5, nthr = (int)blockDim.x;
     unsigned char* base = reinterpret_cast<unsigned char*>(P.sidx) + row * (size_t)P.idx_stride;
-    double2* __restrict__ PT = reinterpret_cast<double2*>(base);
-    T* __restrict__ bmin = reinterpret_cast<T*>(base + (size_t)(AP_THREADS + 1) * 16);
-    // the two median keys (ranks (n-1)/2 and n/2) sit in some thread's registers: static register indices only
-    const int ia = (nvalid - 1) / 2, ib = nvalid / 2, e0 = tid * K;
-    if (nvalid > 0) {
-#pragma unroll
-        for (int q = 0; q < K; q++) {
-            if (e0 + q == ia) s_med[0] = r[q];
-            if (e0 + q == ib) s_med[1] = r[q];
-        }
-    }
+    T* __restrict__ L1 = reinterpret_cast<T*>(base);
+    T* __restrict__ L2 = L1 + 16;
+    double2* __restrict__ PT = reinterpret_cast<double2*>(L2 + 256);
+    // the two median keys (ranks (n-1)/2 and n/2) were just written to the scratch row by some thread of this CTA
     __syncthreads();
-    const double skymid = nvalid > 0 ? 0.5 * (double)s_med[0] + 0.5 * (double)s_med[1] : 0.0;  // mmm.py:121
-    double a = 0.0, qq = 0.0;
+    double skymid = 0.0;
+    if (nvalid > 0) skymid = 0.5 * (double)__ldcg(dst + (nvalid - 1) / 2) + 0.5 * (double)__ldcg(dst + nvalid / 2);  // mmm.py:121
+    const int e0 = tid * K;
+    constexpr int H = K > 16 ? 16 : K;  // keys of this thread in its first index group
+    double a = 0.0, qq = 0.0, ha = 0.0, hq = 0.0;
 #pragma unroll
     for (int q = 0; q < K; q++) {
+        if (q == H) { ha = a; hq = qq; }  // K = 32: sums of the first group
         if (e0 + q < nvalid) {
             const double d = (double)r[q] - skymid;
             a = a + d;
-            qq = qq + d * d;
+            qq = __fma_rn(d, d, qq);
         }
     }
     // inclusive scan over the threads of the warp, then over the warps
@@ -576,9 +579,22 @@ BP_D void sort_index(const AperParams& P, const T (&r)[K], int nvalid, size_t ro
     __syncthreads();
     double ba = 0.0, bq = 0.0;
     for (int w = 0; w < warp; w++) { ba = ba + s_wsum[w][0]; bq = bq + s_wsum[w][1]; }
-    PT[tid] = make_double2(ba + xa, bq + xq);
-    bmin[tid] = r[0];
-    if (tid == nthr - 1) PT[nthr] = make_double2(ba + ia_, bq + iq_);
+    const double pa = ba + xa, pq = bq + xq;  // sums over keys [0, e0)
+    if constexpr (K == 32) {
+        PT[2 * tid] = make_double2(pa, pq);
+        PT[2 * tid + 1] = make_double2(pa + ha, pq + hq);
+        L2[2 * tid] = r[0];
+        L2[2 * tid + 1] = r[16];
+        if ((tid & 7) == 0) L1[tid >> 3] = r[0];
+    } else if constexpr (K == 16) {
+        PT[tid] = make_double2(pa, pq);
+        L2[tid] = r[0];
+        if ((tid & 15) == 0) L1[tid >> 4] = r[0];
+    } else {
+        if ((tid & 1) == 0) { PT[tid >> 1] = make_double2(pa, pq); L2[tid >> 1] = r[0]; }
+        if ((tid & 31) == 0) L1[tid >> 5] = r[0];
+    }
+    if (tid == nthr - 1) PT[nthr * K / 16] = make_double2(ba + ia_, bq + iq_);
 }
 
 // ------------------------------------------------------------ the two stages
@@ -604,7 +620,6 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S
     int* rowoff = span + 4 * P.span_rows;
     __shared__ int s_ntot;
     __shared__ int s_nrej[AP_WARPS], s_nnan[AP_WARPS];
-    __shared__ T s_med[2];
     __shared__ double s_wsum[AP_WARPS][2];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = (int)(blockDim.x >> 5);
@@ -689,7 +704,7 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S
                         else *reinterpret_cast<double2*>(dst + e) = make_double2(r[q], r[q + 1]);
                     }
                 }
-                if (P.sidx) sort_index<T, K>(P, r, nvalid, (size_t)(i - P.s0), tid, s_med, s_wsum);
+                if (P.sidx) sort_index<T, K>(P, r, dst, nvalid, (size_t)(i - P.s0), tid, s_wsum);
             } else {
                 int m = 2;
                 while (m < nslots) m <<= 1;
@@ -808,14 +823,17 @@ __global__ void __launch_bounds__(AP_THREADS) aper_mmm_kernel(const AperParams P
             IndexedView<T> V;
             const unsigned char* base = reinterpret_cast<const unsigned char*>(P.sidx) + (size_t)j * (size_t)P.idx_stride;
             V.k = skeys + (size_t)j * P.sstride;
-            V.PT = reinterpret_cast<const double*>(base);
-            V.bmin = reinterpret_cast<const T*>(base + (size_t)(AP_THREADS + 1) * 16);
-            V.gs = P.idx_gs;
+            V.L1 = reinterpret_cast<const T*>(base);
+            V.L2 = V.L1 + 16;
+            V.PT = reinterpret_cast<const double*>(V.L2 + 256);
             V.n = status;
             V.skymid = status > 0 ? 0.5 * V((status - 1) / 2) + 0.5 * V(status / 2) : 0.0;
             const MmmResult R = mmm_sorted(
                 V, [&](int lo, int hi, double, double* s1, double* s2) { V.delta_sums(lo, hi, s1, s2); },
-                [&](int lo, int hi) { return V.plain_sum(lo, hi); }, [&](double v, bool strict) { return V.first(v, strict); },
+                [&](int lo, int hi) { return V.plain_sum(lo, hi); },
+                [&](double v1, bool st1, bool need1, double v2, bool st2, bool need2, int* r1, int* r2) {
+                    V.first2(v1, st1, need1, v2, st2, need2, r1, r2);
+                },
                 status, P.readnoise, P.minsky, P.mxiter);
             skymod = R.skymod; skysig = R.sigma; iters = R.iters;
         }

@@ -152,6 +152,29 @@ long long annulus_bound(double rin, double rout) {
     return (long long)((area < box ? area : box) + 8.);
 }
 
+// Upper bound on the number of pixel centres strictly inside a disc of radius r, for ANY position of its centre: the
+// centre's offset inside its pixel is cut into 16 x 16 cells and a lattice point counts for a cell if it is within r of
+// the nearest point of the cell.  Rigorous (every centre lies in some cell) and within ~2 of the true maximum
+// (82 for r = 5, true 81; the area bound pi (r + sqrt 2 / 2)^2 + 8 gave 110), which is what sizes the fit kernels'
+// per-warp shared-memory lists.
+int disc_lattice_bound(double r) {
+    const int R = (int)ceil(r) + 1, NC = 16;
+    const double h = 1.0 / NC, rr = r * r * (1.0 + 1e-12);
+    int best = 0;
+    for (int a = 0; a < NC; a++)
+        for (int b = 0; b < NC; b++) {
+            const double x0 = a * h, x1 = x0 + h, y0 = b * h, y1 = y0 + h;
+            int c = 0;
+            for (int i = -R; i <= R + 1; i++)
+                for (int j = -R; j <= R + 1; j++) {
+                    const double dx = i < x0 ? x0 - i : (i > x1 ? i - x1 : 0.0), dy = j < y0 ? y0 - j : (j > y1 ? j - y1 : 0.0);
+                    if (dx * dx + dy * dy < rr) c++;
+                }
+            if (c > best) best = c;
+        }
+    return best;
+}
+
 // ---- visiting order: stars sorted by the 32x32-pixel image tile they sit in (tile rows outermost).
 // Neighbouring CTAs then read overlapping stamps, so stamp reads hit L1/L2 instead of DRAM: a random
 // star order costs ~27 KB of DRAM reads per star at skyrad=[40,50], tile order about 1 KB.
@@ -346,7 +369,7 @@ int bphot_version(void) { return BPHOT_VERSION; }
 const char* bphot_build_flags(void) {
     return "AP_ASM_SELECT=" BP_STR(AP_ASM_SELECT) " AP_BATCH=" BP_STR(AP_BATCH) " AP_S1_CTAS=" BP_STR(AP_S1_CTAS) " AP_MMM_INDEXED=" BP_STR(AP_MMM_INDEXED)
            " AP_S2_MINB=" BP_STR(AP_S2_MINB) " AP_SUMS_CTAS=" BP_STR(AP_SUMS_CTAS) " AP_DYNAMIC=" BP_STR(AP_DYNAMIC)
-           " PK_MINB_FORCED=" BP_STR(PK_MINB_FORCED) " PK_U=" BP_STR(PK_U);
+           " PK_MINB_FORCED=" BP_STR(PK_MINB_FORCED) " PK_U=" BP_STR(PK_U) " PK_HOIST=" BP_STR(PK_HOIST);
 }
 const char* bphot_last_error(void) { return g_err; }
 long long bphot_launch_count(void) { return g_launches.load(); }
@@ -420,7 +443,7 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
         return fail(BPHOT_ERR_CAPACITY, "bphot_aper: sky annulus [%g,%g] needs %zu B of shared memory per star (limit %d)",
                     skyrad_in, skyrad_out, smem, d.smem_optin);
     // scratch rows of sorted annulus keys (stage 1 -> stage 2), one batch of stars at a time
-    P.sstride = (bound + 7) / 8 * 8;
+    P.sstride = (bound + 15) / 16 * 16;  // rows are 64-byte aligned: the indexed mmm reads aligned groups of 16 keys
     const int batch = nstars < APER_BATCH ? nstars : APER_BATCH;
     cudaStream_t st = (cudaStream_t)stream;
     rc = ensure_log10_table(st);
@@ -430,7 +453,6 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     const bool indexed = AP_MMM_INDEXED && K > 0 && !use_setsky && !P.sky_sigclip;
     const size_t keys_bytes = ((size_t)batch * P.sstride * es + 255) & ~(size_t)255;
     P.idx_stride = indexed ? (long long)sort_index_bytes(es) : 0;
-    P.idx_gs = K == 8 ? 3 : K == 16 ? 4 : 5;
     if (!use_setsky) CU_TRY(cudaMallocAsync(&scratch, keys_bytes + (size_t)batch * (size_t)P.idx_stride, st));
     P.skeys = scratch;
     P.sidx = indexed ? (void*)(reinterpret_cast<char*>(scratch) + keys_bytes) : nullptr;
@@ -585,11 +607,7 @@ int bphot_pkfit_device(int variant, const void* d_image, int image_dtype,
     P.psf = d_psf; P.npsf = npsf; P.ronois = ronois; P.phpadu = phpadu; P.radius = radius;
     P.maxiter = maxiter; P.recenter = recenter ? 1 : 0;
     P.scale = d_scale; P.x = d_x; P.y = d_y; P.sky = d_sky; P.nstars = nstars;
-    {   // pixel centres with (dx^2+dy^2) < radius^2: unit cells lie inside a disc of radius + sqrt(2)/2
-        const double rr = radius + 0.70710678118654757;
-        long long c = (long long)(M_PI * rr * rr + 8.);
-        P.cap = (int)((c + 7) / 8 * 8);  // lists are indexed q < ngood, nothing reads a whole 32-slot chunk
-    }
+    P.cap = (disc_lattice_bound(radius) + 7) / 8 * 8;  // lists are indexed q < ngood, nothing reads a whole 32-slot chunk
     P.errmag = d_errmag; P.chi = d_chi; P.sharp = d_sharp; P.niter = d_niter;
     P.scale_out = d_scale_out; P.x_out = d_x_out; P.y_out = d_y_out; P.chi2 = d_chi2;
     P.acap = 2 * (int)ceil(radius) + 4;  // int(x+r)+1 - int(x-r) + 1 <= 2r + 3

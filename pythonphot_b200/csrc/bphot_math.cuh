@@ -21,9 +21,11 @@
 #define BP_HD __host__ __device__ __forceinline__
 #define BP_D __device__ __forceinline__
 #define BP_HDM __host__ __device__ __forceinline__  // member functions
+#define BP_HD_COLD __host__ __device__ __noinline__
 #else
 #define BP_HD static inline
 #define BP_HDM inline
+#define BP_HD_COLD static
 #endif
 
 namespace bphot {
@@ -218,47 +220,11 @@ BP_HD double psf_value(double xx, double yy, const double* gauss, const double* 
 }
 
 // ------------------------------------------------------------ 3x3 inverse
-// What scipy.linalg.inv does to the normal matrix: Cholesky (potrf + potri) when the matrix is
-// symmetric and positive definite, LU with partial pivoting (getrf + getri) otherwise.
-// Returns 0 on success, 1 when singular (scipy raises LinAlgError -> the fit returns NaN).
-BP_HD int inv3(double c[3][3]) {
-    bool sym = (c[0][1] == c[1][0]) && (c[0][2] == c[2][0]) && (c[1][2] == c[2][1]);
-    if (sym) {
-        double l00, l10, l20, l11, l21, l22;
-        double s = c[0][0];
-        if (s > 0.0) {
-            l00 = sqrt(s);
-            l10 = c[1][0] / l00;
-            l20 = c[2][0] / l00;
-            s = c[1][1] - l10 * l10;
-            if (s > 0.0) {
-                l11 = sqrt(s);
-                l21 = (c[2][1] - l20 * l10) / l11;
-                s = c[2][2] - l20 * l20;
-                s = s - l21 * l21;
-                if (s > 0.0) {
-                    l22 = sqrt(s);
-                    // M = inv(L), lower triangular; inv(A) = M^T M
-                    const double m00 = 1.0 / l00, m11 = 1.0 / l11, m22 = 1.0 / l22;
-                    const double m10 = -(l10 * m00) / l11;
-                    const double m21 = -(l21 * m11) / l22;
-                    double t = 0.0 + l20 * m00;
-                    t = t + l21 * m10;
-                    const double m20 = -t / l22;
-                    double a00 = 0.0 + m00 * m00; a00 = a00 + m10 * m10; a00 = a00 + m20 * m20;
-                    double a01 = 0.0 + m10 * m11; a01 = a01 + m20 * m21;
-                    const double a02 = 0.0 + m20 * m22;
-                    double a11 = 0.0 + m11 * m11; a11 = a11 + m21 * m21;
-                    const double a12 = 0.0 + m21 * m22;
-                    const double a22 = 0.0 + m22 * m22;
-                    c[0][0] = a00; c[0][1] = a01; c[0][2] = a02;
-                    c[1][0] = a01; c[1][1] = a11; c[1][2] = a12;
-                    c[2][0] = a02; c[2][1] = a12; c[2][2] = a22;
-                    return 0;
-                }
-            }
-        }
-    }
+// The general case of inv3 (getrf + getri), on a flat copy of the matrix.  Normal matrices of a fit are symmetric positive
+// definite, so this is the cold path: out of line on the device, where its ~400 unrolled instructions would otherwise sit
+// in the middle of the fit loop (the loop's code footprint is what the fit warps stall on).
+BP_HD_COLD int inv3_lu(double* c9) {
+    double (*c)[3] = reinterpret_cast<double (*)[3]>(c9);
     // LU with partial pivoting, then inv(U) and the getri back-substitution.
     double a[3][3];
     int piv[3];
@@ -303,6 +269,54 @@ BP_HD int inv3(double c[3][3]) {
     return 0;
 }
 
+// What scipy.linalg.inv does to the normal matrix: Cholesky (potrf + potri) when the matrix is
+// symmetric and positive definite, LU with partial pivoting (getrf + getri) otherwise.
+// Returns 0 on success, 1 when singular (scipy raises LinAlgError -> the fit returns NaN).
+BP_HD int inv3(double c[3][3]) {
+    bool sym = (c[0][1] == c[1][0]) && (c[0][2] == c[2][0]) && (c[1][2] == c[2][1]);
+    if (sym) {
+        double l00, l10, l20, l11, l21, l22;
+        double s = c[0][0];
+        if (s > 0.0) {
+            l00 = sqrt(s);
+            l10 = c[1][0] / l00;
+            l20 = c[2][0] / l00;
+            s = c[1][1] - l10 * l10;
+            if (s > 0.0) {
+                l11 = sqrt(s);
+                l21 = (c[2][1] - l20 * l10) / l11;
+                s = c[2][2] - l20 * l20;
+                s = s - l21 * l21;
+                if (s > 0.0) {
+                    l22 = sqrt(s);
+                    // M = inv(L), lower triangular; inv(A) = M^T M
+                    const double m00 = 1.0 / l00, m11 = 1.0 / l11, m22 = 1.0 / l22;
+                    const double m10 = -(l10 * m00) / l11;
+                    const double m21 = -(l21 * m11) / l22;
+                    double t = 0.0 + l20 * m00;
+                    t = t + l21 * m10;
+                    const double m20 = -t / l22;
+                    double a00 = 0.0 + m00 * m00; a00 = a00 + m10 * m10; a00 = a00 + m20 * m20;
+                    double a01 = 0.0 + m10 * m11; a01 = a01 + m20 * m21;
+                    const double a02 = 0.0 + m20 * m22;
+                    double a11 = 0.0 + m11 * m11; a11 = a11 + m21 * m21;
+                    const double a12 = 0.0 + m21 * m22;
+                    const double a22 = 0.0 + m22 * m22;
+                    c[0][0] = a00; c[0][1] = a01; c[0][2] = a02;
+                    c[1][0] = a01; c[1][1] = a11; c[1][2] = a12;
+                    c[2][0] = a02; c[2][1] = a12; c[2][2] = a22;
+                    return 0;
+                }
+            }
+        }
+    }
+    double t[9];
+    for (int i = 0; i < 9; i++) t[i] = c[i / 3][i % 3];
+    const int st = inv3_lu(t);
+    for (int i = 0; i < 9; i++) c[i / 3][i % 3] = t[i];
+    return st;
+}
+
 // ------------------------------------------------------------------- mmm
 // Sorted-vector searches.  `at(i)` widens element i to double.
 template <typename Get>
@@ -325,54 +339,50 @@ BP_HD int upper_bound_gt(const Get& at, int n, double v) {  // first i with at(i
 }
 
 // mmm.py:199-215: where the one-index-at-a-time walk of the LOWER edge stops.  `minimm` is the
-// index just below the accepted set (may be -1).  Returns the new minimm; *moved = false when
-// the reference takes its "done" shortcut and leaves sum/sumsq untouched.
-// The walk stops at the first index i (stepping from minimm) with i == -1, i == nlast, or
-// at(i) <= cut1 <= at(i+1); in a sorted vector those i form [lb-1, ub-1], where
-// lb = first(cut1, false) and ub = first(cut1, true):
+// index just below the accepted set (may be -1).  The walk stops at the first index i (stepping from minimm)
+// with i == -1, i == nlast, or at(i) <= cut1 <= at(i+1); in a sorted vector those i form [lb-1, ub-1]
+// (SURVEY App. A), where lb = first(cut1, false) and ub = first(cut1, true):
 //   first(v, strict) = index of the first element > v (strict) or >= v (not strict), nsky if none.
-template <typename Get, typename First>
-BP_HD int mmm_walk_min(const Get& at, const First& first, int nsky, int minimm, double cut1, bool* moved, bool* grew) {
-    const int nlast = nsky - 1;
-    const bool tst_min = at(minimm + 1) >= cut1;
-    *grew = tst_min;
-    bool done = (minimm == -1) && tst_min;
-    if (!done) {
-        const int k = minimm > 0 ? minimm : 0;
-        if (at(k) < cut1 && tst_min) done = true;
-    }
-    *moved = !done;
-    if (done) return minimm;
-    const int e = first(cut1, tst_min) - 1;
+// The walk is split in two so that the searches of both edges can be issued together (one thread per star waits
+// for memory, not for arithmetic): *_pre reads the two keys next to the edge and decides whether the reference
+// takes its "done" shortcut (sum / sumsq untouched) and in which direction the edge moves; *_post turns the
+// search result e = first(cut, ...) - 1 into the new edge.
+struct MmmEdge {
+    bool tst;   // mmm.py:199 tst_min / mmm.py:224 tst_max: the edge grows outward
+    bool done;  // the reference leaves this edge where it is
+};
+template <typename Get>
+BP_HD MmmEdge mmm_min_pre(const Get& at, int minimm, double cut1) {
+    const double a = at(minimm + 1), b = at(minimm > 0 ? minimm : 0);
+    MmmEdge E;
+    E.tst = a >= cut1;
+    E.done = E.tst && ((minimm == -1) || (b < cut1));
+    return E;
+}
+BP_HD int mmm_min_post(int nsky, int minimm, bool tst_min, int e) {  // e = first(cut1, tst_min) - 1
     if (tst_min) {  // grow downward: first i <= minimm-1 inside the bracket set, else -1
         const int r = e < (minimm - 1) ? e : (minimm - 1);
         return r < -1 ? -1 : r;
     }
-    // shrink upward: first i >= minimm+1 inside the bracket set, else nlast
-    const int r = e > (minimm + 1) ? e : (minimm + 1);
-    return r > nlast ? nlast : r;
+    const int r = e > (minimm + 1) ? e : (minimm + 1);  // shrink upward, else nlast
+    return r > nsky - 1 ? nsky - 1 : r;
 }
-
 // mmm.py:224-241: the UPPER edge.  `maximm` is the last accepted index.
-template <typename Get, typename First>
-BP_HD int mmm_walk_max(const Get& at, const First& first, int nsky, int maximm, double cut2, bool* moved, bool* grew) {
+template <typename Get>
+BP_HD MmmEdge mmm_max_pre(const Get& at, int nsky, int maximm, double cut2) {
     const int nlast = nsky - 1;
-    const bool tst_max = at(maximm) <= cut2;
-    *grew = tst_max;
-    bool done = (maximm == nlast) && tst_max;
-    if (!done) {
-        const int k = (maximm + 1 < nlast) ? maximm + 1 : nlast;
-        if (tst_max && at(k) > cut2) done = true;
-    }
-    *moved = !done;
-    if (done) return maximm;
-    const int e = first(cut2, !tst_max) - 1;
+    const double a = at(maximm), b = at((maximm + 1 < nlast) ? maximm + 1 : nlast);
+    MmmEdge E;
+    E.tst = a <= cut2;
+    E.done = E.tst && ((maximm == nlast) || (b > cut2));
+    return E;
+}
+BP_HD int mmm_max_post(int nsky, int maximm, bool tst_max, int e) {  // e = first(cut2, !tst_max) - 1
     if (tst_max) {  // grow upward
         const int r = e > (maximm + 1) ? e : (maximm + 1);
-        return r > nlast ? nlast : r;
+        return r > nsky - 1 ? nsky - 1 : r;
     }
-    // shrink downward
-    const int r = e < (maximm - 1) ? e : (maximm - 1);
+    const int r = e < (maximm - 1) ? e : (maximm - 1);  // shrink downward
     return r < -1 ? -1 : r;
 }
 
@@ -380,7 +390,8 @@ BP_HD int mmm_walk_max(const Get& at, const First& first, int nsky, int maximm, 
 //   at(i)                         element i widened to double
 //   delta_sums(lo, hi, mid, &a, &q)  a = sum(at(i)-mid), q = sum((at(i)-mid)^2) over [lo, hi)
 //   plain_sum(lo, hi)             sum(at(i)) over [lo, hi)
-//   first(v, strict)              first index with at(i) > v (strict) / at(i) >= v (nsky if none)
+//   first2(v1, strict1, need1, v2, strict2, need2, &r1, &r2)   two rank queries at once: r = first index with
+//                                 at(i) > v (strict) / at(i) >= v, nsky if none; a query with need = false is skipped
 // The functors let a whole warp share the reductions on the device (every lane must receive the same
 // bits) and a plain loop stand in on the host (tests/hostcheck).  Failure modes keep the reference's
 // in-band codes (sigma = -1).
@@ -420,73 +431,103 @@ BP_HD void bp_ld2(const double* p, double* x, double* y) {  // p is 16-byte alig
 #endif
 }
 
-// Sorted vector + its block index (aper_kernel.cu sort_index builds it), read by ONE thread: keys k[0..n), per block b of
-// 1 << gs keys the first key bmin[b] and the exclusive prefix sums PT[2b], PT[2b+1] of d = key - skymid and d^2.
+// Sorted vector + its index (aper_kernel.cu sort_index builds it), read by ONE thread.  Keys k[0..n) in a 64-byte
+// aligned row; L2[j] = k[16 j] and L1[i] = k[256 i] (a 16-ary search tree laid out so that every node is one aligned
+// 64-byte group); PT[2g], PT[2g+1] = sums over keys [0, 16 g) of d = key - skymid and d^2.  Everything a thread needs
+// per step is a handful of INDEPENDENT aligned 16-key groups, so the loads of one step are in flight together.
 template <typename T>
 struct IndexedView {
     const T* __restrict__ k;
-    const double* __restrict__ PT;  // (sum d, sum d^2) pairs
-    const T* __restrict__ bmin;
-    int gs, n;  // block size = 1 << gs keys; n valid keys
+    const T* __restrict__ L1;
+    const T* __restrict__ L2;
+    const double* __restrict__ PT;
+    int n;
     double skymid;
     BP_HDM double operator()(int i) const { return (double)bp_ld(k + i); }
-    // sums of d and d^2 over keys [0, i): the nearer block boundary's prefix, then at most K/2 keys
-    BP_HDM void prefix(int i, double* s1, double* s2) const {
-        const int b = i >> gs, start = b << gs, G = 1 << gs;
-        if (2 * (i - start) <= G) {
-            double a, q;
-            bp_ld2(PT + 2 * b, &a, &q);
-            for (int j = start; j < i; j++) { const double d = (double)bp_ld(k + j) - skymid; a = a + d; q = q + d * d; }
-            *s1 = a; *s2 = q;
+    BP_HDM static void load16(const T* p, double (&v)[16]) {
+#if defined(__CUDA_ARCH__)
+        if constexpr (sizeof(T) == 4) {
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const float4 f = __ldg(reinterpret_cast<const float4*>(p) + q);
+                v[4 * q] = (double)f.x; v[4 * q + 1] = (double)f.y; v[4 * q + 2] = (double)f.z; v[4 * q + 3] = (double)f.w;
+            }
         } else {
-            double a, q;
-            bp_ld2(PT + 2 * (b + 1), &a, &q);
-            const int end = (start + G) < n ? (start + G) : n;
-            for (int j = i; j < end; j++) { const double d = (double)bp_ld(k + j) - skymid; a = a - d; q = q - d * d; }
-            *s1 = a; *s2 = q;
+#pragma unroll
+            for (int q = 0; q < 8; q++) {
+                const double2 f = __ldg(reinterpret_cast<const double2*>(p) + q);
+                v[2 * q] = f.x; v[2 * q + 1] = f.y;
+            }
         }
+#else
+        for (int q = 0; q < 16; q++) v[q] = (double)p[q];
+#endif
+    }
+    // sums of d and d^2 over keys [0, i): the prefix at the group boundary below i, then the group's first i % 16 keys
+    BP_HDM void prefix(int i, double* s1, double* s2) const {
+        const int g = i >> 4, c = i & 15;
+        double a, q;
+        bp_ld2(PT + 2 * g, &a, &q);
+        if (c) {
+            double v[16];
+            load16(k + 16 * g, v);
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+            for (int j = 0; j < 15; j++)
+                if (j < c) { const double d = v[j] - skymid; a = a + d; q = q + d * d; }
+        }
+        *s1 = a; *s2 = q;
     }
     BP_HDM void delta_sums(int lo, int hi, double* s1, double* s2) const {
-        if (hi - lo <= (1 << gs)) {
-            double a = 0.0, q = 0.0;
-            for (int j = lo; j < hi; j++) { const double d = (double)bp_ld(k + j) - skymid; a = a + d; q = q + d * d; }
-            *s1 = a; *s2 = q;
-        } else {
-            double a1, q1, a0, q0;
-            prefix(hi, &a1, &q1);
-            prefix(lo, &a0, &q0);
-            *s1 = a1 - a0; *s2 = q1 - q0;
-        }
+        double a1, q1, a0, q0;
+        prefix(hi, &a1, &q1);
+        prefix(lo, &a0, &q0);
+        *s1 = a1 - a0; *s2 = q1 - q0;
     }
     BP_HDM double plain_sum(int lo, int hi) const {
         if (hi <= lo) return 0.0;
-        if (hi - lo <= (1 << gs)) {
-            double a = 0.0;
-            for (int j = lo; j < hi; j++) a = a + (double)bp_ld(k + j);
-            return a;
-        }
         double a1, q1, a0, q0;
         prefix(hi, &a1, &q1);
         prefix(lo, &a0, &q0);
         return (a1 - a0) + (double)(hi - lo) * skymid;
     }
-    // first index with key > v (strict) or key >= v, n if none: bmin picks the block, then a search inside it
-    BP_HDM int first(double v, bool strict) const {
-        const int G = 1 << gs, nb = (n + G - 1) >> gs;
-        int lo = 0, hi = nb;
-        while (lo < hi) {
-            const int mid = (lo + hi) >> 1;
-            const double a = (double)bp_ld(bmin + mid);
-            if (strict ? a > v : a >= v) hi = mid; else lo = mid + 1;
+    // number of entries t = t0 .. 15 of the aligned group at p that exist (t < limit) and FAIL the predicate
+    BP_HDM static int count_fail(const T* p, int t0, int limit, double v, bool strict) {
+        double x[16];
+        load16(p, x);
+        int c = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int t = 0; t < 16; t++) c += (t >= t0 && t < limit && !(strict ? x[t] > v : x[t] >= v)) ? 1 : 0;
+        return c;
+    }
+    // Two rank queries in lockstep (first index with key > v / key >= v, n if none): the failing entries of a sorted
+    // node are a prefix, so their COUNT is the child to descend into -- three levels, three aligned groups per query.
+    BP_HDM void first2(double v1, bool st1, bool need1, double v2, bool st2, bool need2, int* r1, int* r2) const {
+        const int n1 = (n + 255) >> 8, n2 = (n + 15) >> 4;
+        int c1a = 0, c1b = 0;
+        {
+            double x[16];
+            load16(L1, x);
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+            for (int t = 0; t < 16; t++) {
+                c1a += (t < n1 && !(st1 ? x[t] > v1 : x[t] >= v1)) ? 1 : 0;
+                c1b += (t < n1 && !(st2 ? x[t] > v2 : x[t] >= v2)) ? 1 : 0;
+            }
         }
-        if (lo == 0) return 0;
-        int l = ((lo - 1) << gs) + 1, h = (lo << gs) < n ? (lo << gs) : n;  // key[(lo-1)*G] fails, key[lo*G] passes
-        while (l < h) {
-            const int mid = (l + h) >> 1;
-            const double a = (double)bp_ld(k + mid);
-            if (strict ? a > v : a >= v) h = mid; else l = mid + 1;
-        }
-        return l;
+        const bool go1 = need1 && c1a > 0, go2 = need2 && c1b > 0;  // c1 == 0: key[0] passes, the answer is 0
+        const int g1 = 16 * (c1a - 1), g2 = 16 * (c1b - 1);         // L2 group whose entry 0 is the last failing L1 key
+        int j1 = 0, j2 = 0;
+        if (go1) j1 = g1 + count_fail(L2 + g1, 1, n2 - g1, v1, st1);
+        if (go2) j2 = g2 + count_fail(L2 + g2, 1, n2 - g2, v2, st2);
+        int f1 = 0, f2 = 0;                                         // k[16 j] is the last failing L2 key
+        if (go1) f1 = 16 * j1 + 1 + count_fail(k + 16 * j1, 1, n - 16 * j1, v1, st1);
+        if (go2) f2 = 16 * j2 + 1 + count_fail(k + 16 * j2, 1, n - 16 * j2, v2, st2);
+        *r1 = f1; *r2 = f2;
     }
 };
 
@@ -496,8 +537,8 @@ struct MmmResult {
 };
 BP_HD double mmm_nan() { return (double)NAN; }
 
-template <typename Get, typename DSums, typename PSum, typename First>
-BP_HD MmmResult mmm_sorted(const Get& at, const DSums& delta_sums, const PSum& plain_sum, const First& first,
+template <typename Get, typename DSums, typename PSum, typename First2>
+BP_HD MmmResult mmm_sorted(const Get& at, const DSums& delta_sums, const PSum& plain_sum, const First2& first2,
                            int nsky, double readnoise, int minsky, int mxiter) {
     MmmResult R;
     R.iters = 0;
@@ -515,8 +556,9 @@ BP_HD MmmResult mmm_sorted(const Get& at, const DSums& delta_sums, const PSum& p
         cut2 = skymid + c;
         cut1 = skymid - c;
     }
-    const int gmin = first(cut1, false);
-    const int gmax = first(cut2, true) - 1;
+    int gmin = 0, gmax = 0;
+    first2(cut1, false, true, cut2, true, true, &gmin, &gmax);
+    gmax = gmax - 1;
     if (gmin > gmax) {  // mmm.py:134-138
         R.skymod = 0.0; R.sigma = -1.0;
         return R;
@@ -546,12 +588,14 @@ BP_HD MmmResult mmm_sorted(const Get& at, const DSums& delta_sums, const PSum& p
         cut1 = skymod - cut;
         cut2 = skymod + cut;
         redo = false;
-        bool moved, grew;
         // mmm.py:199-248: both edges.  The upper walk reads only the vector, maximm and cut2, so it
         // can be taken before the lower edge's sums are applied; the sums then share one call site.
-        bool moved1, grew1;
-        const int newmin = mmm_walk_min(at, first, nsky, minimm, cut1, &moved, &grew);
-        const int newmax = mmm_walk_max(at, first, nsky, maximm, cut2, &moved1, &grew1);
+        const MmmEdge E0 = mmm_min_pre(at, minimm, cut1), E1 = mmm_max_pre(at, nsky, maximm, cut2);
+        int e0 = 0, e1 = 0;
+        first2(cut1, E0.tst, !E0.done, cut2, !E1.tst, !E1.done, &e0, &e1);
+        const int newmin = E0.done ? minimm : mmm_min_post(nsky, minimm, E0.tst, e0 - 1);
+        const int newmax = E1.done ? maximm : mmm_max_post(nsky, maximm, E1.tst, e1 - 1);
+        const bool moved = !E0.done, grew = E0.tst, moved1 = !E1.done, grew1 = E1.tst;
 #if defined(__CUDA_ARCH__)
 #pragma unroll 1
 #endif

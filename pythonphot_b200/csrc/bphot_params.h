@@ -36,7 +36,6 @@ struct AperParams {
     // index of each sorted row for the thread-per-star mmm (aper_kernel.cu sort_index): null = not built
     void* sidx;
     long long idx_stride;  // bytes per star
-    int idx_gs;            // log2 of the index block size (= keys per stage-1 thread)
     int span_rows;  // rows of the per-CTA column-span table (>= stamp height)
     const int* order;  // visiting order of the stars (image-tile sorted), or null
     // outputs

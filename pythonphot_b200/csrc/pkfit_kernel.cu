@@ -48,7 +48,10 @@ BP_D double pk_max(double v) { return warp_max(v); }
 constexpr int PK_WARPS = 4;
 constexpr int PK_THREADS = PK_WARPS * 32;
 constexpr int PK_NARR_FIT = 10;     // per-warp scratch arrays of `cap` doubles, recentring variants
-constexpr int PK_NARR_FORCED = 7;   // forced variant
+#ifndef PK_HOIST
+#define PK_HOIST 1  // forced fit: W0/sigsq and dfs*dfs/sigsq (operands fixed at set-up) are divided once per star, not per iteration
+#endif
+constexpr int PK_NARR_FORCED = PK_HOIST ? 9 : 7;   // forced variant
 
 struct FitOut {
     double errmag, chi, sharp, scale, x, y, chi2;
@@ -193,6 +196,13 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
     double* SIG = W + 4 * cap;     // noise-image value
     double* W0 = W + 5 * cap;      // radial weight 5/(5 + rsq/(1-rsq)), pkfit_norecent_noise.py:375
     double* DFS = W + 6 * cap;     // sharpness kernel exp(-rho/2)(rho/2 - 1) where rho <= 36, else NaN (:377-390)
+#if PK_HOIST
+    // Two of the loop's eight fp64 divisions per pixel have operands that never change between iterations
+    // (pkfit_norecent_noise.py:414 wt/sigsq and :393 dfdsig**2/sigsq): same operands, same quotient, so they are taken
+    // once at set-up.
+    double* WTR = W + 7 * cap;     // W0 / sigsq
+    double* DDS = W + 8 * cap;     // DFS * DFS / sigsq
+#endif
     const TI* __restrict__ img = reinterpret_cast<const TI*>(P.img);
     const TN* __restrict__ noise = reinterpret_cast<const TN*>(P.noise);
     const uint8_t* __restrict__ mask = P.mask;
@@ -240,7 +250,13 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
                 W0[q] = 5. / (5. + rsq / (1. - rsq));
                 const double rho = dxv * dxv / gx2 + dyv * dyv / gy2;  // :338
                 const double rh = 0.5 * rho;
-                DFS[q] = (rho <= 36.) ? exp(-rh) * (rh - 1.) : nan64();
+                const double dfsv = (rho <= 36.) ? exp(-rh) * (rh - 1.) : nan64();
+                DFS[q] = dfsv;
+#if PK_HOIST
+                const double ssq = nz * nz;
+                WTR[q] = W0[q] / ssq;
+                DDS[q] = dfsv * dfsv / ssq;
+#endif
                 // model inputs, consumed below once the dao_value guard is known
                 MV[q] = dxv; DVX[q] = dyv; DVY[q] = __longlong_as_double((long long)(r * 65536 + c));
                 xmin = fmin(xmin, dxv); xmax = fmax(xmax, dxv);
@@ -281,12 +297,12 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
         // take the pixels in list order (chunk by chunk), so every partial sum has the bits it had with one chunk per pass
         for (int base0 = 0; base0 < ngood; base0 += 32 * PK_U) {
             bool keep[PK_U], lil[PK_U];
-            double df[PK_U], rel[PK_U], sigsq[PK_U], t0[PK_U], dfs[PK_U], wt[PK_U], t1[PK_U], t2[PK_U], wtr[PK_U];
+            double df[PK_U], rel[PK_U], sigsq[PK_U], t0[PK_U], dfs[PK_U], wt[PK_U], t1[PK_U], t2[PK_U], wtr[PK_U], dds[PK_U];
 #pragma unroll
             for (int u = 0; u < PK_U; u++) {
                 const int q = base0 + 32 * u + lane;
                 keep[u] = false; lil[u] = false;
-                df[u] = 0.; rel[u] = 0.; sigsq[u] = 1.; t0[u] = 0.; dfs[u] = 0.; wt[u] = 0.; t1[u] = 0.; t2[u] = 0.; wtr[u] = 0.;
+                df[u] = 0.; rel[u] = 0.; sigsq[u] = 1.; t0[u] = 0.; dfs[u] = 0.; wt[u] = 0.; t1[u] = 0.; t2[u] = 0.; wtr[u] = 0.; dds[u] = 0.;
                 if (q < ngood) {
                     t0[u] = MV[q];
                     const double sg = SIG[q];
@@ -296,9 +312,16 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
                     sigsq[u] = sg * sg;
                     dfs[u] = DFS[q];
                     lil[u] = keep[u] && (dfs[u] == dfs[u]);
+#if PK_HOIST
+                    dds[u] = DDS[q];
+#endif
                     if (keep[u]) {
                         wt[u] = W0[q];
+#if PK_HOIST
+                        wtr[u] = WTR[q];
+#else
                         wtr[u] = wt[u] / sigsq[u];  // :414
+#endif
                         t1[u] = -S.scale * DVX[q];
                         t2[u] = -S.scale * DVY[q];
                     }
@@ -310,7 +333,11 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
                 const unsigned mk = __ballot_sync(FULL, keep[u]);
                 if (lil[u]) {  // :377-410
                     numer = numer + dfs[u] * df[u] / sigsq[u];
+#if PK_HOIST
+                    denom = denom + dds[u];
+#else
                     denom = denom + dfs[u] * dfs[u] / sigsq[u];
+#endif
                     s3 = s3 + df[u] * df[u] / sigsq[u];
                     nl++;
                 }

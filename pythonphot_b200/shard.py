@@ -8,7 +8,10 @@ path shards by star list and needs exactly two collectives, both outside the ker
   * each rank runs the ordinary single-GPU kernels on its contiguous shard of the tile-ordered star
     list and the fixed-width per-star result records are all-gathered (``ShardPlan.gather``).
 
-There is no collective inside a kernel, hence nothing to fuse.  The plumbing below is
+The kernels write their result columns straight into one byte arena per call (``ResultArena``: the columns are typed views
+of one flat buffer), so a pass costs ONE all-gather of that buffer -- no packing step -- and one indexed copy per column into
+caller order; ``gather_arena(..., side_stream=...)`` runs both on a side stream so that the next kernel (the PSF fits after
+``aper``) hides them.  There is no collective inside a kernel, hence nothing to fuse.  The plumbing below is
 ``torch.distributed`` only (NCCL on the GPU box; the same code runs under ``gloo`` with CPU tensors,
 which is how tests/test_shard_gloo.py covers it at world_size 2).  The N-GPU result equals the
 1-GPU result bit for bit after un-permuting, because every star's arithmetic is independent of
@@ -78,7 +81,14 @@ class ShardPlan(object):
         import torch
         key = (which, rank, str(device))
         if key not in self._dev:
-            idx = self.inverse if which == "inverse" else self.indices(rank)
+            if which == "inverse":
+                idx = self.inverse
+            elif which == "rank_of":  # which rank's shard holds star s, and where in it
+                idx = self.inverse // max(self.m, 1)
+            elif which == "pos_of":
+                idx = self.inverse % max(self.m, 1)
+            else:
+                idx = self.indices(rank)
             self._dev[key] = torch.from_numpy(np.ascontiguousarray(idx)).to(device)
         return self._dev[key]
 
@@ -122,6 +132,13 @@ class ShardPlan(object):
         return full.index_select(0, self._index_t("inverse", 0, full.device))
 
 
+def gather_arena(plan, arena, group=None, side_stream=None):
+    """All-gather a ``ResultArena`` (one NCCL ``all_gather_into_tensor`` of ``arena.nbytes`` per rank) and copy every column
+    into caller order.  With ``side_stream`` (CUDA) both run on that stream, after the work already queued on the current
+    one; the returned ``GatherHandle.result()`` joins.  Works on CPU tensors under gloo (tests)."""
+    return _gather_arena(plan, arena, group=group, side_stream=side_stream)
+
+
 def pack_records(columns):
     """Dict of per-star tensors ``[m]`` / ``[m, k]`` -> one ``[m, width]`` tensor PER DTYPE plus the layout needed
     to unpack, so that a pass costs one all-gather and one un-permute per dtype (fp64, int32, uint8) instead of
@@ -144,6 +161,93 @@ def unpack_records(packed, layout):
         block = packed[dtype]
         out[name] = block[:, start:start + width].reshape((block.shape[0],) + tail)
     return out
+
+
+class ResultArena(object):
+    """Per-star result columns of one shard as typed views of ONE flat byte buffer.
+
+    ``spec`` = [(name, torch dtype, tail shape)], ``m`` = stars in the shard.  The kernels are handed ``views`` as their
+    output tensors (``aper_device(out=...)``, ``PkfitEngine.fit_device(out=...)``), so nothing has to be packed before
+    the all-gather: ``flat`` is what travels.  Column offsets are 256-byte aligned."""
+
+    def __init__(self, spec, m, device):
+        import torch
+        self.spec = [(n_, dt, tuple(tail)) for n_, dt, tail in spec]
+        self.m, self.device = int(m), device
+        self.offsets, off = {}, 0
+        for name, dt, tail in self.spec:
+            nb = self.m * int(np.prod(tail, dtype=np.int64)) * torch.empty((), dtype=dt).element_size()
+            self.offsets[name] = (off, nb)
+            off += (nb + 255) // 256 * 256
+        self.nbytes = max(off, 256)
+        self.flat = torch.zeros(self.nbytes, dtype=torch.uint8, device=device)
+        self.views = {}
+        for name, dt, tail in self.spec:
+            o, nb = self.offsets[name]
+            self.views[name] = self.flat[o:o + nb].view(dt).view((self.m,) + tail)
+
+    @classmethod
+    def like(cls, results, device=None):
+        """Arena with one column per tensor of ``results`` (dict name -> [m, ...] tensor)."""
+        first = next(iter(results.values()))
+        spec = [(k, v.dtype, tuple(v.shape[1:])) for k, v in results.items()]
+        return cls(spec, first.shape[0], device if device is not None else first.device)
+
+    def store(self, results):
+        """Copy result tensors that are not already this arena's views into it."""
+        for k, v in results.items():
+            if v.data_ptr() != self.views[k].data_ptr():
+                self.views[k].copy_(v)
+        return self.views
+
+
+class GatherHandle(object):
+    """An all-gather + un-permute in flight; ``result()`` makes the current stream wait for it and returns the dict of
+    full-length tensors in the caller's star order."""
+
+    def __init__(self, outs, side_stream, device):
+        self._outs, self._side, self._device = outs, side_stream, device
+
+    def result(self):
+        if self._side is not None:
+            import torch
+            torch.cuda.current_stream(self._device).wait_stream(self._side)
+            self._side = None
+        return self._outs
+
+
+def _gather_arena(plan, arena, group=None, side_stream=None):
+    import torch
+    dist = _dist()
+    rank, world = world_info(group)
+    assert world == plan.world, "plan was made for %d ranks, group has %d" % (plan.world, world)
+    assert arena.m == plan.m, "arena has %d rows, shard has %d" % (arena.m, plan.m)
+    dev = arena.flat.device
+    use_side = side_stream is not None and dev.type == "cuda"
+    # buffers are allocated on the caller's stream; the side stream only uses them between wait_stream pairs
+    full = arena.flat.reshape(1, -1) if world == 1 else torch.empty((world, arena.nbytes), dtype=torch.uint8, device=dev)
+    ridx, pidx = plan._index_t("rank_of", 0, dev), plan._index_t("pos_of", 0, dev)
+    outs = {name: torch.empty((plan.n,) + tail, dtype=dt, device=dev) for name, dt, tail in arena.spec}
+
+    def work():
+        if world > 1:
+            dist.all_gather_into_tensor(full.reshape(-1), arena.flat, group=group)
+        for name, dt, tail in arena.spec:
+            o, nb = arena.offsets[name]
+            es = outs[name].element_size()
+            k = int(np.prod(tail, dtype=np.int64))
+            typed = full.reshape(-1).view(dt)
+            col = torch.as_strided(typed, (world, plan.m, k), (arena.nbytes // es, k, 1), o // es)  # [rank, star, component]
+            if plan.n:
+                outs[name].reshape(plan.n, k).copy_(col[ridx, pidx])  # row s <- (rank_of[s], pos_of[s])
+    if use_side:
+        cur = torch.cuda.current_stream(dev)
+        side_stream.wait_stream(cur)
+        with torch.cuda.stream(side_stream):
+            work()
+        return GatherHandle(outs, side_stream, dev)
+    work()
+    return GatherHandle(outs, None, dev)
 
 
 def broadcast_exposure(tensors, src=0, group=None):
@@ -176,27 +280,54 @@ def broadcast_columns(columns, n, device, src=0, group=None):
 def run_sharded(plan, columns, compute, group=None):
     """The generic sharded pass: ``columns`` = dict of full-length star-list columns (torch tensors on this
     rank's device, identical on every rank); ``compute(shard_columns) -> dict of per-star result tensors``
-    runs this rank's shard (on the GPU box: the CUDA kernels); the records are packed, all-gathered once
-    and returned as a dict of full-length tensors in the caller's star order."""
+    runs this rank's shard (on the GPU box: the CUDA kernels); the records go through a ``ResultArena`` (one all-gather)
+    and come back as a dict of full-length tensors in the caller's star order."""
     rank, _ = world_info(group)
     shard = {k: plan.take(v, rank) for k, v in columns.items()}
     res = compute(shard)
-    packed, layout = pack_records(res)
-    return unpack_records({dt: plan.gather(block, group=group) for dt, block in packed.items()}, layout)
+    arena = ResultArena.like(res)
+    arena.store(res)
+    return gather_arena(plan, arena, group=group).result()
+
+
+APER_SPEC = lambda torch, naper: [("mag", torch.float64, (naper,)), ("magerr", torch.float64, (naper,)),  # noqa: E731
+                                  ("flux", torch.float64, (naper,)), ("fluxerr", torch.float64, (naper,)),
+                                  ("sky", torch.float64, ()), ("skyerr", torch.float64, ()),
+                                  ("badflag", torch.uint8, (naper,)), ("nsky", torch.int32, ()), ("mmm_iter", torch.int32, ())]
+FIT_SPEC = lambda torch: [(k, torch.float64, ()) for k in ("errmag", "chi", "sharp", "scale", "x", "y", "chi2")] + \
+    [("niter", torch.int32, ())]  # noqa: E731
+
+
+def exposure_header(image_t, noise_t, mask_t):
+    """What the other ranks need to allocate their replica of the exposure."""
+    return {"shape": tuple(image_t.shape), "image_dtype": str(image_t.dtype), "noise_dtype": str(noise_t.dtype) if noise_t is not None else None,
+            "has_mask": mask_t is not None}
+
+
+def broadcast_header(header, src=0, group=None):
+    """``header`` (a small picklable object known on ``src``) -> the same object on every rank."""
+    dist = _dist()
+    _, world = world_info(group)
+    box = [header]
+    if world > 1:
+        dist.broadcast_object_list(box, src=src, group=group)
+    return box[0]
 
 
 class ShardedPhotometry(object):
     """One exposure replicated on every rank's GPU, star lists sharded (one process per GPU).
 
-    Every rank constructs it with the same shapes; only ``src`` needs to hold real pixel data
-    (numpy arrays or tensors), the other ranks may pass ``None`` plus ``shape``/``dtype``:
+    Only ``src`` needs to hold pixel data (numpy arrays or tensors); the other ranks pass ``None`` and learn shape,
+    dtypes and which of noise / mask exist from a header that ``src`` broadcasts first (a float64 image, or a plain
+    ``pkfit`` set-up without noise and mask, therefore cannot desynchronise the NCCL broadcasts):
 
-        sp = ShardedPhotometry(image, gauss, psf, ronois, phpadu, noise, mask, shape=(nrow, ncol))
+        sp = ShardedPhotometry(image, gauss, psf, ronois, phpadu, noise, mask)
         a = sp.aper(xc, yc, apr=np.array([3., 5., 8.]), skyrad=[40, 50], exact=True, ...)
         f = sp.fit('pkfit_noise', scale, x, y, a['sky'], radius=5)
 
     ``xc, yc ...`` must be identical on every rank (use ``broadcast_columns`` when only one rank has
-    them).  Results are dicts of CUDA tensors in the caller's star order, identical on every rank."""
+    them).  Results are dicts of CUDA tensors in the caller's star order, identical on every rank.
+    ``shape`` / ``image_dtype`` / ``with_noise`` are accepted for backward compatibility and checked against the header."""
 
     def __init__(self, image, gauss, psf, ronois, phpadu, noiseim=None, maskim=None, shape=None,
                  image_dtype=None, src=0, group=None, device=None, with_noise=None):
@@ -207,43 +338,68 @@ class ShardedPhotometry(object):
         self.rank, self.world = world_info(group)
         dev = _lib.device_of(device)
         self.device = dev
+        img_t = noise_t = mask_t = None
         if self.rank == src:
             img_t = _lib.to_device_image(image, dev)
             noise_t = _lib.to_device_image(noiseim, dev) if noiseim is not None else None
             mask_t = _lib.to_device_mask(maskim, dev) if maskim is not None else None
-        else:
-            if shape is None:
-                raise ValueError("ranks other than src need shape=(nrow, ncol)")
-            dt = torch.float32 if image_dtype in (None, "float32", np.float32, torch.float32) else torch.float64
-            has_noise = with_noise if with_noise is not None else True
-            img_t = torch.empty(tuple(shape), dtype=dt, device=dev)
-            noise_t = torch.empty(tuple(shape), dtype=dt, device=dev) if has_noise else None
-            mask_t = torch.empty(tuple(shape), dtype=torch.uint8, device=dev) if has_noise else None
+        hdr = broadcast_header(exposure_header(img_t, noise_t, mask_t) if self.rank == src else None, src=src, group=group)
+        if shape is not None and tuple(shape) != tuple(hdr["shape"]):
+            raise ValueError("shape=%r but the source rank holds a %r image" % (tuple(shape), tuple(hdr["shape"])))
+        if with_noise is not None and bool(with_noise) != (hdr["noise_dtype"] is not None):
+            raise ValueError("with_noise=%r disagrees with the source rank" % (with_noise,))
+        if self.rank != src:
+            dt = {"torch.float32": torch.float32, "torch.float64": torch.float64}
+            img_t = torch.empty(hdr["shape"], dtype=dt[hdr["image_dtype"]], device=dev)
+            noise_t = torch.empty(hdr["shape"], dtype=dt[hdr["noise_dtype"]], device=dev) if hdr["noise_dtype"] else None
+            mask_t = torch.empty(hdr["shape"], dtype=torch.uint8, device=dev) if hdr["has_mask"] else None
         broadcast_exposure([img_t, noise_t, mask_t], src=src, group=group)
         self.image_t = img_t
         self.engine = PkfitEngine(img_t, gauss, psf, ronois, phpadu, noise_t, mask_t, device=dev)
+        self._side = torch.cuda.Stream(device=dev)
 
     def plan(self, x, y):
         xh = x.cpu().numpy() if hasattr(x, "cpu") else np.asarray(x)
         yh = y.cpu().numpy() if hasattr(y, "cpu") else np.asarray(y)
         return ShardPlan.for_stars(xh, yh, self.image_t.shape[0], self.image_t.shape[1], self.world)
 
-    def aper(self, xc, yc, plan=None, **kw):
-        """Sharded ``aper.aper`` (aper.py:26-433): keywords as ``aper.aper_device``."""
+    def aper_async(self, xc, yc, plan=None, **kw):
+        """Sharded ``aper.aper`` (aper.py:26-433), keywords as ``aper.aper_device``.  Returns ``(shard_results, handle)``:
+        this rank's own result columns right away (device tensors, e.g. the sky a following fit needs) and a
+        ``GatherHandle`` whose all-gather + un-permute run on a side stream, hidden by whatever is launched next."""
         from . import _lib
         from .aper import aper_device
+        torch = _lib.torch_cuda()
         plan = plan or self.plan(xc, yc)
-        cols = {"x": _lib.to_device_f64(xc, self.device), "y": _lib.to_device_f64(yc, self.device)}
-        return run_sharded(plan, cols, lambda s: aper_device(self.image_t, s["x"], s["y"], **kw), group=self.group)
+        x_s = plan.take(_lib.to_device_f64(xc, self.device), self.rank)
+        y_s = plan.take(_lib.to_device_f64(yc, self.device), self.rank)
+        naper = _lib.host_f64(kw.get("apr", 5)).size
+        arena = ResultArena(APER_SPEC(torch, naper), plan.m, self.device)
+        aper_device(self.image_t, x_s, y_s, out=arena.views, **kw)
+        return arena.views, gather_arena(plan, arena, group=self.group, side_stream=self._side)
 
-    def fit(self, method, scale, x, y, sky, radius, maxiter=25, recenter=True, plan=None):
-        """Sharded ``pkfit`` / ``pkfit_noise`` / ``pkfit_norecent_noise`` over a star list."""
+    def aper(self, xc, yc, plan=None, **kw):
+        return self.aper_async(xc, yc, plan=plan, **kw)[1].result()
+
+    def fit_async(self, method, scale, x, y, sky, radius, maxiter=25, recenter=True, plan=None, sharded_inputs=None):
+        """Sharded ``pkfit`` / ``pkfit_noise`` / ``pkfit_norecent_noise``.  ``sharded_inputs`` = dict with this rank's shard
+        of any of scale / x / y / sky already on the device (e.g. ``aper_async``'s own ``sky`` column), which then are
+        not taken from the full-length arguments."""
         from . import _lib
+        torch = _lib.torch_cuda()
         variant = {"pkfit": _lib.PKFIT, "pkfit_noise": _lib.PKFIT_NOISE, "pkfit_norecent_noise": _lib.PKFIT_NORECENT}[method]
         plan = plan or self.plan(x, y)
-        x_t = _lib.to_device_f64(x, self.device)
-        n = x_t.numel()
-        cols = {"x": x_t, "y": _lib.to_device_f64(y, self.device, n), "scale": _lib.to_device_f64(scale, self.device, n),
-                "sky": _lib.to_device_f64(sky, self.device, n)}
-        return run_sharded(plan, cols, lambda s: self.engine.fit_device(variant, s["scale"], s["x"], s["y"], s["sky"], radius,
-                                                                        maxiter=maxiter, recenter=recenter), group=self.group)
+        n = plan.n
+        cols = {}
+        for name, full in (("scale", scale), ("x", x), ("y", y), ("sky", sky)):
+            if sharded_inputs and name in sharded_inputs:
+                cols[name] = sharded_inputs[name]
+            else:
+                cols[name] = plan.take(_lib.to_device_f64(full, self.device, n), self.rank)
+        arena = ResultArena(FIT_SPEC(torch), plan.m, self.device)
+        self.engine.fit_device(variant, cols["scale"], cols["x"], cols["y"], cols["sky"], radius, maxiter=maxiter,
+                               recenter=recenter, out=arena.views)
+        return arena.views, gather_arena(plan, arena, group=self.group, side_stream=self._side)
+
+    def fit(self, method, scale, x, y, sky, radius, maxiter=25, recenter=True, plan=None):
+        return self.fit_async(method, scale, x, y, sky, radius, maxiter=maxiter, recenter=recenter, plan=plan)[1].result()

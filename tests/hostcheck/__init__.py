@@ -61,15 +61,16 @@ def daoerf_separable(xx, yy, gauss):
     return bool(lib().hc_daoerf_separable(_p(xx), _p(yy), C.c_int(xx.size), _p(gauss)))
 
 
-def mmm_indexed(v, K=32, f32=False, readnoise=0.0, minsky=20, mxiter=50):
-    """mmm through the block index of the sorted vector (what aper_mmm_kernel runs, one thread per star)."""
+def mmm_indexed(v, f32=False, readnoise=0.0, minsky=20, mxiter=50):
+    """mmm through the index of the sorted vector (what aper_mmm_kernel runs, one thread per star); at most 4096 keys."""
     v = np.ascontiguousarray(np.asarray(v).ravel(), np.float64)
     out = np.empty(3)
-    it = lib().hc_mmm_indexed(_p(v), C.c_int(v.size), C.c_int(K), C.c_int(int(f32)), C.c_double(readnoise), C.c_int(minsky),
+    it = lib().hc_mmm_indexed(_p(v), C.c_int(v.size), C.c_int(int(f32)), C.c_double(readnoise), C.c_int(minsky),
                               C.c_int(mxiter), _p(out))
+    assert it >= 0
     return out[0], out[1], out[2], it
 
 
-def indexed_first_ok(v, K=32):
+def indexed_first_ok(v):
     v = np.ascontiguousarray(np.asarray(v).ravel(), np.float64)
-    return bool(lib().hc_indexed_first_ok(_p(v), C.c_int(v.size), C.c_int(K)))
+    return lib().hc_indexed_first_ok(_p(v), C.c_int(v.size)) == 1

@@ -8,37 +8,49 @@
 
 #include "../../pythonphot_b200/csrc/bphot_math.cuh"
 
-// mmm through the block index of the sorted vector (bphot_math.cuh IndexedView, built like aper_kernel.cu sort_index
-// builds it on the device: per block of K keys the first key and the exclusive prefix sums of d and d^2).
-// T = float when f32 != 0 (keys are rounded to fp32 first, like an fp32 image).
+// The index of a sorted vector as aper_kernel.cu sort_index lays it out (bphot_math.cuh IndexedView): 16-ary search tree
+// L1 / L2 and exclusive prefix sums of d, d^2 at every 16th key.  Rows are padded to whole groups of 16.
 template <typename T>
-static int mmm_indexed(const double* v, int n, int K, double readnoise, int minsky, int mxiter, double* out3) {
+struct HostIndex {
+    std::vector<T> k, L1, L2;
+    std::vector<double> PT;
+    bphot::IndexedView<T> V;
+    explicit HostIndex(std::vector<T> sorted) : k(std::move(sorted)) {
+        const int ns = (int)k.size();
+        const int ng = (ns + 15) / 16;
+        k.resize((size_t)(ng + 1) * 16, (T)0);
+        L1.assign(16, (T)0); L2.assign(4096 / 16 + 16, (T)0); PT.assign(2 * (size_t)(ng + 2), 0.0);
+        if ((int)L2.size() < ng + 16) L2.resize(ng + 16, (T)0);
+        V.skymid = ns > 0 ? 0.5 * (double)k[(ns - 1) / 2] + 0.5 * (double)k[ns / 2] : 0.0;
+        double a = 0.0, q = 0.0;
+        for (int g = 0; g <= ng; g++) {
+            PT[2 * g] = a; PT[2 * g + 1] = q;
+            if (g < ng) L2[g] = k[16 * g];
+            for (int j = 16 * g; j < 16 * g + 16 && j < ns; j++) { const double d = (double)k[j] - V.skymid; a = a + d; q = q + d * d; }
+        }
+        for (int i = 0; i < 16 && 256 * i < ns; i++) L1[i] = k[256 * i];
+        V.k = k.data(); V.L1 = L1.data(); V.L2 = L2.data(); V.PT = PT.data(); V.n = ns;
+    }
+};
+
+// mmm through that index, as aper_mmm_kernel runs it (one thread per star).  T = float: keys rounded to fp32 first,
+// like an fp32 image.
+template <typename T>
+static int mmm_indexed(const double* v, int n, double readnoise, int minsky, int mxiter, double* out3) {
     std::vector<T> s;
     s.reserve(n);
     for (int i = 0; i < n; i++)
         if (v[i] == v[i]) s.push_back((T)v[i]);
     std::sort(s.begin(), s.end());
     const int ns = (int)s.size();
-    int gs = 0;
-    while ((1 << gs) < K) gs++;
-    const int nb = (ns + K - 1) / K;
-    std::vector<double> PT(2 * (nb + 2), 0.0);
-    std::vector<T> bmin(nb + 1);
-    bphot::IndexedView<T> V;
-    V.k = s.data(); V.PT = PT.data(); V.bmin = bmin.data(); V.gs = gs; V.n = ns;
-    V.skymid = ns > 0 ? 0.5 * (double)s[(ns - 1) / 2] + 0.5 * (double)s[ns / 2] : 0.0;
-    double a = 0.0, q = 0.0;
-    for (int b = 0; b <= nb; b++) {
-        PT[2 * b] = a; PT[2 * b + 1] = q;
-        if (b < nb) bmin[b] = s[b * K];
-        double ba = 0.0, bq = 0.0;
-        for (int j = b * K; j < (b + 1) * K && j < ns; j++) { const double d = (double)s[j] - V.skymid; ba = ba + d; bq = bq + d * d; }
-        a = a + ba; q = q + bq;
-    }
+    if (ns > 4096) return -1;
+    HostIndex<T> H(s);
+    const bphot::IndexedView<T>& V = H.V;
     bphot::MmmResult R = bphot::mmm_sorted(
         V, [&](int lo, int hi, double, double* s1, double* s2) { V.delta_sums(lo, hi, s1, s2); },
-        [&](int lo, int hi) { return V.plain_sum(lo, hi); }, [&](double x, bool strict) { return V.first(x, strict); }, ns, readnoise,
-        minsky, mxiter);
+        [&](int lo, int hi) { return V.plain_sum(lo, hi); },
+        [&](double v1, bool st1, bool need1, double v2, bool st2, bool need2, int* r1, int* r2) { V.first2(v1, st1, need1, v2, st2, need2, r1, r2); },
+        ns, readnoise, minsky, mxiter);
     out3[0] = R.skymod; out3[1] = R.sigma; out3[2] = R.skew;
     return R.iters;
 }
@@ -110,31 +122,31 @@ int hc_mmm(const double* v, int n, double readnoise, int minsky, int mxiter, dou
     auto first = [&](double v, bool strict) -> int {
         return strict ? bphot::upper_bound_gt(at, ns, v) : bphot::lower_bound_ge(at, ns, v);
     };
-    bphot::MmmResult R = bphot::mmm_sorted(at, dsum, psum, first, ns, readnoise, minsky, mxiter);
+    auto first2 = [&](double v1, bool st1, bool need1, double v2, bool st2, bool need2, int* r1, int* r2) {
+        if (need1) *r1 = first(v1, st1);
+        if (need2) *r2 = first(v2, st2);
+    };
+    bphot::MmmResult R = bphot::mmm_sorted(at, dsum, psum, first2, ns, readnoise, minsky, mxiter);
     out3[0] = R.skymod; out3[1] = R.sigma; out3[2] = R.skew;
     return R.iters;
 }
-int hc_mmm_indexed(const double* v, int n, int K, int f32, double readnoise, int minsky, int mxiter, double* out3) {
-    return f32 ? mmm_indexed<float>(v, n, K, readnoise, minsky, mxiter, out3) : mmm_indexed<double>(v, n, K, readnoise, minsky, mxiter, out3);
+int hc_mmm_indexed(const double* v, int n, int f32, double readnoise, int minsky, int mxiter, double* out3) {
+    return f32 ? mmm_indexed<float>(v, n, readnoise, minsky, mxiter, out3) : mmm_indexed<double>(v, n, readnoise, minsky, mxiter, out3);
 }
-// IndexedView::first against the plain binary searches, on every distinct key and its neighbours
-int hc_indexed_first_ok(const double* v, int n, int K) {
+// IndexedView::first2 against the plain binary searches, on every key and its floating-point neighbours
+int hc_indexed_first_ok(const double* v, int n) {
     std::vector<double> s(v, v + n);
     std::sort(s.begin(), s.end());
-    int gs = 0;
-    while ((1 << gs) < K) gs++;
-    const int nb = (n + K - 1) / K;
-    std::vector<double> PT(2 * (nb + 2), 0.0), bmin(nb + 1);
-    for (int b = 0; b < nb; b++) bmin[b] = s[b * K];
-    bphot::IndexedView<double> V;
-    V.k = s.data(); V.PT = PT.data(); V.bmin = bmin.data(); V.gs = gs; V.n = n; V.skymid = 0.0;
+    if (n > 4096) return -1;
+    HostIndex<double> H(s);
     const double* p = s.data();
     auto at = [p](int i) -> double { return p[i]; };
     for (int i = 0; i < n; i++)
         for (int d = -1; d <= 1; d++) {
             const double x = d == 0 ? s[i] : nextafter(s[i], d < 0 ? -1e300 : 1e300);
-            if (V.first(x, true) != bphot::upper_bound_gt(at, n, x)) return 0;
-            if (V.first(x, false) != bphot::lower_bound_ge(at, n, x)) return 0;
+            int r1 = -7, r2 = -7;
+            H.V.first2(x, true, true, x, false, true, &r1, &r2);
+            if (r1 != bphot::upper_bound_gt(at, n, x) || r2 != bphot::lower_bound_ge(at, n, x)) return 0;
         }
     return 1;
 }
