@@ -129,6 +129,18 @@ def device_of(device=None):
     return dev
 
 
+_copy_streams = {}
+
+
+def copy_stream(device):
+    """One side stream per device for host->device uploads that should overlap kernels on the caller's stream."""
+    torch = torch_cuda()
+    key = str(device)
+    if key not in _copy_streams:
+        _copy_streams[key] = torch.cuda.Stream(device=device)
+    return _copy_streams[key]
+
+
 def dtype_code(t):
     """BPHOT_F32/F64 for a torch tensor or numpy array of floats."""
     name = str(t.dtype)

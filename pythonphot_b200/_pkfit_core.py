@@ -22,9 +22,29 @@ class PkfitEngine(object):
         self.fmask = maskim
         self.ronois = ronois
         self.phpadu = phpadu
-        self._img_t = _lib.to_device_image(image, self.device)
-        self._noise_t = _lib.to_device_image(noiseim, self.device) if noiseim is not None else None
-        self._mask_t = _lib.to_device_mask(maskim, self.device) if maskim is not None else None
+        # Host arrays go up on a copy stream of their own, image first: the constructor returns while the copies run
+        # (when the arrays are page-locked), ``image_device()`` waits for the image only, the fits for all three -- so
+        # work queued in between, e.g. ``aper.aper(pk.image_device(), ...)``, overlaps the noise and mask uploads.
+        host_in = any(a is not None and not isinstance(a, torch.Tensor) for a in (image, noiseim, maskim))
+        self._ev_img = self._ev_all = None
+        if host_in:
+            cur, up = torch.cuda.current_stream(self.device), _lib.copy_stream(self.device)
+            up.wait_stream(cur)
+            with torch.cuda.stream(up):
+                self._img_t = _lib.to_device_image(image, self.device)
+                self._ev_img = torch.cuda.Event()
+                self._ev_img.record(up)
+                self._noise_t = _lib.to_device_image(noiseim, self.device) if noiseim is not None else None
+                self._mask_t = _lib.to_device_mask(maskim, self.device) if maskim is not None else None
+                self._ev_all = torch.cuda.Event()
+                self._ev_all.record(up)
+            for t in (self._img_t, self._noise_t, self._mask_t):
+                if t is not None:
+                    t.record_stream(cur)
+        else:
+            self._img_t = _lib.to_device_image(image, self.device)
+            self._noise_t = _lib.to_device_image(noiseim, self.device) if noiseim is not None else None
+            self._mask_t = _lib.to_device_mask(maskim, self.device) if maskim is not None else None
         for name, t in (("noise", self._noise_t), ("mask", self._mask_t)):
             if t is not None and tuple(t.shape) != tuple(self._img_t.shape):
                 raise ValueError("%s image shape %s differs from image shape %s" % (name, tuple(t.shape), tuple(self._img_t.shape)))
@@ -38,6 +58,20 @@ class PkfitEngine(object):
         self._psf_t = torch.from_numpy(psf_h).to(self.device)
 
     # ------------------------------------------------------------------
+    def image_device(self):
+        """The image as it sits in HBM (a CUDA tensor), for calls that work on the same exposure -- e.g.
+        ``aper.aper(pk.image_device(), xc, yc, ...)`` -- so that it crosses PCIe once.  The current stream is made to
+        wait for the upload."""
+        torch = _lib.torch_cuda()
+        if self._ev_img is not None:
+            torch.cuda.current_stream(self.device).wait_event(self._ev_img)
+        return self._img_t
+
+    def _uploads_done(self):
+        if self._ev_all is not None:
+            torch = _lib.torch_cuda()
+            torch.cuda.current_stream(self.device).wait_event(self._ev_all)
+
     def fit_device(self, variant, scale_t, x_t, y_t, sky_t, radius, maxiter=25, recenter=True, out=None):
         """All star columns are fp64 CUDA vectors of equal length; returns a dict of CUDA tensors
         (errmag, chi, sharp, scale, x, y, chi2 fp64; niter int32) without synchronising."""
@@ -49,6 +83,7 @@ class PkfitEngine(object):
         out = _lib.alloc_out([(k, torch.float64, ()) for k in ("errmag", "chi", "sharp", "scale", "x", "y", "chi2")] +
                              [("niter", torch.int32, ())], n, dev, out)
         img, nz, mk = self._img_t, self._noise_t, self._mask_t
+        self._uploads_done()
         with torch.cuda.device(dev):
             rc = _lib.lib().bphot_pkfit_device(
                 int(variant), _lib.ptr(img), _lib.dtype_code(img),

@@ -542,6 +542,26 @@ BP_D ApPartial aperture_warp(const AperParams& P, const T* __restrict__ stamp, c
 // Index layout per star (idx_stride bytes, 64-byte aligned): T L1[16] | T L2[256] | double2 PT[257].
 constexpr size_t sort_index_bytes(size_t key_size) { return ((size_t)(16 + 256) * key_size + (size_t)257 * 16 + 63) & ~(size_t)63; }
 
+#ifndef AP_IDX_SKIP
+#define AP_IDX_SKIP 0  // timing experiments only (wrong results): 1 = no per-key sums, 2 = no scan, 4 = no writes, 8 = no median read
+#endif
+#ifndef AP_IDX_INTCVT
+#define AP_IDX_INTCVT 1  // fp32 key -> fp64 by integer bit manipulation (exact; zero / subnormal / inf / NaN take F2F)
+#endif
+// (double)x for a float, without the F2F.F64.F32 conversion unit (an eighth of the fp32 issue rate): a normal float's
+// sign, exponent (re-biased by 1023 - 127) and mantissa are moved into place with integer instructions.  Exact.
+BP_D double widen(float x) {
+#if AP_IDX_INTCVT
+    const unsigned b = __float_as_uint(x), e = (b >> 23) & 0xffu;
+    if (e == 0u || e == 0xffu) return (double)x;
+    const unsigned hi = (b & 0x80000000u) | (((b >> 3) & 0x0fffffffu) + 0x38000000u);
+    return __hiloint2double((int)hi, (int)(b << 29));
+#else
+    return (double)x;
+#endif
+}
+BP_D double widen(double x) { return x; }
+
 template <typename T, int K>
 BP_D void sort_index(const AperParams& P, const T (&r)[K], const T* __restrict__ dst, int nvalid, size_t row, int tid, double (*s_wsum)[2]) {
     static_assert(K == 8 || K == 16 || K == 32, "index groups are 16 keys");
@@ -553,15 +573,15 @@ BP_D void sort_index(const AperParams& P, const T (&r)[K], const T* __restrict__
     // the two median keys (ranks (n-1)/2 and n/2) were just written to the scratch row by some thread of this CTA
     __syncthreads();
     double skymid = 0.0;
-    if (nvalid > 0) skymid = 0.5 * (double)__ldcg(dst + (nvalid - 1) / 2) + 0.5 * (double)__ldcg(dst + nvalid / 2);  // mmm.py:121
+    if (!(AP_IDX_SKIP & 8) && nvalid > 0) skymid = 0.5 * (double)__ldcg(dst + (nvalid - 1) / 2) + 0.5 * (double)__ldcg(dst + nvalid / 2);  // mmm.py:121
     const int e0 = tid * K;
     constexpr int H = K > 16 ? 16 : K;  // keys of this thread in its first index group
     double a = 0.0, qq = 0.0, ha = 0.0, hq = 0.0;
 #pragma unroll
     for (int q = 0; q < K; q++) {
         if (q == H) { ha = a; hq = qq; }  // K = 32: sums of the first group
-        if (e0 + q < nvalid) {
-            const double d = (double)r[q] - skymid;
+        if (!(AP_IDX_SKIP & 1) && e0 + q < nvalid) {
+            const double d = widen(r[q]) - skymid;
             a = a + d;
             qq = __fma_rn(d, d, qq);
         }
@@ -570,6 +590,7 @@ BP_D void sort_index(const AperParams& P, const T (&r)[K], const T* __restrict__
     double ia_ = a, iq_ = qq;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
+        if (AP_IDX_SKIP & 2) break;
         const double ua = __shfl_up_sync(FULL, ia_, o), uq = __shfl_up_sync(FULL, iq_, o);
         if (lane >= o) { ia_ = ua + ia_; iq_ = uq + iq_; }
     }
@@ -580,6 +601,7 @@ BP_D void sort_index(const AperParams& P, const T (&r)[K], const T* __restrict__
     double ba = 0.0, bq = 0.0;
     for (int w = 0; w < warp; w++) { ba = ba + s_wsum[w][0]; bq = bq + s_wsum[w][1]; }
     const double pa = ba + xa, pq = bq + xq;  // sums over keys [0, e0)
+    if (AP_IDX_SKIP & 4) { if (pa == 1.2345) PT[0] = make_double2(pa + ha, pq + hq); return; }
     if constexpr (K == 32) {
         PT[2 * tid] = make_double2(pa, pq);
         PT[2 * tid + 1] = make_double2(pa + ha, pq + hq);

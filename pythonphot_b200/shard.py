@@ -268,7 +268,10 @@ def broadcast_columns(columns, n, device, src=0, group=None):
     dist = _dist()
     rank, world = world_info(group)
     if rank == src:
-        buf = torch.from_numpy(np.ascontiguousarray(np.stack([np.asarray(c, dtype=np.float64).reshape(-1) for c in columns]))).to(device)
+        if all(isinstance(c, torch.Tensor) for c in columns):
+            buf = torch.stack([c.to(device=device, dtype=torch.float64).reshape(-1) for c in columns]).contiguous()
+        else:
+            buf = torch.from_numpy(np.ascontiguousarray(np.stack([np.asarray(c, dtype=np.float64).reshape(-1) for c in columns]))).to(device)
         assert buf.shape[1] == n
     else:
         buf = torch.empty((len(columns), n), dtype=torch.float64, device=device)

@@ -133,3 +133,64 @@ def make_field(nrow, ncol, nstars, seed, dtype=np.float32, sky=300.0, phpadu=4.0
                xfit=x + rng.normal(0.0, pos_jitter, nstars),
                yfit=y + rng.normal(0.0, pos_jitter, nstars))
     return out
+
+
+def make_field_device(nrow, ncol, nstars, seed, device, sky=300.0, phpadu=4.0, ronois=5.0, margin=60.0,
+                      nan_frac=1e-4, sat_frac=5e-5, mask_frac=2e-4, scale_range=(0.05, 50.0), pos_jitter=0.05,
+                      R=8, resid_amp=0.03, chunk=250000):
+    """The same kind of exposure as ``make_field`` (sky + pixel-integrated Gaussian + residual-table stars + Poisson/read
+    noise, NaN / saturated / masked pixels), built with torch ON THE DEVICE for the large configurations
+    (BASELINE.json configs[4]: 16384 x 16384, 10 M stars), where the numpy generator needs minutes and ~10 GB of host
+    memory.  Test / bench data only -- nothing here is on the product path.  Returns fp32 ``image`` / ``noise`` and
+    uint8 ``mask`` as CUDA tensors, star columns as fp64 CUDA tensors (``x``, ``y``, ``scale``, ``xfit``, ``yfit``) and
+    the PSF model (``gauss``, ``psf`` as numpy, like ``make_field``).  Deterministic for a given seed and device type."""
+    import torch
+    g = torch.Generator(device=device)
+    g.manual_seed(int(seed))
+    gauss, psf = make_psf(resid_amp=resid_amp)
+    f64 = torch.float64
+    u = lambda n: torch.rand(n, generator=g, device=device, dtype=f64)  # noqa: E731
+    x = margin + u(nstars) * (ncol - 1 - 2 * margin)
+    y = margin + u(nstars) * (nrow - 1 - 2 * margin)
+    lo, hi = scale_range
+    scale = torch.exp(math.log(lo) + u(nstars) * (math.log(hi) - math.log(lo)))
+    model = torch.full((nrow * ncol,), float(sky), dtype=torch.float32, device=device)
+    k = torch.arange(2 * R + 1, device=device)
+    h, sx, sy = float(gauss[0]), float(gauss[3]), float(gauss[4])
+    cdf = lambda t: 0.5 + 0.5 * torch.special.erf(t / math.sqrt(2.0))  # noqa: E731
+    for s in range(0, nstars, chunk):
+        e = min(nstars, s + chunk)
+        xs, ys, sc = x[s:e], y[s:e], scale[s:e]
+        ix0 = torch.floor(xs).long() - R
+        iy0 = torch.floor(ys).long() - R
+        dx = (ix0[:, None] + k[None, :]).to(f64) - xs[:, None]
+        dy = (iy0[:, None] + k[None, :]).to(f64) - ys[:, None]
+        fx = SQRT2PI_REF * sx * (cdf((dx + 0.5) / sx) - cdf((dx - 0.5) / sx))
+        fy = SQRT2PI_REF * sy * (cdf((dy + 0.5) / sy) - cdf((dy - 0.5) / sy))
+        st = h * fy[:, :, None] * fx[:, None, :]
+        if resid_amp:
+            ddx, ddy = dx[:, None, :], dy[:, :, None]
+            q = (ddx / sx) ** 2 + (ddy / sy) ** 2
+            st = st + h * resid_amp * (1.0 - 0.5 * q) * torch.exp(-0.5 * q) * (1.0 + 0.3 * ddx / sx * torch.exp(-0.25 * q))
+        st = st * sc[:, None, None]
+        idx = (iy0[:, None] + k[None, :])[:, :, None] * ncol + (ix0[:, None] + k[None, :])[:, None, :]
+        model.index_add_(0, idx.reshape(-1), st.reshape(-1).to(torch.float32))  # stamps lie inside the frame (margin > R)
+        del dx, dy, fx, fy, st, idx
+    var = torch.clamp(model, min=0.0) / phpadu + ronois ** 2
+    noise = torch.sqrt(var)
+    image = model + torch.randn(model.shape, generator=g, device=device, dtype=torch.float32) * noise
+    del model, var
+    npx = nrow * ncol
+    ri = lambda n: torch.randint(0, npx, (n,), generator=g, device=device)  # noqa: E731
+    mask = torch.zeros(npx, dtype=torch.uint8, device=device)
+    if int(mask_frac * npx):
+        mask[ri(int(mask_frac * npx))] = 1
+        noise[ri(int(0.5 * mask_frac * npx))] = 0.0
+    if int(nan_frac * npx):
+        image[ri(int(nan_frac * npx))] = float("nan")
+    if int(sat_frac * npx):
+        image[ri(int(sat_frac * npx))] = 65535.0
+    jit = lambda n: torch.randn(n, generator=g, device=device, dtype=f64) * pos_jitter  # noqa: E731
+    return dict(image=image.reshape(nrow, ncol), noise=noise.reshape(nrow, ncol), mask=mask.reshape(nrow, ncol),
+                x=x, y=y, scale=scale, xfit=x + jit(nstars), yfit=y + jit(nstars), sky=float(sky), gauss=gauss, psf=psf,
+                phpadu=float(phpadu), ronois=float(ronois))
