@@ -189,7 +189,7 @@ def parity_report(got_aper, got_fit, want, xs, ys, xfs, yfs, shape, fit_cols):
     if got_aper is not None:
         o = want["aper"]
         w = dict(zip(compare.APER_NAMES, o[:7]))
-        r = compare.compare_aper(got_aper, w, o[9], got_aper["nsky"], o[7], got_aper["mmm_iter"], o[8])
+        r = compare.compare_aper(got_aper, w, o[9], got_aper["nsky"], o[7], got_aper["mmm_iter"], o[8], alt=o[10])
         rep["aper"] = r
         rep["mismatches"] += r["mismatches"]
         rep["fragile"] = r["fragile"]

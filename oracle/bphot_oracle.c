@@ -271,7 +271,11 @@ int bo_mmm(const double *v, int n_in, double readnoise, int minsky, int mxiter,
  * fragile[nstars*naper] (may be NULL): 1 when the reference's own badflag / flux for that aperture hinges on
  * rounding noise -- a non-finite or out-of-range pixel sits where Pixwt returns |w| < 1e-9 (outside the
  * circle but inside the bigrad box), so whether it is "in" the aperture (aper.py:329-330, w > 0) depends on
- * the last bits of eight atan() values.  Tests exclude those apertures from bit-exact comparison. */
+ * the last bits of eight atan() values.  fragile bits: 1 = such a pixel exists, 2 = a non-finite one, 4 = a finite
+ * out-of-range one.  alt5[nstars*naper*5] (may be NULL) = (flux, fluxerr, mag, magerr, badflag) of the aperture with every
+ * fragile pixel left OUT: together with "a non-finite one got in" (flux sum zeroed, flag 1) and "a finite one got in"
+ * (same values, flag 1) these are all the outcomes the reference's arithmetic admits, so the tests check a fragile
+ * aperture against that set instead of skipping it. */
 int bo_aper(const void *img, int img_dt, int nrow, int ncol,
             const double *xc, const double *yc, int nstars,
             double phpadu, const double *apr, int naper, double zeropoint,
@@ -280,7 +284,7 @@ int bo_aper(const void *img, int img_dt, int nrow, int ncol,
             double readnoise, int compat_py2,
             double *mag, double *magerr, double *flux, double *fluxerr,
             double *sky, double *skyerr, double *badflag, int *nsky_o, int *mmm_iter_o,
-            unsigned char *fragile, int nthreads) {
+            unsigned char *fragile, double *alt5, int nthreads) {
     if (use_setsky) { skyrad_in = 0.; skyrad_out = apr[0]; for (int k = 1; k < naper; k++) if (apr[k] > skyrad_out) skyrad_out = apr[k]; skyrad_out += 1; } /* aper.py:156-160 */
     double rinsq = skyrad_in * skyrad_in, routsq = skyrad_out * skyrad_out;
 #ifdef _OPENMP
@@ -289,7 +293,8 @@ int bo_aper(const void *img, int img_dt, int nrow, int ncol,
 #pragma omp parallel
     {
         size_t cap = 0;
-        double *skybuf = NULL, *work = NULL, *wv = NULL;
+        double *skybuf = NULL, *work = NULL, *wv = NULL, *v2 = NULL, *w2 = NULL;
+        unsigned char *fr = NULL;
 #pragma omp for schedule(dynamic, 16)
         for (int i = 0; i < nstars; i++) {
             double *o_mag = mag + (size_t)i * naper, *o_magerr = magerr + (size_t)i * naper;
@@ -315,7 +320,10 @@ int bo_aper(const void *img, int img_dt, int nrow, int ncol,
             if (ny + 0.5 - dy < edge) edge = ny + 0.5 - dy;
             size_t npix = (size_t)nx * ny;
             if (npix > cap) {
-                cap = npix; free(skybuf); free(work); free(wv);
+                cap = npix; free(skybuf); free(work); free(wv); free(fr); free(v2); free(w2);
+                fr = (unsigned char *)malloc(cap);
+                v2 = (double *)malloc(cap * sizeof(double));
+                w2 = (double *)malloc(cap * sizeof(double));
                 skybuf = (double *)malloc(cap * sizeof(double));
                 work = (double *)malloc(cap * sizeof(double));
                 wv = (double *)malloc(cap * sizeof(double));
@@ -354,7 +362,7 @@ int bo_aper(const void *img, int img_dt, int nrow, int ncol,
             for (int k = 0; k < naper; k++) { /* aper.py:310-380 */
                 double ap = apr[k], area = M_PI * ap * ap;
                 if (!(edge >= ap)) continue; /* aper.py:311,350-353 */
-                int nw = 0, anynonfinite = 0, anybad = 0;
+                int nw = 0, anynonfinite = 0, anybad = 0, nfr = 0;
                 /* collect (value, weight) in row-major order */
                 if (exact) {
                     double bigrad = ap + 0.5, smallrad = ap / sqrt(2.) - 0.5; /* aper.py:179-181 */
@@ -367,17 +375,21 @@ int bo_aper(const void *img, int img_dt, int nrow, int ncol,
                             if (x1 > bigrad || y1 > bigrad) continue; /* aper.py:319-320 */
                             if (x1 < smallrad && y1 < smallrad) w = 1.0; /* aper.py:316-318 */
                             else {
+                                int isfr = 0;
                                 w = bo_pixwt(dx, dy, ap, xxp, yyp); /* aper.py:328-329 */
                                 if (fragile && fabs(w) < 1e-9) {
                                     double pv = ld(img, img_dt, (size_t)(ly + r) * ncol + (lx + c));
-                                    if (!isfinite(pv) || (badlo < badhi && (pv <= badlo || pv >= badhi)))
-                                        fragile[(size_t)i * naper + k] = 1;
+                                    if (!isfinite(pv)) { fragile[(size_t)i * naper + k] |= 3; isfr = 1; }
+                                    else if (badlo < badhi && (pv <= badlo || pv >= badhi)) { fragile[(size_t)i * naper + k] |= 5; isfr = 1; }
                                 }
                                 if (w < 0.0) w = 0.0;
+                                if (!(w > 0.0)) continue; /* aper.py:330 */
+                                skybuf[nw] = ld(img, img_dt, (size_t)(ly + r) * ncol + (lx + c));
+                                wv[nw] = w; fr[nw] = (unsigned char)isfr; nfr += isfr; nw++;
+                                continue;
                             }
-                            if (!(w > 0.0)) continue; /* aper.py:330 */
                             skybuf[nw] = ld(img, img_dt, (size_t)(ly + r) * ncol + (lx + c));
-                            wv[nw] = w; nw++;
+                            wv[nw] = w; fr[nw] = 0; nw++;
                         }
                 } else { /* aper.py:336-349 */
                     int nfull = 0; int np_ = 0;
@@ -398,6 +410,20 @@ int bo_aper(const void *img, int img_dt, int nrow, int ncol,
                     double factor = (area - nfull) / pw_sum(work, np_);
                     for (int q = 0; q < nw; q++) if (wv[q] != 1.0) wv[q] = wv[q] * factor;
                 }
+                if (alt5 && exact && fragile && fragile[(size_t)i * naper + k]) {
+                    /* the same aperture with the fragile pixels left out (aper.py:358-403 on the shorter lists) */
+                    double *o5 = alt5 + ((size_t)i * naper + k) * 5;
+                    int m = 0, nf2 = 0, nb2 = 0;
+                    for (int q = 0; q < nw; q++) if (!fr[q]) { v2[m] = skybuf[q]; w2[m] = wv[q]; m++; }
+                    for (int q = 0; q < m; q++) if (!isfinite(v2[q])) { nf2 = 1; v2[q] = 0; }
+                    if (nf2) for (int q = 0; q < m; q++) w2[q] = 0;
+                    if (badlo < badhi) for (int q = 0; q < m; q++) if (v2[q] <= badlo || v2[q] >= badhi) { nb2 = 1; v2[q] = 0; }
+                    for (int q = 0; q < m; q++) v2[q] = v2[q] * w2[q];
+                    double f2 = pw_sum(v2, m) - skymod * area;
+                    double er2 = sqrt(area * skyvar + fabs(f2) / phpadu + sigsq * (area * area));
+                    o5[0] = f2; o5[1] = er2; o5[2] = NAN; o5[3] = NAN; o5[4] = (nf2 || nb2) ? 1 : 0;
+                    if (f2 > 0.0) { o5[3] = 1.0857 * er2 / f2; o5[2] = zeropoint - 2.5 * log10(f2); }
+                }
                 o_bad[k] = 0; /* aper.py:358 */
                 for (int q = 0; q < nw; q++) if (!isfinite(skybuf[q])) { anynonfinite = 1; skybuf[q] = 0; } /* aper.py:359-366 */
                 if (anynonfinite) { o_bad[k] = 1; for (int q = 0; q < nw; q++) wv[q] = 0; }
@@ -417,7 +443,7 @@ int bo_aper(const void *img, int img_dt, int nrow, int ncol,
                 }
             }
         }
-        free(skybuf); free(work); free(wv);
+        free(skybuf); free(work); free(wv); free(fr); free(v2); free(w2);
     }
     return 0;
 }

@@ -43,24 +43,66 @@ def underdetermined(x, y, radius, shape):
     return (cnt < 4) & np.isfinite(x) & np.isfinite(y)
 
 
-def compare_aper(got, want, fragile, nsky=None, want_nsky=None, mmm_iter=None, want_iter=None):
+def _aper_values_ok(got, cand, sel):
+    """[n, naper] bool: the four value columns of `got` agree with `cand` (dict of [n, naper]) where `sel`."""
+    ok = np.ones(sel.shape, dtype=bool)
+    for nm in ("flux", "fluxerr", "mag", "magerr"):
+        atol = 1e-7 if nm in ("flux", "fluxerr") else 1e-9
+        ok &= close_mask(got[nm], cand[nm], 1e-9, atol)
+    return ok | ~sel
+
+
+def compare_aper(got, want, fragile, nsky=None, want_nsky=None, mmm_iter=None, want_iter=None, alt=None):
     """got / want: dicts with APER_NAMES ([n, naper] and [n] arrays).  `fragile` [n, naper] bool from the oracle.
-    Returns {"stars", "mismatches", "fragile", "fragile_frac", "first_bad": {column: [indices]}}."""
+
+    Robust apertures: badflag exact, values within tolerance.  Fragile apertures (a NaN / out-of-range pixel sits where
+    Pixwt returns 0 +- 1e-16, so the reference's own result depends on the sign of a rounding error): with `alt` (the
+    oracle's tenth output) the GPU result must equal ONE of the outcomes the reference's arithmetic admits --
+    the oracle's own; every fragile pixel left out; a finite out-of-range one let in (same values, flag 1); a non-finite
+    one let in (pixel sum zeroed, aper.py:366, flag 1) -- without `alt` they are only counted.
+    Returns {"stars", "mismatches", "fragile", "fragile_frac", "fragile_checked", "first_bad": {column: [indices]}}."""
     n = np.asarray(want["sky"]).size
     shp = (n, -1)
     fragile = np.asarray(fragile, dtype=bool).reshape(shp)
-    gb, wb = np.asarray(got["badflag"]).reshape(shp).astype(bool), np.asarray(want["badflag"]).reshape(shp).astype(bool)
+    g = {k: np.asarray(got[k], dtype=np.float64).reshape(shp) for k in ("flux", "fluxerr", "mag", "magerr", "badflag")}
+    w = {k: np.asarray(want[k], dtype=np.float64).reshape(shp) for k in ("flux", "fluxerr", "mag", "magerr", "badflag")}
+    gb, wb = g["badflag"] != 0, w["badflag"] != 0
     bad = {}
     flag_mism = gb != wb
     robust_flag_mism = flag_mism & ~fragile
     if robust_flag_mism.any():
         bad["badflag"] = np.nonzero(robust_flag_mism.any(axis=1))[0]
-    ok_ap = ~flag_mism & ~fragile  # apertures whose value is comparable
-    for nm in ("flux", "fluxerr", "mag", "magerr"):
-        atol = 1e-7 if nm in ("flux", "fluxerr") else 1e-9
-        c = close_mask(np.asarray(got[nm]).reshape(shp), np.asarray(want[nm]).reshape(shp), 1e-9, atol) | ~ok_ap
-        if not c.all():
-            bad[nm] = np.nonzero(~c.all(axis=1))[0]
+    ok_ap = ~flag_mism & ~fragile  # apertures whose value is comparable one to one
+    vals_ok = _aper_values_ok(g, w, ok_ap)
+    if not vals_ok.all():
+        bad["values"] = np.nonzero(~vals_ok.all(axis=1))[0]
+    checked = 0
+    if alt is not None and fragile.any():
+        kind = np.asarray(alt["kind"]).reshape(shp)
+        a5 = {k: np.asarray(alt[k], dtype=np.float64).reshape(shp) for k in ("flux", "fluxerr", "mag", "magerr", "badflag")}
+        # outcome "a non-finite fragile pixel got in": the weighted sum is zeroed, the rest of aper.py:383-403 as usual
+        apr = np.asarray(alt["apr"], dtype=np.float64).reshape(1, -1)
+        area = np.pi * apr * apr
+        sky = np.asarray(want["sky"], dtype=np.float64).reshape(-1, 1)
+        skysig = np.asarray(want["skyerr"], dtype=np.float64).reshape(-1, 1)
+        if alt.get("setsky") is not None:
+            nsk = np.full((n, 1), float(alt["setsky"][2]))
+        else:
+            nsk = np.maximum(np.asarray(alt["nsky"], dtype=np.float64).reshape(-1, 1), 1.0)
+        with np.errstate(invalid="ignore", divide="ignore"):
+            skyvar = skysig * skysig
+            zf = 0.0 - sky * area
+            ze = np.sqrt(area * skyvar + np.abs(zf) / alt["phpadu"] + (skyvar / nsk) * (area * area))
+            zm = np.where(zf > 0, alt["zeropoint"] - 2.5 * np.log10(np.where(zf > 0, zf, 1.0)), np.nan)
+            zme = np.where(zf > 0, 1.0857 * ze / np.where(zf > 0, zf, 1.0), np.nan)
+        zero = {"flux": zf + 0 * area, "fluxerr": ze, "mag": zm, "magerr": zme}
+        own = _aper_values_ok(g, w, fragile) & (gb == wb)
+        excl = _aper_values_ok(g, a5, fragile) & ((gb == (a5["badflag"] != 0)) | (gb & ((kind & 4) != 0)))
+        zeroed = _aper_values_ok(g, zero, fragile) & gb & ((kind & 2) != 0)
+        fr_ok = (own | excl | zeroed) | ~fragile
+        checked = int(fragile.sum())
+        if not fr_ok.all():
+            bad["fragile"] = np.nonzero(~fr_ok.all(axis=1))[0]
     for nm in ("sky", "skyerr"):
         c = close_mask(np.asarray(got[nm]).reshape(-1), np.asarray(want[nm]).reshape(-1), 1e-9, 1e-9)
         if not c.all():
@@ -72,7 +114,7 @@ def compare_aper(got, want, fragile, nsky=None, want_nsky=None, mmm_iter=None, w
                 bad[nm] = np.nonzero(~c)[0]
     stars_bad = np.unique(np.concatenate([v for v in bad.values()])) if bad else np.zeros(0, np.int64)
     return {"stars": int(n), "mismatches": int(stars_bad.size), "fragile": int(fragile.sum()),
-            "fragile_frac": float(fragile.mean()) if fragile.size else 0.0,
+            "fragile_frac": float(fragile.mean()) if fragile.size else 0.0, "fragile_checked": checked,
             "fragile_flag_differs": int((flag_mism & fragile).sum()),
             "first_bad": {k: [int(i) for i in v[:8]] for k, v in bad.items()}}
 

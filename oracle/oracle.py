@@ -86,6 +86,7 @@ def aper(image, xc, yc, phpadu=1, apr=5, zeropoint=25, skyrad=(40, 50), badpix=(
     sky, skyerr = np.empty(n), np.empty(n)
     nsky, mit = np.empty(n, np.int32), np.empty(n, np.int32)
     fragile = np.zeros((n, na), np.uint8)
+    alt5 = np.full((n, na, 5), np.nan)
     if setskyval is not None:
         ssv = np.atleast_1d(np.asarray(setskyval, dtype=np.float64))
         if ssv.size == 1:
@@ -101,10 +102,14 @@ def aper(image, xc, yc, phpadu=1, apr=5, zeropoint=25, skyrad=(40, 50), badpix=(
                   C.c_int(use), _p(ssv), C.c_int(int(minsky)), C.c_int(int(bool(exact))), C.c_double(float(readnoise or 0)),
                   C.c_int(1 if compat == "py2" else 0),
                   _p(outs[0]), _p(outs[1]), _p(outs[2]), _p(outs[3]), _p(sky), _p(skyerr), _p(bad), _p(nsky), _p(mit),
-                  _p(fragile), C.c_int(nthreads))
+                  _p(fragile), _p(alt5), C.c_int(nthreads))
     res = (outs[0], outs[1], outs[2], outs[3], sky, skyerr, bad)
     if return_extra:
-        return res + (nsky, mit, fragile.astype(bool))
+        # [9] fragile (bool), [10] the admissible alternative outcome of fragile apertures (oracle/compare.py)
+        alt = {"flux": alt5[..., 0], "fluxerr": alt5[..., 1], "mag": alt5[..., 2], "magerr": alt5[..., 3], "badflag": alt5[..., 4],
+               "kind": fragile.copy(), "phpadu": float(phpadu), "zeropoint": float(zeropoint), "apr": apr.copy(), "nsky": nsky.copy(),
+               "setsky": (ssv.copy() if use else None)}
+        return res + (nsky, mit, fragile.astype(bool), alt)
     return res
 
 

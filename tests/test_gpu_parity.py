@@ -87,23 +87,15 @@ def test_mmm_batch_vs_oracle_ties(pp, oracle):
 
 
 # ------------------------------------------------------------------ aper vs the reference's goldens
-def _check_aper(got, want, fragile, what, nsky=None, want_nsky=None):
-    """got/want: dicts of arrays.  badflag bit-exact except where the reference's own flag hinges on
-    rounding noise (`fragile`, see oracle/bphot_oracle.c); values compared where flags agree."""
-    gb, wb = got["badflag"].astype(bool), want["badflag"].astype(bool)
-    mism = gb != wb
-    assert not (mism & ~fragile).any(), "%s: badflag differs on %d robust apertures" % (what, (mism & ~fragile).sum())
-    # a fragile aperture holds a NaN / out-of-range pixel whose pixwt weight is 0 +- 1e-9: whether the reference
-    # zeroes the whole aperture (aper.py:366) hinges on the last bit of atan(), so its VALUE is not comparable either
-    ok = ~mism & ~fragile
-    for nm in ("flux", "fluxerr", "mag", "magerr"):
-        atol = 1e-7 if nm in ("flux", "fluxerr") else 1e-9
-        assert_close(got[nm][ok], want[nm][ok], rtol=1e-9, atol=atol, what="%s %s" % (what, nm))
-    assert_close(got["sky"], want["sky"], rtol=1e-9, atol=1e-9, what=what + " sky")
-    assert_close(got["skyerr"], want["skyerr"], rtol=1e-9, atol=1e-9, what=what + " skyerr")
-    if nsky is not None:
-        assert np.array_equal(nsky, want_nsky), what + ": nsky differs"
-    return int(mism.sum())
+def _check_aper(got, want, o, what, nsky=None, want_nsky=None, mmm_iter=None):
+    """got/want: dicts of arrays; `o` = the oracle's return_extra tuple for the same call.  badflag bit-exact and values
+    1e-9 on robust apertures; a fragile aperture (its flag hinges on the sign of a rounding error in the reference itself,
+    see oracle/bphot_oracle.c) must equal one of the outcomes the reference admits (oracle/compare.py) -- nothing is skipped."""
+    from oracle import compare
+    rep = compare.compare_aper(got, want, o[9], nsky, want_nsky, mmm_iter, o[8] if mmm_iter is not None else None, alt=o[10])
+    assert rep["mismatches"] == 0, "%s: %r" % (what, rep)
+    assert rep["fragile_checked"] == rep["fragile"]
+    return rep
 
 
 @pytest.mark.parametrize("mode", ["py3", "py2"])
@@ -122,9 +114,9 @@ def test_aper_golden(pp, oracle, mode, cname):
     want = {nm: g["%s__%s__%s" % (mode, cname, nm)] for nm in NAMES}
     o = oracle.aper(g["image"], g["x"], g["y"], phpadu=float(g["phpadu"]), zeropoint=25.0, compat=mode,
                     return_extra=True, **kw)
-    nm = _check_aper(got, want, o[-1], "%s/%s" % (mode, cname), r[8]["nsky"], o[7])
-    assert np.array_equal(r[8]["mmm_iter"], o[8]), "mmm iteration counts differ"
-    print("fragile apertures: %d, of which flag differs: %d" % (o[-1].sum(), nm))
+    rep = _check_aper(got, want, o, "%s/%s" % (mode, cname), r[8]["nsky"], o[7], r[8]["mmm_iter"])
+    print("fragile apertures: %d (checked against the admissible outcomes), flag differs from the oracle's on %d" % (
+        rep["fragile"], rep["fragile_flag_differs"]))
 
 
 def test_aper_scalar_star_squeezes(pp):
@@ -146,9 +138,8 @@ def test_aper_vs_oracle_field(pp, oracle, dtype, exact, compat):
     got = dict(zip(NAMES, r[:7]))
     o = oracle.aper(f["image"], f["x"], f["y"], compat=compat, nthreads=0, return_extra=True, **kw)
     want = dict(zip(NAMES, o[:7]))
-    nm = _check_aper(got, want, o[-1], "field %s exact=%s %s" % (np.dtype(dtype).name, exact, compat), r[8]["nsky"], o[7])
-    assert np.array_equal(r[8]["mmm_iter"], o[8])
-    print("fragile: %d mismatching: %d of %d" % (o[-1].sum(), nm, o[-1].size))
+    rep = _check_aper(got, want, o, "field %s exact=%s %s" % (np.dtype(dtype).name, exact, compat), r[8]["nsky"], o[7], r[8]["mmm_iter"])
+    print("fragile: %d of %d, flag differs from the oracle's on %d" % (rep["fragile"], o[9].size, rep["fragile_flag_differs"]))
 
 
 @pytest.mark.parametrize("skyrad,fit96", [([12, 19.8], 768), ([40, 51.5], 3072)])
@@ -187,7 +178,7 @@ def test_aper_edge_matrix(pp, oracle):
                dict(apr=np.array([2., 3.]), skyrad=[10, 15], badpix=[-100, 60000], exact=True, setskyval=99.0)):
         r = pp.aper.aper(img, x, y, phpadu=2.0, verbose=False, return_info=True, **kw)
         o = oracle.aper(img, x, y, phpadu=2.0, return_extra=True, **kw)
-        _check_aper(dict(zip(NAMES, r[:7])), dict(zip(NAMES, o[:7])), o[-1], "edge %r" % (kw,), r[8]["nsky"], o[7])
+        _check_aper(dict(zip(NAMES, r[:7])), dict(zip(NAMES, o[:7])), o, "edge %r" % (kw,), r[8]["nsky"], o[7])
 
 
 def test_aper_properties_full_size(pp):
@@ -364,7 +355,7 @@ def test_c_abi_host_entry_points(pp, oracle):
     o = oracle.aper(img, f["x"], f["y"], phpadu=f["phpadu"], apr=apr, skyrad=(40, 50), badpix=(-12000, 60000), exact=True,
                     return_extra=True)
     got = dict(mag=outs[0], magerr=outs[1], flux=outs[2], fluxerr=outs[3], sky=sky, skyerr=skyerr, badflag=bad)
-    _check_aper(got, dict(zip(NAMES, o[:7])), o[-1], "bphot_aper_host", nsky, o[7])
+    _check_aper(got, dict(zip(NAMES, o[:7])), o, "bphot_aper_host", nsky, o[7])
 
     res = {k: np.empty(n) for k in ("errmag", "chi", "sharp", "scale", "x", "y", "chi2")}
     niter = np.empty(n, np.int32)

@@ -109,3 +109,39 @@ def test_pkfit_golden(kind, radius):
             assert_close(got[off], w[off], rtol=1e-6, atol=1e-12, what="%s r=%g sharp(off-frame)" % (kind, radius))
             got, w = got[~off], w[~off]
         assert_close(got, w, rtol=1e-9, atol=1e-12, what="%s r=%g %s" % (kind, radius, nm))
+
+
+@pytest.mark.parametrize("mode", ["py3", "py2"])
+def test_fragile_apertures_are_checked_against_the_admissible_outcomes(mode):
+    """oracle/compare.py on the reference's own goldens: every aperture is compared -- robust ones one to one, fragile ones
+    (a bad pixel where Pixwt returns 0 +- 1e-16) against the set of outcomes the reference's arithmetic admits.  The
+    'every fragile pixel left out' outcome (what a geometric classification of the pixels yields) must pass too, and a
+    wrong value on a robust or on a fragile aperture must not."""
+    from oracle import compare
+    g = load_golden("golden_aper.npz")
+    kw = dict(dict(APER_CASES)["exact_4050"])
+    o = oracle.aper(g["image"], g["x"], g["y"], phpadu=float(g["phpadu"]), zeropoint=25.0, compat=mode, return_extra=True, **kw)
+    want = {nm: g["%s__exact_4050__%s" % (mode, nm)] for nm in compare.APER_NAMES}
+    fragile, alt = o[9], o[10]
+    assert fragile.sum() > 20
+    rep = compare.compare_aper(dict(zip(compare.APER_NAMES, o[:7])), want, fragile, o[7], o[7], o[8], o[8], alt=alt)
+    assert rep["mismatches"] == 0 and rep["fragile_checked"] == rep["fragile"] == int(fragile.sum())
+    # an implementation that leaves every fragile pixel out
+    other = {nm: np.array(a, copy=True) for nm, a in zip(compare.APER_NAMES, o[:7])}
+    for nm in ("flux", "fluxerr", "mag", "magerr", "badflag"):
+        other[nm][fragile] = alt[nm][fragile]
+    assert (other["badflag"] != o[6]).any(), "the two outcomes should differ somewhere"
+    assert compare.compare_aper(other, want, fragile, alt=alt)["mismatches"] == 0
+    # wrong values are caught on both kinds of aperture
+    for sel in (fragile, ~fragile & np.isfinite(o[2])):
+        i, k = np.argwhere(sel)[3]
+        broken = {nm: np.array(a, copy=True) for nm, a in other.items()}
+        broken["flux"][i, k] *= 1.0 + 1e-6
+        assert compare.compare_aper(broken, want, fragile, alt=alt)["mismatches"] == 1
+    # a flag raised on a fragile aperture whose fragile pixels are all non-finite needs the zeroed sum with it
+    only_nan = fragile & ((alt["kind"] & 4) == 0) & (alt["badflag"] == 0)
+    if only_nan.any():
+        i, k = np.argwhere(only_nan)[0]
+        broken = {nm: np.array(a, copy=True) for nm, a in other.items()}
+        broken["badflag"][i, k] = 1
+        assert compare.compare_aper(broken, want, fragile, alt=alt)["mismatches"] == 1
