@@ -403,8 +403,9 @@ BP_D int2 gather_rows(const AperParams& P, const T* __restrict__ stamp, const St
 #pragma unroll
             for (int u = 0; u < U; u++) {
                 if (t < tot[u]) {
-                    const double dv = (double)val[u];
-                    const bool rej = window && (dv < P.badlo || dv > P.badhi);
+                    // aper.py:260-266 in the key type: for fp32 pixels badlo_t / badhi_t are the window rounded INWARD to
+                    // fp32 on the host, so val < badlo_t <=> (double)val < badlo exactly, without a conversion per pixel
+                    const bool rej = window && (val[u] < (T)(sizeof(T) == 4 ? P.badlo_t : P.badlo) || val[u] > (T)(sizeof(T) == 4 ? P.badhi_t : P.badhi));
                     const bool isnan_ = !rej && !(val[u] == val[u]);
                     nrej += rej;
                     nnan += isnan_;
@@ -545,23 +546,6 @@ constexpr size_t sort_index_bytes(size_t key_size) { return ((size_t)(16 + 256) 
 #ifndef AP_IDX_SKIP
 #define AP_IDX_SKIP 0  // timing experiments only (wrong results): 1 = no per-key sums, 2 = no scan, 4 = no writes, 8 = no median read
 #endif
-#ifndef AP_IDX_INTCVT
-#define AP_IDX_INTCVT 1  // fp32 key -> fp64 by integer bit manipulation (exact; zero / subnormal / inf / NaN take F2F)
-#endif
-// (double)x for a float, without the F2F.F64.F32 conversion unit (an eighth of the fp32 issue rate): a normal float's
-// sign, exponent (re-biased by 1023 - 127) and mantissa are moved into place with integer instructions.  Exact.
-BP_D double widen(float x) {
-#if AP_IDX_INTCVT
-    const unsigned b = __float_as_uint(x), e = (b >> 23) & 0xffu;
-    if (e == 0u || e == 0xffu) return (double)x;
-    const unsigned hi = (b & 0x80000000u) | (((b >> 3) & 0x0fffffffu) + 0x38000000u);
-    return __hiloint2double((int)hi, (int)(b << 29));
-#else
-    return (double)x;
-#endif
-}
-BP_D double widen(double x) { return x; }
-
 template <typename T, int K>
 BP_D void sort_index(const AperParams& P, const T (&r)[K], const T* __restrict__ dst, int nvalid, size_t row, int tid, double (*s_wsum)[2]) {
     static_assert(K == 8 || K == 16 || K == 32, "index groups are 16 keys");
@@ -576,16 +560,23 @@ BP_D void sort_index(const AperParams& P, const T (&r)[K], const T* __restrict__
     if (!(AP_IDX_SKIP & 8) && nvalid > 0) skymid = 0.5 * (double)__ldcg(dst + (nvalid - 1) / 2) + 0.5 * (double)__ldcg(dst + nvalid / 2);  // mmm.py:121
     const int e0 = tid * K;
     constexpr int H = K > 16 ? 16 : K;  // keys of this thread in its first index group
-    double a = 0.0, qq = 0.0, ha = 0.0, hq = 0.0;
+    // four independent chains of K/4 keys each (the adds of one chain wait for each other), folded pairwise
+    constexpr int C = K / 4;
+    double ca[4] = {0.0, 0.0, 0.0, 0.0}, cq[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
-    for (int q = 0; q < K; q++) {
-        if (q == H) { ha = a; hq = qq; }  // K = 32: sums of the first group
-        if (!(AP_IDX_SKIP & 1) && e0 + q < nvalid) {
-            const double d = widen(r[q]) - skymid;
-            a = a + d;
-            qq = __fma_rn(d, d, qq);
+    for (int q = 0; q < C; q++) {
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            if (!(AP_IDX_SKIP & 1) && e0 + c * C + q < nvalid) {
+                const double d = bp_widen(r[c * C + q]) - skymid;
+                ca[c] = ca[c] + d;
+                cq[c] = __fma_rn(d, d, cq[c]);
+            }
         }
     }
+    const double ha = ca[0] + ca[1], hq = cq[0] + cq[1];  // K = 32: sums of this thread's first group of 16
+    const double a = ha + (ca[2] + ca[3]), qq = hq + (cq[2] + cq[3]);
+    (void)H;
     // inclusive scan over the threads of the warp, then over the warps
     double ia_ = a, iq_ = qq;
 #pragma unroll

@@ -369,7 +369,7 @@ int bphot_version(void) { return BPHOT_VERSION; }
 const char* bphot_build_flags(void) {
     return "AP_ASM_SELECT=" BP_STR(AP_ASM_SELECT) " AP_BATCH=" BP_STR(AP_BATCH) " AP_S1_CTAS=" BP_STR(AP_S1_CTAS) " AP_MMM_INDEXED=" BP_STR(AP_MMM_INDEXED)
            " AP_S2_MINB=" BP_STR(AP_S2_MINB) " AP_SUMS_CTAS=" BP_STR(AP_SUMS_CTAS) " AP_DYNAMIC=" BP_STR(AP_DYNAMIC)
-           " PK_MINB_FORCED=" BP_STR(PK_MINB_FORCED) " PK_U=" BP_STR(PK_U) " PK_HOIST=" BP_STR(PK_HOIST) " AP_IDX_INTCVT=" BP_STR(AP_IDX_INTCVT) " AP_IDX_SKIP=" BP_STR(AP_IDX_SKIP);
+           " PK_MINB_FORCED=" BP_STR(PK_MINB_FORCED) " PK_U=" BP_STR(PK_U) " PK_HOIST=" BP_STR(PK_HOIST) " AP_IDX_SKIP=" BP_STR(AP_IDX_SKIP);
 }
 const char* bphot_last_error(void) { return g_err; }
 long long bphot_launch_count(void) { return g_launches.load(); }
@@ -422,6 +422,12 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     }
     if (!(skyrad_out >= 0.) || !(skyrad_in >= 0.) || !(skyrad_out < 1e4)) return fail(BPHOT_ERR_ARG, "bphot_aper: skyrad out of range");
     P.skyrad_in = skyrad_in; P.skyrad_out = skyrad_out; P.badlo = badlo; P.badhi = badhi;
+    {   // (double)v < badlo  <=>  v < (smallest float >= badlo);  (double)v > badhi  <=>  v > (largest float <= badhi)
+        float lo = (float)badlo, hi = (float)badhi;
+        if ((double)lo < badlo) lo = nextafterf(lo, INFINITY);
+        if ((double)hi > badhi) hi = nextafterf(hi, -INFINITY);
+        P.badlo_t = lo; P.badhi_t = hi;
+    }
     P.minsky = minsky; P.exact = exact ? 1 : 0; P.compat_py2 = (flags & BPHOT_APER_PY2) ? 1 : 0; P.mxiter = 50;
     P.sky_sigclip = (flags & BPHOT_APER_SIGMACLIP) ? 1 : 0;
     P.readnoise = readnoise;

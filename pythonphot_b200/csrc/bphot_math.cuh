@@ -413,6 +413,21 @@ BP_HD double mmm_log10n(int n) {
 }
 
 // ------------------------------------------------ indexed sorted vector
+// (double)x for a float without the F2F.F64.F32 conversion (measured on B200: replacing the 32 conversions per thread of
+// the stage-1 index by these integer instructions took 4.8 ms per 1 M stars off the kernel): a normal float's sign,
+// exponent (re-biased by 1023 - 127) and mantissa are moved into place.  Exact; zero, subnormal, inf and NaN take F2F.
+BP_HD double bp_widen(float x) {
+#if defined(__CUDA_ARCH__)
+    const unsigned b = __float_as_uint(x), e = (b >> 23) & 0xffu;
+    if (e == 0u || e == 0xffu) return (double)x;
+    const unsigned hi = (b & 0x80000000u) | (((b >> 3) & 0x0fffffffu) + 0x38000000u);
+    return __hiloint2double((int)hi, (int)(b << 29));
+#else
+    return (double)x;
+#endif
+}
+BP_HD double bp_widen(double x) { return x; }
+
 // read-only loads: __ldg on the device, plain on the host (tests/hostcheck)
 template <typename T>
 BP_HD T bp_ld(const T* p) {
@@ -450,7 +465,7 @@ struct IndexedView {
 #pragma unroll
             for (int q = 0; q < 4; q++) {
                 const float4 f = __ldg(reinterpret_cast<const float4*>(p) + q);
-                v[4 * q] = (double)f.x; v[4 * q + 1] = (double)f.y; v[4 * q + 2] = (double)f.z; v[4 * q + 3] = (double)f.w;
+                v[4 * q] = bp_widen(f.x); v[4 * q + 1] = bp_widen(f.y); v[4 * q + 2] = bp_widen(f.z); v[4 * q + 3] = bp_widen(f.w);
             }
         } else {
 #pragma unroll

@@ -21,6 +21,7 @@ struct AperParams {
     int naper;
     double skyrad_in, skyrad_out;  // already [0, max(apr)+1] when use_setsky (aper.py:156-160)
     double badlo, badhi;
+    float badlo_t, badhi_t;  // fp32 images: smallest float >= badlo, largest float <= badhi (exact fp32 form of the window test)
     int use_setsky;
     double setsky[3];
     int minsky, exact, compat_py2, mxiter;
