@@ -176,7 +176,15 @@ def cpu_baseline(field, a, nsample, threads=0, keep=False):
     idx = rng.choice(field["x"].size, size=min(nsample, field["x"].size), replace=False)
     t_aper, t_fit, out = oracle_pass(field, a.workload, field["x"][idx], field["y"][idx], field["xfit"][idx], field["yfit"][idx], nt)
     total = t_aper + t_fit
-    info = {"value": idx.size / total, "unit": "stars/s", "cores": nt, "kind": "port",
+    numpy_ref = None
+    try:  # the UNMODIFIED numpy reference on this workload, timed where /root/reference exists: a constant
+        t = json.load(open(os.path.join(ROOT, "tests", "golden", "reference_timing.json")))
+        numpy_ref = {"one_core_stars_per_s": t["one_core_readme_loop"]["stars_per_s"], "pool_stars_per_s": t["pool_all_cores"]["stars_per_s"],
+                     "pool_processes": t["pool_all_cores"]["processes"], "host": "authoring container (%d vCPU), not this box" % t["host"]["cpu_count"],
+                     "source": "tests/golden/reference_timing.json"}
+    except Exception:
+        pass
+    info = {"value": idx.size / total, "unit": "stars/s", "cores": nt, "kind": "port", "numpy_reference": numpy_ref,
             "sample": "%d random stars of the same exposure and star list (oracle/bphot_oracle.c, OpenMP, %d threads)" % (idx.size, nt),
             "aper_stars_per_s": (idx.size / t_aper) if t_aper else None, "pkfit_stars_per_s": (idx.size / t_fit) if t_fit else None}
     return (info, idx, out) if keep else info

@@ -369,7 +369,7 @@ int bphot_version(void) { return BPHOT_VERSION; }
 const char* bphot_build_flags(void) {
     return "AP_ASM_SELECT=" BP_STR(AP_ASM_SELECT) " AP_BATCH=" BP_STR(AP_BATCH) " AP_S1_CTAS=" BP_STR(AP_S1_CTAS) " AP_MMM_INDEXED=" BP_STR(AP_MMM_INDEXED)
            " AP_S2_MINB=" BP_STR(AP_S2_MINB) " AP_SUMS_CTAS=" BP_STR(AP_SUMS_CTAS) " AP_DYNAMIC=" BP_STR(AP_DYNAMIC)
-           " PK_MINB_FORCED=" BP_STR(PK_MINB_FORCED) " PK_U=" BP_STR(PK_U) " PK_HOIST=" BP_STR(PK_HOIST) " AP_IDX_SKIP=" BP_STR(AP_IDX_SKIP);
+           " PK_MINB_FORCED=" BP_STR(PK_MINB_FORCED) " PK_U=" BP_STR(PK_U) " PK_HOIST=" BP_STR(PK_HOIST) " PK_PSF_GLOBAL=" BP_STR(PK_PSF_GLOBAL) " AP_IDX_SKIP=" BP_STR(AP_IDX_SKIP);
 }
 const char* bphot_last_error(void) { return g_err; }
 long long bphot_launch_count(void) { return g_launches.load(); }
@@ -618,7 +618,8 @@ int bphot_pkfit_device(int variant, const void* d_image, int image_dtype,
     P.scale_out = d_scale_out; P.x_out = d_x_out; P.y_out = d_y_out; P.chi2 = d_chi2;
     P.acap = 2 * (int)ceil(radius) + 4;  // int(x+r)+1 - int(x-r) + 1 <= 2r + 3
     const int narr = (variant == BPHOT_PKFIT_NORECENT) ? PK_NARR_FORCED : PK_NARR_FIT;
-    const size_t smem = (size_t)npsf * npsf * 8 + (size_t)PK_WARPS * ((size_t)P.cap * (narr * 8 + 4) + (size_t)P.acap * 32);
+    const size_t tab = (PK_PSF_GLOBAL && variant == BPHOT_PKFIT_NORECENT) ? 0 : (size_t)npsf * npsf * 8;
+    const size_t smem = tab + (size_t)PK_WARPS * ((size_t)P.cap * (narr * 8 + 4) + (size_t)P.acap * 32);
     DevInfo d;
     int rc = dev_info(&d);
     if (rc) return rc;

@@ -413,9 +413,10 @@ BP_HD double mmm_log10n(int n) {
 }
 
 // ------------------------------------------------ indexed sorted vector
-// (double)x for a float without the F2F.F64.F32 conversion (measured on B200: replacing the 32 conversions per thread of
-// the stage-1 index by these integer instructions took 4.8 ms per 1 M stars off the kernel): a normal float's sign,
-// exponent (re-biased by 1023 - 127) and mantissa are moved into place.  Exact; zero, subnormal, inf and NaN take F2F.
+// (double)x for a float without the F2F.F64.F32 conversion: a normal float's sign, exponent (re-biased by 1023 - 127) and
+// mantissa are moved into place by integer instructions.  Exact; zero, subnormal, inf and NaN take F2F.  Measured on
+// B200: in the stage-1 index (32 conversions per thread feeding dependent fp64 adds) it took 4.8 ms per 1 M stars off
+// the kernel; in the indexed mmm's 16-key group loads it cost 1.9 ms (the branch per key), so only the index uses it.
 BP_HD double bp_widen(float x) {
 #if defined(__CUDA_ARCH__)
     const unsigned b = __float_as_uint(x), e = (b >> 23) & 0xffu;
@@ -465,7 +466,7 @@ struct IndexedView {
 #pragma unroll
             for (int q = 0; q < 4; q++) {
                 const float4 f = __ldg(reinterpret_cast<const float4*>(p) + q);
-                v[4 * q] = bp_widen(f.x); v[4 * q + 1] = bp_widen(f.y); v[4 * q + 2] = bp_widen(f.z); v[4 * q + 3] = bp_widen(f.w);
+                v[4 * q] = (double)f.x; v[4 * q + 1] = (double)f.y; v[4 * q + 2] = (double)f.z; v[4 * q + 3] = (double)f.w;
             }
         } else {
 #pragma unroll

@@ -48,6 +48,9 @@ BP_D double pk_max(double v) { return warp_max(v); }
 constexpr int PK_WARPS = 4;
 constexpr int PK_THREADS = PK_WARPS * 32;
 constexpr int PK_NARR_FIT = 10;     // per-warp scratch arrays of `cap` doubles, recentring variants
+#ifndef PK_PSF_GLOBAL
+#define PK_PSF_GLOBAL 0  // 1 = the residual look-up table is read from global memory (L1-resident, 13 KB) instead of a per-CTA shared copy
+#endif
 #ifndef PK_HOIST
 #define PK_HOIST 1  // forced fit: W0/sigsq and dfs*dfs/sigsq (operands fixed at set-up) are divided once per star, not per iteration
 #endif
@@ -604,13 +607,14 @@ template <int V, typename TI, typename TN>
 __global__ void __launch_bounds__(PK_THREADS, V == 2 ? PK_MINB_FORCED : 1) pkfit_kernel(const PkfitParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int NARR = (V == 2) ? PK_NARR_FORCED : PK_NARR_FIT;
-    double* psf = reinterpret_cast<double*>(smem_raw);
-    const int ntab = P.npsf * P.npsf;
+    double* sbase = reinterpret_cast<double*>(smem_raw);
+    const int ntab = (PK_PSF_GLOBAL && V == 2) ? 0 : P.npsf * P.npsf;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    double* W = psf + ntab + (size_t)warp * NARR * P.cap;
-    double* AX = psf + ntab + (size_t)PK_WARPS * NARR * P.cap + (size_t)warp * 4 * P.acap;
-    int* GIDX = reinterpret_cast<int*>(psf + ntab + (size_t)PK_WARPS * (NARR * P.cap + 4 * P.acap)) + (size_t)warp * P.cap;
-    for (int i = threadIdx.x; i < ntab; i += PK_THREADS) psf[i] = P.psf[i];
+    double* W = sbase + ntab + (size_t)warp * NARR * P.cap;
+    double* AX = sbase + ntab + (size_t)PK_WARPS * NARR * P.cap + (size_t)warp * 4 * P.acap;
+    int* GIDX = reinterpret_cast<int*>(sbase + ntab + (size_t)PK_WARPS * (NARR * P.cap + 4 * P.acap)) + (size_t)warp * P.cap;
+    for (int i = threadIdx.x; i < ntab; i += PK_THREADS) sbase[i] = P.psf[i];
+    const double* __restrict__ psf = ntab ? sbase : P.psf;
     __syncthreads();
     // stars are drawn from a counter, not a fixed stride: fits take 3 to 25 iterations, and a launch should end with
     // its last star, not with the warp that was dealt the most slow ones
