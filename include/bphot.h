@@ -95,6 +95,23 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
                       double* d_mag, double* d_magerr, double* d_flux, double* d_fluxerr,
                       double* d_sky, double* d_skyerr, unsigned char* d_badflag,
                       int* d_nsky, int* d_mmm_iter, void* stream);
+/*
+ * The same call for an image that is STILL BEING UPLOADED: the caller copies the image into d_image in bands of
+ * `band_rows` rows, top to bottom, on a copy stream of its own, and records band_events[k] (cudaEvent_t) once rows
+ * [0, (k+1)*band_rows) are resident.  Stars are visited in image-tile order, so every batch of the sort stage waits only
+ * for the band that covers its lowest stamp row and the upload runs under the kernels instead of in front of them
+ * (bench.py's end-to-end leg; pythonphot_b200.aper.aper does this for host arrays).  nbands = 0 is bphot_aper_device.
+ */
+int bphot_aper_device_banded(const void* d_image, int image_dtype, int nrow, int ncol, long long pitch,
+                             const double* d_xc, const double* d_yc, int nstars,
+                             double phpadu, const double* apr, int naper, double zeropoint,
+                             double skyrad_in, double skyrad_out, double badlo, double badhi,
+                             int use_setsky, const double* setsky, int minsky, int exact,
+                             double readnoise, int flags,
+                             double* d_mag, double* d_magerr, double* d_flux, double* d_fluxerr,
+                             double* d_sky, double* d_skyerr, unsigned char* d_badflag,
+                             int* d_nsky, int* d_mmm_iter,
+                             const void* const* band_events, int nbands, int band_rows, void* stream);
 
 int bphot_aper_host(const void* image, int image_dtype, int nrow, int ncol,
                     const double* xc, const double* yc, int nstars,

@@ -33,6 +33,8 @@ _SIGNATURES = {
     "bphot_kernel_times": (C.c_int, [_vp, _vp]),
     "bphot_aper_device": (C.c_int, [_vp, _i, _i, _i, _ll, _vp, _vp, _i, _d, _vp, _i, _d, _d, _d, _d, _d, _i, _vp, _i, _i,
                                     _d, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "bphot_aper_device_banded": (C.c_int, [_vp, _i, _i, _i, _ll, _vp, _vp, _i, _d, _vp, _i, _d, _d, _d, _d, _d, _i, _vp, _i, _i,
+                                           _d, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
     "bphot_aper_host": (C.c_int, [_vp, _i, _i, _i, _vp, _vp, _i, _d, _vp, _i, _d, _d, _d, _d, _d, _i, _vp, _i, _i,
                                   _d, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i]),
     "bphot_pkfit_device": (C.c_int, [_i, _vp, _i, _vp, _i, _vp, _i, _i, _ll, _ll, _ll, _vp, _vp, _i, _d, _d,
@@ -139,6 +141,62 @@ def copy_stream(device):
     if key not in _copy_streams:
         _copy_streams[key] = torch.cuda.Stream(device=device)
     return _copy_streams[key]
+
+
+class DeviceImage(object):
+    """An image in HBM that may still be arriving: ``tensor`` plus, for a banded upload, one CUDA event per band of
+    ``band_rows`` rows (event k fires when rows [0, (k+1)*band_rows) are resident).  ``aper.aper`` hands the events to
+    ``bphot_aper_device_banded`` so that its kernels start while the upload runs; everything else calls ``ready()``."""
+
+    def __init__(self, tensor, events=None, band_rows=0):
+        self.tensor, self.events, self.band_rows = tensor, events, band_rows
+
+    @property
+    def shape(self):
+        return self.tensor.shape
+
+    @property
+    def device(self):
+        return self.tensor.device
+
+    def ready(self):
+        """The tensor, after making the current stream wait for the whole upload."""
+        if self.events:
+            torch_cuda().cuda.current_stream(self.tensor.device).wait_event(self.events[-1])
+        return self.tensor
+
+
+BAND_MIN_BYTES = 32 << 20  # smaller images go up in one piece
+
+
+def upload_image_banded(a, device, nbands=16):
+    """Host array -> ``DeviceImage`` uploaded in ``nbands`` row bands on the copy stream (asynchronous when ``a`` is
+    page-locked).  Small images and CUDA tensors come back as a plain, already ordered ``DeviceImage``."""
+    torch = torch_cuda()
+    if isinstance(a, DeviceImage):
+        return a
+    if isinstance(a, torch.Tensor) or np.asarray(a).nbytes < BAND_MIN_BYTES:
+        return DeviceImage(to_device_image(a, device))
+    a = np.asarray(a)
+    if a.dtype != np.float32:
+        a = a.astype(np.float64, copy=False)
+    a = np.ascontiguousarray(a)
+    if a.ndim != 2:
+        raise BphotError("image must be 2-D, got shape %s" % (a.shape,))
+    host = torch.from_numpy(a)
+    cur, up = torch.cuda.current_stream(device), copy_stream(device)
+    t = torch.empty(a.shape, dtype=host.dtype, device=device)
+    up.wait_stream(cur)
+    rows = (a.shape[0] + nbands - 1) // nbands
+    events = []
+    with torch.cuda.stream(up):
+        for r0 in range(0, a.shape[0], rows):
+            t[r0:r0 + rows].copy_(host[r0:r0 + rows], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(up)
+            events.append(ev)
+    t.record_stream(up)
+    return DeviceImage(t, events, rows)
 
 
 def dtype_code(t):

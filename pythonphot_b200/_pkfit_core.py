@@ -25,24 +25,22 @@ class PkfitEngine(object):
         # Host arrays go up on a copy stream of their own, image first: the constructor returns while the copies run
         # (when the arrays are page-locked), ``image_device()`` waits for the image only, the fits for all three -- so
         # work queued in between, e.g. ``aper.aper(pk.image_device(), ...)``, overlaps the noise and mask uploads.
-        host_in = any(a is not None and not isinstance(a, torch.Tensor) for a in (image, noiseim, maskim))
-        self._ev_img = self._ev_all = None
+        host_in = any(a is not None and not isinstance(a, (torch.Tensor, _lib.DeviceImage)) for a in (image, noiseim, maskim))
+        self._ev_all = None
+        self._dimg = _lib.upload_image_banded(image, self.device)  # banded, on the copy stream, when it is a large host array
+        self._img_t = self._dimg.tensor
         if host_in:
             cur, up = torch.cuda.current_stream(self.device), _lib.copy_stream(self.device)
             up.wait_stream(cur)
             with torch.cuda.stream(up):
-                self._img_t = _lib.to_device_image(image, self.device)
-                self._ev_img = torch.cuda.Event()
-                self._ev_img.record(up)
                 self._noise_t = _lib.to_device_image(noiseim, self.device) if noiseim is not None else None
                 self._mask_t = _lib.to_device_mask(maskim, self.device) if maskim is not None else None
                 self._ev_all = torch.cuda.Event()
                 self._ev_all.record(up)
-            for t in (self._img_t, self._noise_t, self._mask_t):
+            for t in (self._noise_t, self._mask_t):
                 if t is not None:
                     t.record_stream(cur)
         else:
-            self._img_t = _lib.to_device_image(image, self.device)
             self._noise_t = _lib.to_device_image(noiseim, self.device) if noiseim is not None else None
             self._mask_t = _lib.to_device_mask(maskim, self.device) if maskim is not None else None
         for name, t in (("noise", self._noise_t), ("mask", self._mask_t)):
@@ -59,15 +57,13 @@ class PkfitEngine(object):
 
     # ------------------------------------------------------------------
     def image_device(self):
-        """The image as it sits in HBM (a CUDA tensor), for calls that work on the same exposure -- e.g.
-        ``aper.aper(pk.image_device(), xc, yc, ...)`` -- so that it crosses PCIe once.  The current stream is made to
-        wait for the upload."""
-        torch = _lib.torch_cuda()
-        if self._ev_img is not None:
-            torch.cuda.current_stream(self.device).wait_event(self._ev_img)
-        return self._img_t
+        """The image as it sits (or arrives) in HBM, a ``_lib.DeviceImage``, for calls that work on the same exposure --
+        e.g. ``aper.aper(pk.image_device(), xc, yc, ...)`` -- so that it crosses PCIe once.  ``.ready()`` gives the
+        plain CUDA tensor after the upload."""
+        return self._dimg
 
     def _uploads_done(self):
+        self._dimg.ready()
         if self._ev_all is not None:
             torch = _lib.torch_cuda()
             torch.cuda.current_stream(self.device).wait_event(self._ev_all)

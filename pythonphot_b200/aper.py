@@ -42,13 +42,15 @@ def _minsky_value(minsky):
 
 def aper_device(image_t, xc_t, yc_t, phpadu=1, apr=5, zeropoint=25, skyrad=(40, 50), badpix=(0, 0),
                 setskyval=None, minsky=20, exact=False, readnoise=0, compat='py3', out=None, skyalgorithm='mmm',
-                _narrow_ctas=False):
+                _narrow_ctas=False, bands=None):
     """Device-resident core: ``image_t`` [nrow, ncol] and ``xc_t``/``yc_t`` [nstars] are CUDA tensors.
 
     Enqueues one kernel on the current stream and returns a dict of CUDA tensors
     (mag, magerr, flux, fluxerr [nstars, naper] fp64; sky, skyerr [nstars] fp64; badflag uint8
     [nstars, naper]; nsky, mmm_iter int32 [nstars]) without synchronising.  ``out`` may carry a
-    dict from a previous call with the same shapes to reuse its buffers (checked: shape, dtype, device)."""
+    dict from a previous call with the same shapes to reuse its buffers (checked: shape, dtype, device).
+    ``bands`` = ``(events, band_rows)`` of an image that is still being uploaded band by band (``_lib.DeviceImage``):
+    the kernels of each star batch wait only for the band they read (``bphot_aper_device_banded``)."""
     torch = _lib.torch_cuda()
     if compat not in ('py3', 'py2'):
         raise ValueError("compat must be 'py3' or 'py2'")
@@ -72,8 +74,12 @@ def aper_device(image_t, xc_t, yc_t, phpadu=1, apr=5, zeropoint=25, skyrad=(40, 
     out = _lib.alloc_out([('mag', f64, na), ('magerr', f64, na), ('flux', f64, na), ('fluxerr', f64, na), ('sky', f64, ()),
                           ('skyerr', f64, ()), ('badflag', torch.uint8, na), ('nsky', torch.int32, ()),
                           ('mmm_iter', torch.int32, ())], n, dev, out)
+    ev_arr, nbands, band_rows = None, 0, 0
+    if bands is not None and bands[0]:
+        nbands, band_rows = len(bands[0]), int(bands[1])
+        ev_arr = (C.c_void_p * nbands)(*[C.c_void_p(e.cuda_event) for e in bands[0]])
     with torch.cuda.device(dev):
-        rc = _lib.lib().bphot_aper_device(
+        rc = _lib.lib().bphot_aper_device_banded(
             _lib.ptr(image_t), _lib.dtype_code(image_t), image_t.shape[0], image_t.shape[1], image_t.stride(0),
             _lib.ptr(xc_t), _lib.ptr(yc_t), n, float(phpadu), _lib.nptr(apr_h), naper, float(zeropoint),
             float(skyrad[0]), float(skyrad[1]), float(badpix[0]), float(badpix[1]), use_setsky, _lib.nptr(ssv),
@@ -82,7 +88,8 @@ def aper_device(image_t, xc_t, yc_t, phpadu=1, apr=5, zeropoint=25, skyrad=(40, 
             | (_lib.APER_NARROW_CTAS if _narrow_ctas else 0),
             _lib.ptr(out['mag']), _lib.ptr(out['magerr']), _lib.ptr(out['flux']), _lib.ptr(out['fluxerr']),
             _lib.ptr(out['sky']), _lib.ptr(out['skyerr']), _lib.ptr(out['badflag']), _lib.ptr(out['nsky']),
-            _lib.ptr(out['mmm_iter']), _lib.stream_ptr(dev))
+            _lib.ptr(out['mmm_iter']), C.cast(ev_arr, C.c_void_p) if ev_arr is not None else C.c_void_p(0), nbands, band_rows,
+            _lib.stream_ptr(dev))
     _lib.check(rc)
     return out
 
@@ -98,30 +105,36 @@ def aper(image, xc, yc, phpadu=1, apr=5, zeropoint=25,
     (keyword only in spirit): ``compat`` selects how aper.py:246-248 is read -- 'py3' = as the
     reference runs today (pixel y-centre = row + col/nx when exact=True), 'py2' = the Python-2
     integer row it was written for; ``device`` picks the CUDA device; ``return_info`` appends a dict
-    with ``nsky`` and ``mmm_iter`` per star.  ``image`` may be a numpy array or a CUDA tensor; a
+    with ``nsky`` and ``mmm_iter`` per star.  ``image`` may be a numpy array, a CUDA tensor or the ``DeviceImage`` a
+    ``pkfit_class`` made of the same exposure (``pk.image_device()``: the image then crosses PCIe once for both); a
     float32 image is widened per pixel on the GPU, i.e. results equal the reference called with
     ``image.astype(float64)``.  ``apr`` may also be a list (the reference needs scalar/ndarray).
     """
     if skyalgorithm != 'mmm' and not str(skyalgorithm).startswith('sigmaclip'):  # aper.py:275: anything else means mmm
         skyalgorithm = 'mmm'
     torch = _lib.torch_cuda()
-    dev = _lib.device_of(device if device is not None else (image.device if isinstance(image, torch.Tensor) and image.is_cuda else None))
+    on_dev = isinstance(image, _lib.DeviceImage) or (isinstance(image, torch.Tensor) and image.is_cuda)
+    dev = _lib.device_of(device if device is not None else (image.device if on_dev else None))
     # aper.py:134-148
     if not np.iterable(xc):
         xc, yc = np.array([xc]), np.array([yc])
     assert len(xc) == len(yc), 'xc and yc arrays must be identical length.'
     nstars = len(xc)
-    img_t = _lib.to_device_image(image, dev)
+    # a large host image goes up in row bands on a copy stream while the kernels already work on the rows that arrived
+    dimg = _lib.upload_image_banded(image, dev)
+    img_t = dimg.tensor
     xc_t = _lib.to_device_f64(xc, dev)
     yc_t = _lib.to_device_f64(yc, dev)
     o = aper_device(img_t, xc_t, yc_t, phpadu=phpadu, apr=apr, zeropoint=zeropoint, skyrad=skyrad, badpix=badpix,
                     setskyval=setskyval, minsky=_minsky_value(minsky), exact=exact, readnoise=readnoise,
-                    compat=compat, skyalgorithm=skyalgorithm)
+                    compat=compat, skyalgorithm=skyalgorithm, bands=(dimg.events, dimg.band_rows) if dimg.events else None)
+    o = dict(o)
+    o['badflag'] = o['badflag'].to(torch.float64)  # the reference stores 0./1. (aper.py:174); cast on the device, not on the host
     with torch.cuda.device(dev):
         h = dict(zip(o.keys(), _lib.to_host(list(o.values()))))
     mag, magerr, flux, fluxerr = h['mag'], h['magerr'], h['flux'], h['fluxerr']
     sky, skyerr = h['sky'], h['skyerr']
-    badflag = h['badflag'].astype(np.float64)  # the reference stores 0./1. (aper.py:174)
+    badflag = h['badflag']
     xh = np.asarray(xc.cpu() if isinstance(xc, torch.Tensor) else xc, dtype=np.float64).reshape(-1)
     yh = np.asarray(yc.cpu() if isinstance(yc, torch.Tensor) else yc, dtype=np.float64).reshape(-1)
     outstr = OutStr(xh, yh, mag, magerr)

@@ -7,6 +7,7 @@
 #include <string.h>
 
 #include <atomic>
+#include <vector>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_select.cuh>
 #include <thrust/iterator/counting_iterator.h>
@@ -188,6 +189,23 @@ __global__ void tile_key_kernel(const double* x, const double* y, int n, int nro
         keys[i] = ((unsigned)((int)yv >> 5) << 16) | (unsigned)((int)xv >> 5);
         idx[i] = i;
     }
+}
+// largest y of the stars of each batch of the visiting order (one CTA per batch): which image rows the batch needs
+__global__ void batch_maxrow_kernel(const double* y, const int* order, int n, int batch, float* out) {
+    __shared__ float s[256];
+    const int b = blockIdx.x;
+    float m = -1e30f;
+    for (int i = b * batch + threadIdx.x; i < n && i < (b + 1) * batch; i += blockDim.x) {
+        const double v = y[order[i]];
+        if (v == v) m = fmaxf(m, (float)v + 1.0f);  // +1: fp32 rounding of the row
+    }
+    s[threadIdx.x] = m;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) s[threadIdx.x] = fmaxf(s[threadIdx.x], s[threadIdx.x + o]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[b] = s[0];
 }
 struct StarOrder {  // stream-ordered allocations, released by release()
     void* block = nullptr;
@@ -400,7 +418,24 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
                       double* d_mag, double* d_magerr, double* d_flux, double* d_fluxerr,
                       double* d_sky, double* d_skyerr, unsigned char* d_badflag,
                       int* d_nsky, int* d_mmm_iter, void* stream) {
+    return bphot_aper_device_banded(d_image, image_dtype, nrow, ncol, pitch, d_xc, d_yc, nstars, phpadu, apr, naper, zeropoint,
+                                    skyrad_in, skyrad_out, badlo, badhi, use_setsky, setsky, minsky, exact, readnoise, flags,
+                                    d_mag, d_magerr, d_flux, d_fluxerr, d_sky, d_skyerr, d_badflag, d_nsky, d_mmm_iter,
+                                    nullptr, 0, 0, stream);
+}
+
+int bphot_aper_device_banded(const void* d_image, int image_dtype, int nrow, int ncol, long long pitch,
+                             const double* d_xc, const double* d_yc, int nstars,
+                             double phpadu, const double* apr, int naper, double zeropoint,
+                             double skyrad_in, double skyrad_out, double badlo, double badhi,
+                             int use_setsky, const double* setsky, int minsky, int exact,
+                             double readnoise, int flags,
+                             double* d_mag, double* d_magerr, double* d_flux, double* d_fluxerr,
+                             double* d_sky, double* d_skyerr, unsigned char* d_badflag,
+                             int* d_nsky, int* d_mmm_iter,
+                             const void* const* band_events, int nbands, int band_rows, void* stream) {
     using namespace bphot;
+    if (nbands < 0 || (nbands > 0 && (!band_events || band_rows <= 0))) return fail(BPHOT_ERR_ARG, "bphot_aper: bad band description");
     if (!d_image || !apr || nstars < 0 || nrow <= 0 || ncol <= 0) return fail(BPHOT_ERR_ARG, "bphot_aper: null image/apr or bad shape");
     if (naper < 1 || naper > BPHOT_MAX_APER) return fail(BPHOT_ERR_ARG, "bphot_aper: naper=%d outside 1..%d", naper, BPHOT_MAX_APER);
     if (image_dtype != BPHOT_F32 && image_dtype != BPHOT_F64) return fail(BPHOT_ERR_ARG, "bphot_aper: image dtype %d", image_dtype);
@@ -472,6 +507,30 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
     rc = make_star_order(d_xc, d_yc, nstars, nrow, ncol, st, &ord);
     if (rc) { if (scratch) cudaFreeAsync(scratch, st); cudaFreeAsync(counters, st); return rc; }
     P.order = ord.order;
+    // image still in flight (band_events): which band has to be resident before each batch of stars may start
+    std::vector<int> batch_band;
+    auto wait_band = [&](int band) { cudaStreamWaitEvent(st, (cudaEvent_t)band_events[band < nbands - 1 ? band : nbands - 1], 0); };
+    if (nbands > 0) {
+        batch_band.assign(nbatch, nbands - 1);
+        if (ord.order) {
+            float* d_max = nullptr;
+            std::vector<float> h_max(nbatch, 0.f);
+            cudaError_t e = cudaMallocAsync((void**)&d_max, nbatch * sizeof(float), st);
+            if (e == cudaSuccess) {
+                batch_maxrow_kernel<<<nbatch, 256, 0, st>>>(d_yc, ord.order, nstars, batch, d_max);
+                e = cudaMemcpyAsync(h_max.data(), d_max, nbatch * sizeof(float), cudaMemcpyDeviceToHost, st);
+                if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+                cudaFreeAsync(d_max, st);
+                g_launches += 1;
+            }
+            if (e == cudaSuccess)
+                for (int b = 0; b < nbatch; b++) {
+                    const double last = (double)h_max[b] + skyrad_out + 2.0;  // lowest image row any stamp of the batch reads
+                    const long long band = (long long)(last < 0 ? 0 : last) / band_rows;
+                    batch_band[b] = (int)(band < nbands - 1 ? band : nbands - 1);
+                }
+        }
+    }
     int grid1 = 0, grid2 = 0;
     // stage-1 CTA: 4 warps, or 3 when every annulus fits 96 threads x K keys (the 4th warp of the network would hold
     // only padding; without it 8 CTAs fit an SM instead of 6)
@@ -526,7 +585,7 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
         cudaEventRecord(ev_fork, st);
         cudaStreamWaitEvent(side, ev_fork, 0);
     }
-    {
+    auto launch_sums = [&]() {
         int grida = 0;
         const long long nb = ((long long)nstars + AP_WARPS - 1) / AP_WARPS;
         cudaStream_t sa = side ? side : st;
@@ -544,10 +603,12 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
         lt.end();
         g_launches += 1;
         if (side) cudaEventRecord(ev_join, side);
-    }
+    };
+    if (nbands == 0) launch_sums();  // otherwise after the batches: by then the whole image is resident
     for (int s0 = 0; s0 < nstars && !rc; s0 += batch) {
         P.s0 = s0;
         P.scount = (nstars - s0) < batch ? (nstars - s0) : batch;
+        if (nbands > 0) wait_band(batch_band[s0 / batch]);
         lt.begin(KT_APER_STAGE1);
         if (image_dtype == BPHOT_F32) BP_STAGE1_K(float);
         else BP_STAGE1_K(double);
@@ -562,6 +623,11 @@ int bphot_aper_device(const void* d_image, int image_dtype, int nrow, int ncol, 
 #undef BP_STAGE2
 #undef BP_STAGE1_K
 #undef BP_STAGE1
+    if (nbands > 0 && !rc) {
+        wait_band(nbands - 1);
+        P.s0 = 0; P.scount = nstars;
+        launch_sums();
+    }
     if (side) {
         cudaStreamWaitEvent(st, ev_join, 0);
         cudaEventDestroy(ev_fork);

@@ -24,3 +24,33 @@ def test_notebook_pipeline_recovers_the_planted_stars():
     # recentring fits converge for the bulk of the stars and recover the planted fluxes of isolated bright stars
     conv = (r["niter"] > 0) & (r["niter"] < 25) & np.isfinite(r["scale"])
     assert conv.mean() > 0.8
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pinned", [False, True])
+def test_aper_banded_upload_equals_resident_image(pinned):
+    """A large host image goes up in row bands on a copy stream while the kernels of the first star batches already run
+    (bphot_aper_device_banded); every output must equal the call on the resident image bit for bit, for page-locked and
+    pageable host memory, and pkfit_class must hand the same (possibly still arriving) image to aper."""
+    import torch
+    import pythonphot_b200 as pp
+    from pythonphot_b200 import _lib, synth
+    f = synth.make_field(3000, 3100, 140000, seed=17, dtype=np.float32)
+    assert f["image"].nbytes >= _lib.BAND_MIN_BYTES
+    img = torch.from_numpy(f["image"]).pin_memory().numpy() if pinned else f["image"]
+    kw = dict(phpadu=f["phpadu"], apr=np.array([3., 5.]), skyrad=[40, 50], badpix=[-12000, 60000], exact=True, verbose=False)
+    want = pp.aper.aper(torch.from_numpy(f["image"]).cuda(), f["x"], f["y"], **kw)
+    got = pp.aper.aper(img, f["x"], f["y"], **kw)
+    pk = pp.pkfit_class(img, f["gauss"], f["psf"], f["ronois"], f["phpadu"], f["noise"], f["mask"])
+    assert pk.image_device().events, "the engine should have uploaded the image in bands"
+    via_pk = pp.aper.aper(pk.image_device(), f["x"], f["y"], **kw)
+    for i in range(7):
+        for other in (got, via_pk):
+            assert np.array_equal(np.nan_to_num(other[i], nan=-1.0), np.nan_to_num(want[i], nan=-1.0)), "output %d differs" % i
+    n = 2000
+    a = pk.pkfit_norecent_noise(np.ones(n), f["xfit"][:n], f["yfit"][:n], np.full(n, f["sky"]), 5.0)
+    pk2 = pp.pkfit_class(torch.from_numpy(f["image"]).cuda(), f["gauss"], f["psf"], f["ronois"], f["phpadu"],
+                         torch.from_numpy(f["noise"]).cuda(), torch.from_numpy(f["mask"]).cuda())
+    b = pk2.pkfit_norecent_noise(np.ones(n), f["xfit"][:n], f["yfit"][:n], np.full(n, f["sky"]), 5.0)
+    for u, v in zip(a, b):
+        assert np.array_equal(np.nan_to_num(u, nan=-1.0), np.nan_to_num(v, nan=-1.0))
