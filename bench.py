@@ -57,6 +57,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-config5", action="store_true", help="N > 1: skip the config5 block")
+    ap.add_argument("--image-dtype", default="float32", choices=["float32", "float64"],
+                    help="pixel type of image and noise (float64 = the reference's native dtype; the default workload is fp32)")
     ap.add_argument("--c5-size", type=int, default=16384)
     ap.add_argument("--c5-stars", type=int, default=10000000, help="config5: stars in TOTAL (strong scaling)")
     return ap.parse_args()
@@ -71,15 +73,17 @@ def host_threads():
 
 
 def workload_name(a):
-    return "%dx%d fp32 image+noise+u8 mask, %d stars/GPU, aper exact apr=[3,5,8] skyrad=[40,50] + forced pkfit_norecent_noise r=5" % (
+    name = "%dx%d fp32 image+noise+u8 mask, %d stars/GPU, aper exact apr=[3,5,8] skyrad=[40,50] + forced pkfit_norecent_noise r=5" % (
         a.size, a.size, a.stars) if a.workload == "both" else (
         "%dx%d fp32, %d stars/GPU, aper exact apr=[3,5,8] skyrad=[40,50]" % (a.size, a.size, a.stars) if a.workload == "aper"
         else "%dx%d fp32 image+noise+u8 mask, %d stars/GPU, forced pkfit_norecent_noise r=5" % (a.size, a.size, a.stars))
+    return name.replace("fp32", "fp64") if a.image_dtype == "float64" else name
 
 
 def config_dict(a, world):
     """The same dict from both arms (the driver compares them): it names the workload, nothing measured goes in here."""
-    mb = a.size * a.size * (4 + 4 + 1) / 1e6
+    es = 8 if a.image_dtype == "float64" else 4
+    mb = a.size * a.size * (es + es + 1) / 1e6
     return {"workload": workload_name(a), "stars_total": world * a.stars,
             "l2_policy": "inputs larger than L2 (image+noise+mask = %.0f MB)" % mb,
             "parallelism": "star-sharded x%d, exposure replicated" % world}
@@ -87,7 +91,7 @@ def config_dict(a, world):
 
 def make_field(a, seed=1004):
     from pythonphot_b200 import synth
-    return synth.make_field(a.size, a.size, a.stars, seed=seed, dtype=np.float32)
+    return synth.make_field(a.size, a.size, a.stars, seed=seed, dtype=np.dtype(a.image_dtype).type)
 
 
 # ----------------------------------------------------------------------------- clocks
@@ -435,8 +439,9 @@ def main():
     else:
         field, host = None, None
     shape = (a.size, a.size)
-    img_t = host["image"].to(dev, non_blocking=True) if rank == 0 else torch.empty(shape, dtype=torch.float32, device=dev)
-    noise_t = host["noise"].to(dev, non_blocking=True) if rank == 0 else torch.empty(shape, dtype=torch.float32, device=dev)
+    tdt = torch.float64 if a.image_dtype == "float64" else torch.float32
+    img_t = host["image"].to(dev, non_blocking=True) if rank == 0 else torch.empty(shape, dtype=tdt, device=dev)
+    noise_t = host["noise"].to(dev, non_blocking=True) if rank == 0 else torch.empty(shape, dtype=tdt, device=dev)
     mask_t = host["mask"].to(dev, non_blocking=True) if rank == 0 else torch.empty(shape, dtype=torch.uint8, device=dev)
     if world > 1:
         torch.cuda.synchronize()

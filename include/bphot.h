@@ -35,6 +35,7 @@ extern "C" {
 #define BPHOT_PKFIT 0          /* PythonPhot/pkfit.py:132            pkfit_class.pkfit */
 #define BPHOT_PKFIT_NOISE 1    /* PythonPhot/pkfit_noise.py:131      pkfit_class.pkfit_noise */
 #define BPHOT_PKFIT_NORECENT 2 /* PythonPhot/pkfit_norecent_noise.py:132 pkfit_class.pkfit_norecent_noise */
+#define BPHOT_PKFIT_NORECENTER 3 /* PythonPhot/pkfit_norecenter.py:346  pkfit_class.pkfit_norecenter (its Python-2 semantics) */
 
 #define BPHOT_MAX_APERTURES 16
 

@@ -616,6 +616,7 @@ void bo_inv3(double *c9, int *status) { double c[3][3]; memcpy(c, c9, sizeof(c))
 #define BO_PKFIT 0          /* pkfit.py:132 (no noise/mask image, analytic variance) */
 #define BO_PKFIT_NOISE 1    /* pkfit_noise.py:131 */
 #define BO_PKFIT_NORECENT 2 /* pkfit_norecent_noise.py:132 */
+#define BO_PKFIT_NORECENTER 3 /* pkfit_norecenter.py:346 (Python-2 semantics: it raises under Python 3, :435) */
 
 typedef struct { double errmag, chi, sharp, scale, x, y, chi2; int niter; } bo_fit;
 
@@ -634,6 +635,9 @@ static void pkfit_one(int variant, const void *f, int f_dt, const void *fnoise, 
     double clamp[3] = {1, 1, 1}, dtold[3] = {0, 0, 0};
     int niter = 0;
     double chiold = 1., chi = NAN, sharp = NAN, errmag = NAN, chi2 = NAN;
+    /* pkfit_norecenter: analytic variance like pkfit.py, position frozen; errmag = chi = sharp = 100000 until computed (:352-354) */
+    const int analytic = (variant == BO_PKFIT || variant == BO_PKFIT_NORECENTER);
+    if (variant == BO_PKFIT_NORECENTER) { chi = 100000; sharp = 100000; errmag = 100000; }
     o->chi2 = NAN;
     int cap = (int)((2 * fabs(radius) + 4) * (2 * fabs(radius) + 4)) + 16;
     double *buf = (double *)malloc(sizeof(double) * (size_t)cap * 16);
@@ -668,7 +672,7 @@ static void pkfit_one(int variant, const void *f, int f_dt, const void *fnoise, 
                 double rsq = (dxsq + dysq) / radsq; /* pkfit.py:184 */
                 if (!(rsq < 1.)) continue;
                 size_t gi = (size_t)(iylo + r) * nx + (ixlo + c);
-                if (variant != BO_PKFIT) { /* pkfit_noise.py:206-208 */
+                if (!analytic) { /* pkfit_noise.py:206-208 */
                     if (!(ld(fnoise, n_dt, gi) > 0)) continue;
                     if (fmask[gi] != 0) continue;
                 }
@@ -676,7 +680,7 @@ static void pkfit_one(int variant, const void *f, int f_dt, const void *fnoise, 
                 gdx[ngood] = dxv; gdy[ngood] = dyv; rsqv[ngood] = rsq;
                 rhosq[ngood] = dxsq / (gauss[3] * gauss[3]) + dysq / (gauss[4] * gauss[4]); /* pkfit.py:292 */
                 fsub[ngood] = ld(f, f_dt, gi);
-                if (variant != BO_PKFIT) { sig[ngood] = ld(fnoise, n_dt, gi); sigsq[ngood] = sig[ngood] * sig[ngood]; }
+                if (!analytic) { sig[ngood] = ld(fnoise, n_dt, gi); sigsq[ngood] = sig[ngood] * sig[ngood]; }
                 ngood++;
             }
         }
@@ -684,7 +688,7 @@ static void pkfit_one(int variant, const void *f, int f_dt, const void *fnoise, 
         bo_dao_value(gdx, gdy, ngood, gauss, psf, npsf, t0, dvx, dvy); /* pkfit.py:224 */
         for (int q = 0; q < ngood; q++) { t1[q] = -scale * dvx[q]; t2[q] = -scale * dvy[q]; } /* pkfit.py:243-244 */
         for (int q = 0; q < ngood; q++) df[q] = fsub[q] - scale * t0[q] - sky; /* pkfit.py:262 */
-        if (variant == BO_PKFIT) { /* pkfit.py:277-282 */
+        if (analytic) { /* pkfit.py:277-282 */
             for (int q = 0; q < ngood; q++) {
                 double fpos = fsub[q] - df[q];
                 if (fpos < 0.) fpos = 0;
@@ -699,7 +703,7 @@ static void pkfit_one(int variant, const void *f, int f_dt, const void *fnoise, 
         if (niter >= 2) { /* pkfit.py:296-321 */
             int nbad = 0;
             for (int q = 0; q < ngood; q++) if (fabs(relerr[q] / chiold) >= 10.) nbad++;
-            if (nbad == ngood) {
+            if (nbad == ngood && !(variant == BO_PKFIT_NORECENTER && nbad <= 1)) { /* pkfit_norecenter.py:509: only if len(badpix) > 1 */
                 if (variant == BO_PKFIT_NORECENT) RETURN_NAN(0, 1); /* pkfit_norecent_noise.py:347-356 */
                 RETURN_NAN(1, 1);                                   /* pkfit.py:303-309 */
             }
@@ -715,7 +719,7 @@ static void pkfit_one(int variant, const void *f, int f_dt, const void *fnoise, 
         }
         /* pkfit.py keeps t un-compacted and slices t[:,0:lenwt] (pkfit.py:369-372):
          * the k-th surviving pixel is paired with the k-th ORIGINAL pixel's t. */
-        if (variant == BO_PKFIT) for (int q = 0; q < m; q++) gidx[q] = q;
+        if (analytic) for (int q = 0; q < m; q++) gidx[q] = q;
         for (int q = 0; q < m; q++) wt[q] = 5. / (5. + rsqv[q] / (1. - rsqv[q])); /* pkfit.py:323 */
         int nl = 0; double numer, denom;
         {
@@ -725,20 +729,23 @@ static void pkfit_one(int variant, const void *f, int f_dt, const void *fnoise, 
                 double rh = 0.5 * rhosq[q];
                 double dfdsig = exp(-rh) * (rh - 1.); /* pkfit.py:336 */
                 double s;
-                if (variant == BO_PKFIT) { /* pkfit.py:341-346 */
+                if (analytic) { /* pkfit.py:341-346 */
                     double fpos = fsub[q];
                     if (fsub[q] - sky < 0.) fpos = sky;
                     s = fpos / phpadu + ronois + (0.0075 * fpos) * (0.0075 * fpos) +
                         (pkerr * (fpos - sky)) * (pkerr * (fpos - sky));
                 } else s = sig[q] * sig[q]; /* pkfit_noise.py:361 */
                 /* pkfit.py:350 pairs dfdsig with df[0:len(lilrho)] (first nl entries) */
-                double dfv = (variant == BO_PKFIT) ? df[nl] : df[q];
+                double dfv = analytic ? df[nl] : df[q];
                 a1[nl] = dfdsig * dfv / s;
                 a2[nl] = dfdsig * dfdsig / s;
                 a3[nl] = dfv * dfv / s;
                 nl++;
             }
             if (nl == 0) RETURN_NAN(0, 0); /* pkfit.py:325-333 */
+            /* pkfit_norecenter.py:537,570-573 multiplies df[lilrho] (nl long) with wt (m long): numpy raises unless every pixel is
+             * within 6 sigma; reported as a failed fit here */
+            if (variant == BO_PKFIT_NORECENTER && nl != m) RETURN_NAN(0, 0);
             numer = pw_sum(a1, nl); denom = pw_sum(a2, nl);
             if (variant == BO_PKFIT_NORECENT) chi2 = pw_sum(a3, nl) / (nl - 1); /* pkfit_norecent_noise.py:409-410 */
         }
@@ -771,7 +778,7 @@ static void pkfit_one(int variant, const void *f, int f_dt, const void *fnoise, 
         double csum = 0;
         for (int a_ = 0; a_ < 3; a_++) for (int b_ = 0; b_ < 3; b_++) csum += c[a_][b_];
         int skip_inv = 0;
-        if (variant == BO_PKFIT_NOISE) { /* pkfit_noise.py:399-410: NaN => inversion skipped; inf => inv raises => NaN return */
+        if (variant == BO_PKFIT_NOISE || variant == BO_PKFIT_NORECENTER) { /* pkfit_noise.py:399-410, pkfit_norecenter.py:586-594: NaN => inversion skipped; inf => inv raises => NaN return */
             if (isnan(csum)) skip_inv = 1;
             else if (isinf(csum)) RETURN_NAN(0, 0);
         } else if (isnan(csum) || isinf(csum)) RETURN_NAN(0, 0); /* pkfit.py:383-406 */
@@ -792,7 +799,7 @@ static void pkfit_one(int variant, const void *f, int f_dt, const void *fnoise, 
         int redo = 0;
         sharp = 2. * gauss[3] * gauss[4] * numer / (gauss[0] * scale * denom); /* pkfit.py:440 */
         errmag = chiold * sqrt(c[0][0]);
-        if (variant == BO_PKFIT) { /* pkfit.py:442 (python max: b if b > a else a) */
+        if (variant == BO_PKFIT) { /* pkfit.py:442 (python max: b if b > a else a); pkfit_norecenter.py:631 has the `or` form */
             double a_ = 0.05 * errmag, b_ = 0.001 * scale;
             double mx = (b_ > a_) ? b_ : a_;
             if (adt[0] > mx) redo = 1;

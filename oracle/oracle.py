@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "libbphot_oracle.so")
 _lib = None
 
-PKFIT, PKFIT_NOISE, PKFIT_NORECENT = 0, 1, 2
+PKFIT, PKFIT_NOISE, PKFIT_NORECENT, PKFIT_NORECENTER = 0, 1, 2, 3
 
 
 def build(force=False):
@@ -162,7 +162,7 @@ def pkfit(variant, image, gauss, psf, ronois, phpadu, noise, mask, scale, x, y, 
 
     Returns dict(errmag, chi, sharp, niter, scale, x, y, chi2), arrays of len(x)."""
     img, dt = _img(image)
-    if variant == PKFIT:
+    if variant in (PKFIT, PKFIT_NORECENTER):
         nz, ndt, mk = img, dt, np.zeros(1, np.uint8)
     else:
         nz, ndt = _img(noise)

@@ -11,7 +11,7 @@ plus the unified ``pkfit_class`` carrying all three fit methods.  Every numerica
 hand-written CUDA in ``csrc/`` behind the C ABI of ``include/bphot.h``; there is no CPU fallback.
 """
 from . import _lib  # noqa: F401
-from . import aper, pkfit, pkfit_noise, pkfit_norecent_noise  # noqa: F401
+from . import aper, pkfit, pkfit_noise, pkfit_norecent_noise, pkfit_norecenter  # noqa: F401
 from . import mmm, pixwt, dao_value, daoerf, rinter  # noqa: F401
 from . import getpsf, rdpsf, find, cntrd, shard  # noqa: F401
 from ._pkfit_core import PkfitEngine as _PkfitEngine
@@ -25,7 +25,8 @@ class pkfit_class(_PkfitEngine):
     pkfit = pkfit.pkfit_class.pkfit
     pkfit_noise = pkfit_noise.pkfit_class.pkfit_noise
     pkfit_norecent_noise = pkfit_norecent_noise.pkfit_class.pkfit_norecent_noise
+    pkfit_norecenter = pkfit_norecenter.pkfit_class.pkfit_norecenter
 
 
-__all__ = ["aper", "pkfit", "pkfit_noise", "pkfit_norecent_noise", "mmm", "pixwt", "dao_value", "daoerf",
+__all__ = ["aper", "pkfit", "pkfit_noise", "pkfit_norecent_noise", "pkfit_norecenter", "mmm", "pixwt", "dao_value", "daoerf",
            "rinter", "getpsf", "rdpsf", "find", "cntrd", "shard", "pkfit_class"]

@@ -16,7 +16,7 @@ SO_PATH = os.path.join(CSRC, "libbphot.so")
 F32, F64 = 0, 1
 ERR_CAPACITY = -3
 APER_NARROW_CTAS = 256  # bphot.h BPHOT_APER_NARROW_CTAS (testing aid)
-PKFIT, PKFIT_NOISE, PKFIT_NORECENT = 0, 1, 2
+PKFIT, PKFIT_NOISE, PKFIT_NORECENT, PKFIT_NORECENTER = 0, 1, 2, 3
 MAX_APERTURES = 16
 
 _lib = None

@@ -74,7 +74,7 @@ class PkfitEngine(object):
         torch = _lib.torch_cuda()
         n = x_t.numel()
         dev = self.device
-        if variant != _lib.PKFIT and (self._noise_t is None or self._mask_t is None):
+        if variant not in (_lib.PKFIT, _lib.PKFIT_NORECENTER) and (self._noise_t is None or self._mask_t is None):
             raise ValueError("this fit needs the noise and mask images given to pkfit_class(...)")
         out = _lib.alloc_out([(k, torch.float64, ()) for k in ("errmag", "chi", "sharp", "scale", "x", "y", "chi2")] +
                              [("niter", torch.int32, ())], n, dev, out)

@@ -661,11 +661,12 @@ int bphot_pkfit_device(int variant, const void* d_image, int image_dtype,
                        double* d_scale_out, double* d_x_out, double* d_y_out, double* d_chi2,
                        void* stream) {
     using namespace bphot;
-    if (variant < 0 || variant > 2) return fail(BPHOT_ERR_ARG, "bphot_pkfit: variant %d", variant);
+    if (variant < 0 || variant > 3) return fail(BPHOT_ERR_ARG, "bphot_pkfit: variant %d", variant);
+    const bool analytic = (variant == BPHOT_PKFIT || variant == BPHOT_PKFIT_NORECENTER);
     if (!d_image || !gauss || !d_psf || npsf < 4 || nrow <= 0 || ncol <= 0 || nstars < 0) return fail(BPHOT_ERR_ARG, "bphot_pkfit: null image/gauss/psf or bad shape");
-    if (variant != BPHOT_PKFIT && (!d_noise || !d_mask)) return fail(BPHOT_ERR_ARG, "bphot_pkfit: noise and mask images are required for variant %d", variant);
+    if (!analytic && (!d_noise || !d_mask)) return fail(BPHOT_ERR_ARG, "bphot_pkfit: noise and mask images are required for variant %d", variant);
     if (image_dtype != BPHOT_F32 && image_dtype != BPHOT_F64) return fail(BPHOT_ERR_ARG, "bphot_pkfit: image dtype %d", image_dtype);
-    if (variant != BPHOT_PKFIT && noise_dtype != BPHOT_F32 && noise_dtype != BPHOT_F64) return fail(BPHOT_ERR_ARG, "bphot_pkfit: noise dtype %d", noise_dtype);
+    if (!analytic && noise_dtype != BPHOT_F32 && noise_dtype != BPHOT_F64) return fail(BPHOT_ERR_ARG, "bphot_pkfit: noise dtype %d", noise_dtype);
     if (!(radius > 0.) || !(radius < 64.)) return fail(BPHOT_ERR_ARG, "bphot_pkfit: radius %g outside (0, 64)", radius);
     if (nstars == 0) return BPHOT_OK;
     if (!d_scale || !d_x || !d_y || !d_sky || !d_errmag || !d_chi || !d_sharp || !d_niter || !d_scale_out || !d_x_out || !d_y_out || !d_chi2)
@@ -694,7 +695,7 @@ int bphot_pkfit_device(int variant, const void* d_image, int image_dtype,
     const long long nblocks = ((long long)nstars + PK_WARPS - 1) / PK_WARPS;
     int grid = 0;
     cudaStream_t st = (cudaStream_t)stream;
-    const int nd = (variant == BPHOT_PKFIT) ? image_dtype : noise_dtype;
+    const int nd = analytic ? image_dtype : noise_dtype;
     StarOrder ord;
     rc = make_star_order(d_x, d_y, nstars, nrow, ncol, st, &ord);
     if (rc) return rc;
@@ -723,6 +724,9 @@ int bphot_pkfit_device(int variant, const void* d_image, int image_dtype,
     if (variant == BPHOT_PKFIT) {  // no noise image: TN is unused
         if (image_dtype == BPHOT_F32) BP_LAUNCH(0, float, float);
         else BP_LAUNCH(0, double, double);
+    } else if (variant == BPHOT_PKFIT_NORECENTER) {
+        if (image_dtype == BPHOT_F32) BP_LAUNCH(3, float, float);
+        else BP_LAUNCH(3, double, double);
     } else if (variant == BPHOT_PKFIT_NOISE) BP_LAUNCH_T(1);
     else BP_LAUNCH_T(2);
 #undef BP_LAUNCH_T
@@ -1036,14 +1040,15 @@ int bphot_pkfit_host(int variant, const void* image, int image_dtype,
                      int device) {
     if (bphot_device_count() < 1) return fail(BPHOT_ERR_NODEVICE, "no CUDA device (libbphot has no CPU fallback)");
     if (!image || !gauss || !psf || nstars < 0 || nrow <= 0 || ncol <= 0 || npsf < 4) return fail(BPHOT_ERR_ARG, "bphot_pkfit_host: bad argument");
-    if (variant != BPHOT_PKFIT && (!noise || !mask)) return fail(BPHOT_ERR_ARG, "bphot_pkfit_host: noise and mask images are required for variant %d", variant);
+    const bool analytic = (variant == BPHOT_PKFIT || variant == BPHOT_PKFIT_NORECENTER);
+    if (!analytic && (!noise || !mask)) return fail(BPHOT_ERR_ARG, "bphot_pkfit_host: noise and mask images are required for variant %d", variant);
     if (image_dtype != BPHOT_F32 && image_dtype != BPHOT_F64) return fail(BPHOT_ERR_ARG, "bphot_pkfit_host: image dtype %d", image_dtype);
     if (nstars == 0) return BPHOT_OK;
     CU_TRY(cudaSetDevice(device));
     const size_t nb = (size_t)nstars * sizeof(double), npx = (size_t)nrow * ncol;
     DevBuf dimg, dnz, dmk, dpsf, ds, dx, dy, dsk, o_err, o_chi, o_sh, o_it, o_sc, o_x, o_y, o_c2;
     UP(dimg, image, npx * esize(image_dtype));
-    if (variant != BPHOT_PKFIT) {
+    if (!analytic) {
         if (noise_dtype != BPHOT_F32 && noise_dtype != BPHOT_F64) return fail(BPHOT_ERR_ARG, "bphot_pkfit_host: noise dtype %d", noise_dtype);
         UP(dnz, noise, npx * esize(noise_dtype));
         UP(dmk, mask, npx);

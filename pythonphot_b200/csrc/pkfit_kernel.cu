@@ -4,6 +4,7 @@
 //   variant 0  PythonPhot/pkfit.py:132-458                (analytic noise model, optional recentring)
 //   variant 1  PythonPhot/pkfit_noise.py:131-462          (noise + mask images, recentring)
 //   variant 2  PythonPhot/pkfit_norecent_noise.py:132-531 (noise + mask images, forced position)
+//   variant 3  PythonPhot/pkfit_norecenter.py:346-657     (analytic noise model, forced position; Python-2 semantics)
 // and their callee dao_value.dao_value (dao_value.py:9-121 -> daoerf.py, rinter.py).
 //
 // Per star, one warp runs the damped Gauss-Newton loop.  Pixels of the fitting box are
@@ -112,12 +113,13 @@ struct FitState {
     double chiold, chi, sharp, errmag, chi2, scale, x, y;
     int niter;
 };
-BP_D FitState fit_init(double scale, double x, double y) {
+BP_D FitState fit_init(double scale, double x, double y, bool norecenter = false) {
     FitState S;
     S.clamp0 = S.clamp1 = S.clamp2 = 1.;
     S.dtold0 = S.dtold1 = S.dtold2 = 0.;
     S.chiold = 1.;
     S.chi = S.sharp = S.errmag = S.chi2 = nan64();
+    if (norecenter) S.chi = S.sharp = S.errmag = 100000.;  // pkfit_norecenter.py:352-354
     S.scale = scale; S.x = x; S.y = y;
     S.niter = 0;
     return S;
@@ -150,7 +152,7 @@ BP_D bool fit_tail(const PkfitParams& P, const double* gauss, FitState& S, doubl
     for (int a = 0; a < 3; a++)
         for (int b = 0; b < 3; b++) csum = csum + c[a][b];
     bool skip_inv = false;
-    if (V == 1) {  // pkfit_noise.py:399-410: NaN -> inversion skipped; inf -> inv raises -> NaN return
+    if (V == 1 || V == 3) {  // pkfit_noise.py:399-410, pkfit_norecenter.py:586-594: NaN -> inversion skipped; inf -> inv raises -> NaN return
         if (isnan(csum)) skip_inv = true;
         else if (isinf(csum)) return false;
     } else if (isnan(csum) || isinf(csum)) return false;  // pkfit.py:383-406
@@ -389,8 +391,9 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
 }
 
 // ------------------------------------------------------- variants 0 and 1
-// pkfit.py:132-458 (V = 0) and pkfit_noise.py:131-462 (V = 1): x, y move, so the pixel list and the model
-// are rebuilt every iteration.  W = PK_NARR_FIT arrays of `cap` doubles, GIDX = cap ints, AX = 4 x acap doubles.
+// pkfit.py:132-458 (V = 0), pkfit_noise.py:131-462 (V = 1) and pkfit_norecenter.py:346-657 (V = 3: pkfit.py's analytic
+// noise model with the position frozen, pkfit_noise's convergence test, its own early returns): the pixel list and the
+// model are rebuilt every iteration.  W = PK_NARR_FIT arrays of `cap` doubles, GIDX = cap ints, AX = 4 x acap doubles.
 template <int V, typename TI, typename TN>
 BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__ psf, double* W, int* GIDX, double* AX,
                                 double scale, double x, double y, const double sky, const int lane) {
@@ -416,8 +419,9 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
     const double pkerr = 0.027 / ((gauss[3] * gauss[4]) * (gauss[3] * gauss[4]));  // pkfit.py:146
     const double half = (double)(npsf - 1) / 2.;
     const unsigned lt = (1u << lane) - 1u;
+    constexpr bool ANALYTIC = (V == 0 || V == 3);  // variance from the model (pkfit.py:277-282), no noise / mask image
 
-    FitState S = fit_init(scale, x, y);
+    FitState S = fit_init(scale, x, y, V == 3);
     bool loop = true;
     while (loop) {
         S.niter++;
@@ -445,7 +449,7 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
                 ok = rsq < 1.;
                 if (ok) {
                     const size_t row = (size_t)(b.iylo + r), col = (size_t)(b.ixlo + c);
-                    if (V != 0) {
+                    if (!ANALYTIC) {
                         nz = (double)noise[row * P.npitch + col];
                         ok = (nz > 0) && (mask[row * P.mpitch + col] == 0);
                     }
@@ -461,7 +465,7 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
                 if (q < cap) {
                     DX[q] = dxv; DY[q] = dyv; RSQ[q] = rsq; RHO[q] = rho; FSUB[q] = fv;
                     GIDX[q] = r * 65536 + c;
-                    if (V != 0) { SIG[q] = nz; SIGSQ[q] = nz * nz; }
+                    if (!ANALYTIC) { SIG[q] = nz; SIGSQ[q] = nz * nz; }
                     xmin = fmin(xmin, dxv); xmax = fmax(xmax, dxv);
                     ymin = fmin(ymin, dyv); ymax = fmax(ymax, dyv);
                 }
@@ -488,7 +492,7 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
             T2[q] = -scl * dvy;
             const double fsub = FSUB[q];
             const double df = fsub - scl * mval - sky;
-            if (V == 0) {  // pkfit.py:277-282 (ronois enters un-squared, as in the reference)
+            if (ANALYTIC) {  // pkfit.py:277-282 (ronois enters un-squared, as in the reference)
                 double fpos = fsub - df;
                 if (fpos < 0.) fpos = 0.;
                 const double s2 = fpos / P.phpadu + P.ronois + (0.0075 * fpos) * (0.0075 * fpos) +
@@ -509,7 +513,8 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
             for (int q = lane; q < ngood; q += 32)
                 if (fabs(REL[q] / chiold) >= 10.) nbad++;
             nbad = warp_sum_int(nbad);
-            if (nbad == ngood) return fit_nan(S, true, true);  // pkfit.py:303-309
+            // pkfit.py:303-309; pkfit_norecenter.py:509 takes this return only when more than one pixel is rejected
+            if (nbad == ngood && !(V == 3 && nbad <= 1)) return fit_nan(S, true, true);
             if (nbad > 0) {
                 compacted = true;
                 m = 0;
@@ -536,7 +541,7 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
         }
         // pkfit.py keeps t un-compacted and slices t[:, 0:lenwt] (pkfit.py:369-372): the k-th surviving
         // pixel is paired with the k-th ORIGINAL pixel's t.  pkfit_noise indexes t by goodind.
-        const bool direct = !compacted || V == 0;
+        const bool direct = !compacted || ANALYTIC;
 
         // ---- weights and sums (pkfit.py:323-372)
         double numer = 0., denom = 0., schi = 0., sumwt = 0.;
@@ -552,7 +557,7 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
                 const double rh = 0.5 * rho;
                 const double dfdsig = exp(-rh) * (rh - 1.);  // pkfit.py:336
                 double s;
-                if (V == 0) {  // pkfit.py:341-346
+                if (ANALYTIC) {  // pkfit.py:341-346
                     double fpos = FSUB[q];
                     if (fpos - sky < 0.) fpos = sky;
                     s = fpos / P.phpadu + P.ronois + (0.0075 * fpos) * (0.0075 * fpos) +
@@ -562,7 +567,7 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
                     s = sg * sg;  // pkfit_noise.py:361
                 }
                 // pkfit.py:350 pairs dfdsig with df[0:len(lilrho)] (the FIRST nl residuals)
-                const double dfv = (V == 0) ? DF[nl + __popc(mk & lt)] : DF[q];
+                const double dfv = ANALYTIC ? DF[nl + __popc(mk & lt)] : DF[q];
                 numer = numer + dfdsig * dfv / s;
                 denom = denom + dfdsig * dfdsig / s;
             }
@@ -586,6 +591,9 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
             }
         }
         if (nl == 0) return fit_nan(S, false, false);  // pkfit.py:325-333
+        // pkfit_norecenter.py:537,570-573 multiplies df[lilrho] (nl long) with wt (m long): numpy raises unless every pixel
+        // lies within 6 sigma; reported as a failed fit
+        if (V == 3 && nl != m) return fit_nan(S, false, false);
         numer = pk_sum(numer); denom = pk_sum(denom);
         schi = pk_sum(schi);
         S.chi = schi;

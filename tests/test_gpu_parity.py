@@ -381,3 +381,26 @@ def test_c_abi_errors_are_reported(pp):
     assert rc == -1 and b"null" in lib.bphot_last_error()
     with pytest.raises(_lib.BphotError):  # annulus too large for one CTA's shared memory
         pp.aper.aper(np.zeros((64, 64), np.float32), [30.0], [30.0], skyrad=[100, 400], verbose=False)
+
+
+# ------------------------------------------------------------------ fourth fit variant
+@pytest.mark.parametrize("radius", [3.0, 5.0])
+def test_pkfit_norecenter_golden(pp, radius):
+    """pkfit_norecenter.pkfit_class.pkfit_norecenter (pkfit_norecenter.py:346-657, Python-2 semantics) on the GPU against the
+    reference's own outputs, scalar and batched calls, and through the unified pkfit_class."""
+    from oracle import compare
+    g = load_golden("golden_pkfit.npz")
+    w = load_golden("golden_pkfit_norecenter.npz")["norecenter__r%d" % radius]
+    cols = ("errmag", "chi", "sharp", "niter", "scale")
+    want = {c: w[:, j] for j, c in enumerate(cols)}
+    pk = pp.pkfit_norecenter.pkfit_class(g["image"], g["gauss"], g["psf"], float(g["ronois"]), float(g["phpadu"]))
+    got = dict(zip(cols, pk.pkfit_norecenter(g["scale0"], g["x"], g["y"], g["sky"], radius)))
+    rep = compare.compare_pkfit(got, want, cols, g["x"], g["y"], g["image"].shape, radius)
+    assert rep["mismatches"] == 0 and rep["rank_deficient"] <= 3, rep
+    one = pk.pkfit_norecenter(float(g["scale0"][5]), float(g["x"][5]), float(g["y"][5]), float(g["sky"][5]), radius)
+    assert len(one) == 5 and one[3] == int(w[5, 3]) and abs(one[4] - w[5, 4]) <= 1e-9 * abs(w[5, 4])
+    pk2 = pp.pkfit_class(g["image"], g["gauss"], g["psf"], float(g["ronois"]), float(g["phpadu"]))
+    again = pk2.pkfit_norecenter(g["scale0"], g["x"], g["y"], g["sky"], radius)
+    assert np.array_equal(again[3], got["niter"])
+    with pytest.raises(NotImplementedError):
+        pk.pkfit_fast_norecenter(1, 2, 3, 4, 5)

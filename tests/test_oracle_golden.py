@@ -145,3 +145,22 @@ def test_fragile_apertures_are_checked_against_the_admissible_outcomes(mode):
         broken = {nm: np.array(a, copy=True) for nm, a in other.items()}
         broken["badflag"][i, k] = 1
         assert compare.compare_aper(broken, want, fragile, alt=alt)["mismatches"] == 1
+
+
+@pytest.mark.parametrize("radius", [3.0, 5.0])
+def test_pkfit_norecenter_golden(radius):
+    """The fourth fit variant, pkfit_norecenter.pkfit_norecenter (pkfit_norecenter.py:346-657), against the reference run
+    under its Python-2 semantics (tests/golden/gen_golden_norecenter.py)."""
+    from oracle import compare
+    g = load_golden("golden_pkfit.npz")
+    w = load_golden("golden_pkfit_norecenter.npz")["norecenter__r%d" % radius]
+    cols = ("errmag", "chi", "sharp", "niter", "scale")
+    want = {c: w[:, j] for j, c in enumerate(cols)}
+    o = oracle.pkfit(oracle.PKFIT_NORECENTER, g["image"], g["gauss"], g["psf"], float(g["ronois"]), float(g["phpadu"]), None, None,
+                     g["scale0"], g["x"], g["y"], g["sky"], radius)
+    rep = compare.compare_pkfit(o, want, cols, g["x"], g["y"], g["image"].shape, radius)
+    assert rep["mismatches"] == 0 and rep["rank_deficient"] <= 3, rep
+    # it is NOT pkfit(recenter=False): the two differ where pixels are rejected or an early return is taken
+    p = oracle.pkfit(oracle.PKFIT, g["image"], g["gauss"], g["psf"], float(g["ronois"]), float(g["phpadu"]), None, None,
+                     g["scale0"], g["x"], g["y"], g["sky"], radius, recenter=False)
+    assert (p["niter"] != o["niter"]).any()
