@@ -110,33 +110,17 @@ BP_D void shfl_mirror(T (&r)[K], int m, bool keepmin) {
     }
 }
 // partner thread in another warp: through shared memory, row stride K+1 keeps both the writes and
-// the partner reads conflict-free.  `doit` is warp-uniform: false for warps that hold only padding, or whose
+// the partner reads conflict-free.  (Measured dead end, round 2: letting only the two partner warps meet at a named barrier
+// `bar.sync id, 64` instead of the CTA barrier made stage 1 slower, 36.5 -> 46.8 ms per 1 M stars, and hung the unit kernel.)  `doit` is warp-uniform: false for warps that hold only padding, or whose
 // partner warp does (then the exchange cannot change anything); every thread still reaches the barriers.
-#ifndef AP_PAIR_BARRIER
-#define AP_PAIR_BARRIER 1  // cross-warp stages synchronise the two partner warps only (named barrier), not the CTA
-#endif
-// The exchange involves exactly two warps, w and w ^ (m >> 5): they meet at a named barrier of their own (ids 1..2, 64
-// threads) instead of stopping the whole CTA twice per stage -- a warp whose partner holds only padding does not stop at
-// all.  ncu (r02a): 18.5 % of stage 1's warp samples sat on CTA barriers, most of them here.
-BP_D void pair_sync(int warp, int partner, bool doit) {
-#if AP_PAIR_BARRIER
-    if (doit) {
-        const int id = 1 + (warp < partner ? warp : partner);
-        asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory");
-    }
-#else
-    __syncthreads();
-#endif
-}
 template <typename T, int K>
 BP_D void smem_stage(T (&r)[K], int m, bool mirror, bool keepmin, T* xbuf, int tid, bool doit) {
     T* mine = xbuf + tid * (K + 1);
-    const int warp = tid >> 5, partner = warp ^ (m >> 5);
     if (doit) {
 #pragma unroll
         for (int q = 0; q < K; q++) mine[q] = r[q];
     }
-    pair_sync(warp, partner, doit);
+    __syncthreads();
     if (doit) {
         const T* theirs = xbuf + (tid ^ m) * (K + 1);
 #pragma unroll
@@ -145,7 +129,7 @@ BP_D void smem_stage(T (&r)[K], int m, bool mirror, bool keepmin, T* xbuf, int t
             AP_KSEL(r[q], o, keepmin);
         }
     }
-    pair_sync(warp, partner, doit);
+    __syncthreads();
 }
 // `nwarps` = warps that hold real keys.  The network is standard (every comparator leaves the minimum at the lower
 // index), so threads above them, which start with +inf in every register, can never receive anything else: their
@@ -255,7 +239,12 @@ BP_D MmmResult mmm_warp(const View at, int nsky, double readnoise, int minsky, i
         if (need1) *r1 = first(v1, st1);  // need* are warp-uniform
         if (need2) *r2 = first(v2, st2);
     };
-    return mmm_sorted(at, delta_sums, plain_sum, first2, nsky, readnoise, minsky, mxiter);
+    auto sums3 = [&](int lo0, int hi0, bool need0, int lo1, int hi1, bool need1, int lo2, int hi2, double mid, double* o5) {
+        if (need0) delta_sums(lo0, hi0, mid, &o5[0], &o5[1]);  // need* are warp-uniform
+        if (need1) delta_sums(lo1, hi1, mid, &o5[2], &o5[3]);
+        o5[4] = plain_sum(lo2, hi2);
+    };
+    return mmm_sorted(at, delta_sums, plain_sum, first2, sums3, nsky, readnoise, minsky, mxiter);
 }
 
 // scipy.stats.sigmaclip(skybuf, low, high) followed by np.mean / np.std of the survivors (aper.py:275-282), by one
@@ -863,6 +852,9 @@ __global__ void __launch_bounds__(AP_THREADS) aper_mmm_kernel(const AperParams P
                 [&](int lo, int hi) { return V.plain_sum(lo, hi); },
                 [&](double v1, bool st1, bool need1, double v2, bool st2, bool need2, int* r1, int* r2) {
                     V.first2(v1, st1, need1, v2, st2, need2, r1, r2);
+                },
+                [&](int lo0, int hi0, bool need0, int lo1, int hi1, bool need1, int lo2, int hi2, double, double* o5) {
+                    V.sums3(lo0, hi0, need0, lo1, hi1, need1, lo2, hi2, o5);
                 },
                 status, P.readnoise, P.minsky, P.mxiter);
             skymod = R.skymod; skysig = R.sigma; iters = R.iters;

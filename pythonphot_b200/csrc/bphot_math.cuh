@@ -392,6 +392,9 @@ BP_HD int mmm_max_post(int nsky, int maximm, bool tst_max, int e) {  // e = firs
 //   plain_sum(lo, hi)             sum(at(i)) over [lo, hi)
 //   first2(v1, strict1, need1, v2, strict2, need2, &r1, &r2)   two rank queries at once: r = first index with
 //                                 at(i) > v (strict) / at(i) >= v, nsky if none; a query with need = false is skipped
+//   sums3(lo0, hi0, need0, lo1, hi1, need1, lo2, hi2, mid, out5)   the three range sums of one clipping pass at once:
+//                                 out5 = delta_sums over [lo0, hi0) and over [lo1, hi1) (skipped when need = false),
+//                                 then plain_sum over [lo2, hi2)
 // The functors let a whole warp share the reductions on the device (every lane must receive the same
 // bits) and a plain loop stand in on the host (tests/hostcheck).  Failure modes keep the reference's
 // in-band codes (sigma = -1).
@@ -495,6 +498,44 @@ struct IndexedView {
         }
         *s1 = a; *s2 = q;
     }
+    // The three range sums of one clipping pass (mmm_sorted's sums3): six prefix evaluations whose loads are all
+    // issued before the first one is consumed.
+    BP_HDM void sums3(int lo0, int hi0, bool need0, int lo1, int hi1, bool need1, int lo2, int hi2, double* o5) const {
+        const int idx[6] = {need0 ? hi0 : 0, need0 ? lo0 : 0, need1 ? hi1 : 0, need1 ? lo1 : 0, hi2 > lo2 ? hi2 : 0, hi2 > lo2 ? lo2 : 0};
+        double pa[6], pq[6];
+#if defined(__CUDA_ARCH__)
+        if constexpr (sizeof(T) == 4) {
+            float4 raw[6][4];
+#pragma unroll
+            for (int e = 0; e < 6; e++) {
+                const int g = idx[e] >> 4, c = idx[e] & 15;
+                bp_ld2(PT + 2 * g, &pa[e], &pq[e]);
+                const float4* p4 = reinterpret_cast<const float4*>(k + 16 * (c ? g : 0));  // c == 0: nothing is added, any group will do
+#pragma unroll
+                for (int u = 0; u < 4; u++) raw[e][u] = __ldg(p4 + u);
+            }
+#pragma unroll
+            for (int e = 0; e < 6; e++) {
+                const int c = idx[e] & 15;
+                double a = pa[e], q = pq[e];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const float f4[4] = {raw[e][u].x, raw[e][u].y, raw[e][u].z, raw[e][u].w};
+#pragma unroll
+                    for (int w = 0; w < 4; w++)
+                        if (4 * u + w < c) { const double d = (double)f4[w] - skymid; a = a + d; q = q + d * d; }
+                }
+                pa[e] = a; pq[e] = q;
+            }
+        } else
+#endif
+        {
+            for (int e = 0; e < 6; e++) prefix(idx[e], &pa[e], &pq[e]);
+        }
+        o5[0] = pa[0] - pa[1]; o5[1] = pq[0] - pq[1];
+        o5[2] = pa[2] - pa[3]; o5[3] = pq[2] - pq[3];
+        o5[4] = hi2 > lo2 ? (pa[4] - pa[5]) + (double)(hi2 - lo2) * skymid : 0.0;
+    }
     BP_HDM void delta_sums(int lo, int hi, double* s1, double* s2) const {
         double a1, q1, a0, q0;
         prefix(hi, &a1, &q1);
@@ -536,14 +577,31 @@ struct IndexedView {
             }
         }
         const bool go1 = need1 && c1a > 0, go2 = need2 && c1b > 0;  // c1 == 0: key[0] passes, the answer is 0
-        const int g1 = 16 * (c1a - 1), g2 = 16 * (c1b - 1);         // L2 group whose entry 0 is the last failing L1 key
-        int j1 = 0, j2 = 0;
-        if (go1) j1 = g1 + count_fail(L2 + g1, 1, n2 - g1, v1, st1);
-        if (go2) j2 = g2 + count_fail(L2 + g2, 1, n2 - g2, v2, st2);
-        int f1 = 0, f2 = 0;                                         // k[16 j] is the last failing L2 key
-        if (go1) f1 = 16 * j1 + 1 + count_fail(k + 16 * j1, 1, n - 16 * j1, v1, st1);
-        if (go2) f2 = 16 * j2 + 1 + count_fail(k + 16 * j2, 1, n - 16 * j2, v2, st2);
-        *r1 = f1; *r2 = f2;
+        // L2 group whose entry 0 is the last failing L1 key; a query that is not needed walks group 0 and is discarded, so
+        // that the loads of both queries are unconditional and in flight together
+        const int g1 = go1 ? 16 * (c1a - 1) : 0, g2 = go2 ? 16 * (c1b - 1) : 0;
+        double xa[16], xb[16];
+        load16(L2 + g1, xa);
+        load16(L2 + g2, xb);
+        int j1 = g1, j2 = g2;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int t = 1; t < 16; t++) {
+            j1 += (t < n2 - g1 && !(st1 ? xa[t] > v1 : xa[t] >= v1)) ? 1 : 0;
+            j2 += (t < n2 - g2 && !(st2 ? xb[t] > v2 : xb[t] >= v2)) ? 1 : 0;
+        }
+        load16(k + 16 * j1, xa);                                    // k[16 j] is the last failing L2 key
+        load16(k + 16 * j2, xb);
+        int f1 = 16 * j1 + 1, f2 = 16 * j2 + 1;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int t = 1; t < 16; t++) {
+            f1 += (t < n - 16 * j1 && !(st1 ? xa[t] > v1 : xa[t] >= v1)) ? 1 : 0;
+            f2 += (t < n - 16 * j2 && !(st2 ? xb[t] > v2 : xb[t] >= v2)) ? 1 : 0;
+        }
+        *r1 = go1 ? f1 : 0; *r2 = go2 ? f2 : 0;
     }
 };
 
@@ -553,8 +611,8 @@ struct MmmResult {
 };
 BP_HD double mmm_nan() { return (double)NAN; }
 
-template <typename Get, typename DSums, typename PSum, typename First2>
-BP_HD MmmResult mmm_sorted(const Get& at, const DSums& delta_sums, const PSum& plain_sum, const First2& first2,
+template <typename Get, typename DSums, typename PSum, typename First2, typename Sums3>
+BP_HD MmmResult mmm_sorted(const Get& at, const DSums& delta_sums, const PSum& plain_sum, const First2& first2, const Sums3& sums3,
                            int nsky, double readnoise, int minsky, int mxiter) {
     MmmResult R;
     R.iters = 0;
@@ -612,25 +670,41 @@ BP_HD MmmResult mmm_sorted(const Get& at, const DSums& delta_sums, const PSum& p
         const int newmin = E0.done ? minimm : mmm_min_post(nsky, minimm, E0.tst, e0 - 1);
         const int newmax = E1.done ? maximm : mmm_max_post(nsky, maximm, E1.tst, e1 - 1);
         const bool moved = !E0.done, grew = E0.tst, moved1 = !E1.done, grew1 = E1.tst;
-#if defined(__CUDA_ARCH__)
-#pragma unroll 1
-#endif
-        for (int e = 0; e < 2; e++) {
-            const bool mv = e ? moved1 : moved, gr = e ? grew1 : grew;
-            if (!mv) continue;
-            // lower edge: grown range (newmin, minimm], shrunk range (minimm, newmin]
-            // upper edge: grown range (maximm, newmax], shrunk range (newmax, maximm]
-            const int from = e ? (gr ? maximm : newmax) : (gr ? newmin : minimm);
-            const int to = e ? (gr ? newmax : maximm) : (gr ? minimm : newmin);
-            double s1, s2;
-            delta_sums(from + 1, to + 1, skymid, &s1, &s2);
-            if (gr) { sum = sum + s1; sumsq = sumsq + s2; }
-            else { sum = sum - s1; sumsq = sumsq - s2; }
+        // lower edge: grown range (newmin, minimm], shrunk range (minimm, newmin]
+        // upper edge: grown range (maximm, newmax], shrunk range (newmax, maximm]
+        const int from0 = grew ? newmin : minimm, to0 = grew ? minimm : newmin;
+        const int from1 = grew1 ? maximm : newmax, to1 = grew1 ? newmax : maximm;
+        // robust median: mean of the central 20 % of the NEW window (mmm.py:271-289; np.round = half-to-even).  Its index
+        // range depends on the new edges only, so its sum is asked for together with the edge sums (one thread per star
+        // then waits for memory once, not three times).
+        const int ns = newmax - newmin;  // mmm.py:253-257
+        const double center = (newmin + 1 + newmax) / 2.;
+        const double side = rint(0.2 * (newmax - newmin)) / 2. + 0.25;
+        double j = rint(center - side), k = rint(center + side);
+        if (readnoise != 0.0 && ns >= minsky) {  // mmm.py:280-287
+            const double L = rint(center - 0.25), M = rint(center + 0.25), Rn = 0.25 * readnoise;
+            while (j > 0 && k < ns - 1 && ((at((int)L) - at((int)j)) < Rn || (at((int)k) - at((int)M)) < Rn)) {
+                j -= 1; k += 1;
+            }
+        }
+        int ji = (int)j, ki = (int)k + 1;
+        if (ji < 0) ji = 0;
+        if (ki > nsky) ki = nsky;
+        if (ns < minsky) { ji = 0; ki = 0; }  // the pass returns before the median is used
+        double o5[5] = {0., 0., 0., 0., 0.};
+        sums3(from0 + 1, to0 + 1, moved, from1 + 1, to1 + 1, moved1, ji, ki, skymid, o5);
+        if (moved) {
+            if (grew) { sum = sum + o5[0]; sumsq = sumsq + o5[1]; }
+            else { sum = sum - o5[0]; sumsq = sumsq - o5[1]; }
+            redo = true;
+        }
+        if (moved1) {
+            if (grew1) { sum = sum + o5[2]; sumsq = sumsq + o5[3]; }
+            else { sum = sum - o5[2]; sumsq = sumsq - o5[3]; }
             redo = true;
         }
         minimm = newmin;
         maximm = newmax;
-        const int ns = maximm - minimm;  // mmm.py:253-257
         if (ns < minsky) {
             R.skymod = skymod; R.sigma = -1.0; R.iters = niter;
             return R;
@@ -640,20 +714,7 @@ BP_HD MmmResult mmm_sorted(const Get& at, const DSums& delta_sums, const PSum& p
         if (var < 0) var = 0;
         sigma = sqrt(var);
         skymn = skymn + skymid;
-        // robust median: mean of the central 20 % (mmm.py:271-289; np.round = half-to-even)
-        const double center = (minimm + 1 + maximm) / 2.;
-        const double side = rint(0.2 * (maximm - minimm)) / 2. + 0.25;
-        double j = rint(center - side), k = rint(center + side);
-        if (readnoise != 0.0) {  // mmm.py:280-287
-            const double L = rint(center - 0.25), M = rint(center + 0.25), Rn = 0.25 * readnoise;
-            while (j > 0 && k < ns - 1 && ((at((int)L) - at((int)j)) < Rn || (at((int)k) - at((int)M)) < Rn)) {
-                j -= 1; k += 1;
-            }
-        }
-        int ji = (int)j, ki = (int)k + 1;
-        if (ji < 0) ji = 0;
-        if (ki > nsky) ki = nsky;
-        skymed = plain_sum(ji, ki) / (k - j + 1);
+        skymed = o5[4] / (k - j + 1);
         const double dmod = (skymed < skymn) ? 3. * skymed - 2. * skymn - skymod : skymn - skymod;  // mmm.py:294-296
         if (dmod * old < 0) clamp = 0.5 * clamp;  // mmm.py:299-301
         skymod = skymod + clamp * dmod;

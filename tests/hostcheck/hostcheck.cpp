@@ -50,6 +50,7 @@ static int mmm_indexed(const double* v, int n, double readnoise, int minsky, int
         V, [&](int lo, int hi, double, double* s1, double* s2) { V.delta_sums(lo, hi, s1, s2); },
         [&](int lo, int hi) { return V.plain_sum(lo, hi); },
         [&](double v1, bool st1, bool need1, double v2, bool st2, bool need2, int* r1, int* r2) { V.first2(v1, st1, need1, v2, st2, need2, r1, r2); },
+        [&](int lo0, int hi0, bool need0, int lo1, int hi1, bool need1, int lo2, int hi2, double, double* o5) { V.sums3(lo0, hi0, need0, lo1, hi1, need1, lo2, hi2, o5); },
         ns, readnoise, minsky, mxiter);
     out3[0] = R.skymod; out3[1] = R.sigma; out3[2] = R.skew;
     return R.iters;
@@ -126,7 +127,12 @@ int hc_mmm(const double* v, int n, double readnoise, int minsky, int mxiter, dou
         if (need1) *r1 = first(v1, st1);
         if (need2) *r2 = first(v2, st2);
     };
-    bphot::MmmResult R = bphot::mmm_sorted(at, dsum, psum, first2, ns, readnoise, minsky, mxiter);
+    auto sums3 = [&](int lo0, int hi0, bool need0, int lo1, int hi1, bool need1, int lo2, int hi2, double mid, double* o5) {
+        if (need0) dsum(lo0, hi0, mid, &o5[0], &o5[1]);
+        if (need1) dsum(lo1, hi1, mid, &o5[2], &o5[3]);
+        o5[4] = psum(lo2, hi2);
+    };
+    bphot::MmmResult R = bphot::mmm_sorted(at, dsum, psum, first2, sums3, ns, readnoise, minsky, mxiter);
     out3[0] = R.skymod; out3[1] = R.sigma; out3[2] = R.skew;
     return R.iters;
 }
