@@ -498,43 +498,13 @@ struct IndexedView {
         }
         *s1 = a; *s2 = q;
     }
-    // The three range sums of one clipping pass (mmm_sorted's sums3): six prefix evaluations whose loads are all
-    // issued before the first one is consumed.
+    // The three range sums of one clipping pass (mmm_sorted's sums3).  Only what is needed is loaded: measured on B200, issuing
+    // all six prefix evaluations unconditionally (so that their loads overlap) was slower, 6.1 -> 8.3 ms per 1 M stars -- the
+    // kernel is bound by the bytes it pulls through L2, and most passes near convergence move one edge or none.
     BP_HDM void sums3(int lo0, int hi0, bool need0, int lo1, int hi1, bool need1, int lo2, int hi2, double* o5) const {
-        const int idx[6] = {need0 ? hi0 : 0, need0 ? lo0 : 0, need1 ? hi1 : 0, need1 ? lo1 : 0, hi2 > lo2 ? hi2 : 0, hi2 > lo2 ? lo2 : 0};
-        double pa[6], pq[6];
-#if defined(__CUDA_ARCH__)
-        if constexpr (sizeof(T) == 4) {
-            float4 raw[6][4];
-#pragma unroll
-            for (int e = 0; e < 6; e++) {
-                const int g = idx[e] >> 4, c = idx[e] & 15;
-                bp_ld2(PT + 2 * g, &pa[e], &pq[e]);
-                const float4* p4 = reinterpret_cast<const float4*>(k + 16 * (c ? g : 0));  // c == 0: nothing is added, any group will do
-#pragma unroll
-                for (int u = 0; u < 4; u++) raw[e][u] = __ldg(p4 + u);
-            }
-#pragma unroll
-            for (int e = 0; e < 6; e++) {
-                const int c = idx[e] & 15;
-                double a = pa[e], q = pq[e];
-#pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const float f4[4] = {raw[e][u].x, raw[e][u].y, raw[e][u].z, raw[e][u].w};
-#pragma unroll
-                    for (int w = 0; w < 4; w++)
-                        if (4 * u + w < c) { const double d = (double)f4[w] - skymid; a = a + d; q = q + d * d; }
-                }
-                pa[e] = a; pq[e] = q;
-            }
-        } else
-#endif
-        {
-            for (int e = 0; e < 6; e++) prefix(idx[e], &pa[e], &pq[e]);
-        }
-        o5[0] = pa[0] - pa[1]; o5[1] = pq[0] - pq[1];
-        o5[2] = pa[2] - pa[3]; o5[3] = pq[2] - pq[3];
-        o5[4] = hi2 > lo2 ? (pa[4] - pa[5]) + (double)(hi2 - lo2) * skymid : 0.0;
+        if (need0) delta_sums(lo0, hi0, &o5[0], &o5[1]);
+        if (need1) delta_sums(lo1, hi1, &o5[2], &o5[3]);
+        o5[4] = plain_sum(lo2, hi2);
     }
     BP_HDM void delta_sums(int lo, int hi, double* s1, double* s2) const {
         double a1, q1, a0, q0;
@@ -577,31 +547,14 @@ struct IndexedView {
             }
         }
         const bool go1 = need1 && c1a > 0, go2 = need2 && c1b > 0;  // c1 == 0: key[0] passes, the answer is 0
-        // L2 group whose entry 0 is the last failing L1 key; a query that is not needed walks group 0 and is discarded, so
-        // that the loads of both queries are unconditional and in flight together
-        const int g1 = go1 ? 16 * (c1a - 1) : 0, g2 = go2 ? 16 * (c1b - 1) : 0;
-        double xa[16], xb[16];
-        load16(L2 + g1, xa);
-        load16(L2 + g2, xb);
-        int j1 = g1, j2 = g2;
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-        for (int t = 1; t < 16; t++) {
-            j1 += (t < n2 - g1 && !(st1 ? xa[t] > v1 : xa[t] >= v1)) ? 1 : 0;
-            j2 += (t < n2 - g2 && !(st2 ? xb[t] > v2 : xb[t] >= v2)) ? 1 : 0;
-        }
-        load16(k + 16 * j1, xa);                                    // k[16 j] is the last failing L2 key
-        load16(k + 16 * j2, xb);
-        int f1 = 16 * j1 + 1, f2 = 16 * j2 + 1;
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-        for (int t = 1; t < 16; t++) {
-            f1 += (t < n - 16 * j1 && !(st1 ? xa[t] > v1 : xa[t] >= v1)) ? 1 : 0;
-            f2 += (t < n - 16 * j2 && !(st2 ? xb[t] > v2 : xb[t] >= v2)) ? 1 : 0;
-        }
-        *r1 = go1 ? f1 : 0; *r2 = go2 ? f2 : 0;
+        const int g1 = 16 * (c1a - 1), g2 = 16 * (c1b - 1);         // L2 group whose entry 0 is the last failing L1 key
+        int j1 = 0, j2 = 0;
+        if (go1) j1 = g1 + count_fail(L2 + g1, 1, n2 - g1, v1, st1);
+        if (go2) j2 = g2 + count_fail(L2 + g2, 1, n2 - g2, v2, st2);
+        int f1 = 0, f2 = 0;                                         // k[16 j] is the last failing L2 key
+        if (go1) f1 = 16 * j1 + 1 + count_fail(k + 16 * j1, 1, n - 16 * j1, v1, st1);
+        if (go2) f2 = 16 * j2 + 1 + count_fail(k + 16 * j2, 1, n - 16 * j2, v2, st2);
+        *r1 = f1; *r2 = f2;
     }
 };
 

@@ -46,6 +46,9 @@ BP_D double pk_max(double v) { return warp_max(v); }
 #ifndef PK_MINB_FORCED
 #define PK_MINB_FORCED 5  // resident CTAs per SM the forced variant's register budget is compiled for
 #endif
+#ifndef PK_MINB_FIT
+#define PK_MINB_FIT 1  // resident CTAs per SM the recentring variants' register budget is compiled for
+#endif
 constexpr int PK_WARPS = 4;
 constexpr int PK_THREADS = PK_WARPS * 32;
 constexpr int PK_NARR_FIT = 10;     // per-warp scratch arrays of `cap` doubles, recentring variants
@@ -612,7 +615,7 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
 
 // Shared memory: [psf table | per-warp W arrays | per-warp AX | per-warp GIDX (variants 0, 1)].
 template <int V, typename TI, typename TN>
-__global__ void __launch_bounds__(PK_THREADS, V == 2 ? PK_MINB_FORCED : 1) pkfit_kernel(const PkfitParams P) {
+__global__ void __launch_bounds__(PK_THREADS, V == 2 ? PK_MINB_FORCED : PK_MINB_FIT) pkfit_kernel(const PkfitParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int NARR = (V == 2) ? PK_NARR_FORCED : PK_NARR_FIT;
     double* sbase = reinterpret_cast<double*>(smem_raw);
