@@ -47,7 +47,7 @@ BP_D double pk_max(double v) { return warp_max(v); }
 #define PK_MINB_FORCED 5  // resident CTAs per SM the forced variant's register budget is compiled for
 #endif
 #ifndef PK_MINB_FIT
-#define PK_MINB_FIT 1  // resident CTAs per SM the recentring variants' register budget is compiled for
+#define PK_MINB_FIT 5  // resident CTAs per SM the recentring variants are compiled for (config5 fits: 323.8 ms at 1, 297.6 at 4, 287.7 at 5 per 2.5 M stars)
 #endif
 constexpr int PK_WARPS = 4;
 constexpr int PK_THREADS = PK_WARPS * 32;
