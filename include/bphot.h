@@ -62,6 +62,13 @@ long long bphot_launch_count(void);
  * accumulators; returns the previous setting.  bphot_kernel_times fills ms[4] / launches[4] with the summed
  * durations and launch counts of 0 aper_stage1 (gather + sort), 1 aper_sums, 2 aper_stage2 (mmm), 3 pkfit.
  */
+/*
+ * Copies a PAGE-LOCKED host buffer into device memory with a kernel that reads the host pages directly (zero-copy loads
+ * over PCIe) instead of a cudaMemcpyAsync: the transfer then does not queue on the copy engine behind image uploads that
+ * are already in flight (a star list of 16 MB otherwise waits for 600 MB of exposure).  Returns BPHOT_ERR_ARG when h_src is
+ * not page-locked (the caller falls back to cudaMemcpyAsync).
+ */
+int bphot_fetch_host(void* d_dst, const void* h_src, long long nbytes, void* stream);
 int bphot_profile(int enable);
 int bphot_kernel_times(double* ms, long long* launches);
 

@@ -29,6 +29,7 @@ _SIGNATURES = {
     "bphot_last_error": (C.c_char_p, []),
     "bphot_device_count": (C.c_int, []),
     "bphot_launch_count": (C.c_longlong, []),
+    "bphot_fetch_host": (C.c_int, [_vp, _vp, _ll, _vp]),
     "bphot_profile": (C.c_int, [_i]),
     "bphot_kernel_times": (C.c_int, [_vp, _vp]),
     "bphot_aper_device": (C.c_int, [_vp, _i, _i, _i, _ll, _vp, _vp, _i, _d, _vp, _i, _d, _d, _d, _d, _d, _i, _vp, _i, _i,
@@ -258,8 +259,19 @@ def to_device_f64(a, device, n=None):
     if isinstance(a, torch.Tensor):
         t = a.to(device=device, dtype=torch.float64, non_blocking=True).reshape(-1)
     else:
-        t = torch.from_numpy(np.ascontiguousarray(np.atleast_1d(np.asarray(a, dtype=np.float64)).reshape(-1))).to(
-            device, non_blocking=True)
+        h = torch.from_numpy(np.ascontiguousarray(np.atleast_1d(np.asarray(a, dtype=np.float64)).reshape(-1)))
+        if h.numel() >= 4096 and h.is_pinned():
+            # page-locked column: fetched by a kernel reading the host pages (bphot_fetch_host), so that it does not wait on
+            # the copy engine behind an exposure upload that is still in flight
+            t = torch.empty(h.shape, dtype=torch.float64, device=device)
+            with torch.cuda.device(device):
+                rc = lib().bphot_fetch_host(ptr(t), C.c_void_p(h.data_ptr()), h.numel() * 8, stream_ptr(device))
+            if rc != 0:
+                t = h.to(device, non_blocking=True)
+            else:
+                t._bphot_keepalive = h  # the host block must outlive the kernel; dropped with the tensor
+        else:
+            t = h.to(device, non_blocking=True)
     if n is not None and t.numel() != n:
         if t.numel() != 1:
             raise BphotError("star-list column has %d entries, expected %d" % (t.numel(), n))

@@ -107,19 +107,19 @@ class PkfitEngine(object):
         y_t = _lib.to_device_f64(y, dev, n)
         scale_t = _lib.to_device_f64(scale, dev, n)
         sky_t = _lib.to_device_f64(sky, dev, n)
-        o = self.fit_device(variant, scale_t, x_t, y_t, sky_t, radius, maxiter=maxiter, recenter=recenter)
+        from .shard import FIT_SPEC, ResultArena
+        arena = ResultArena(FIT_SPEC(torch), n, dev)  # the kernel writes into one byte arena: one device->host copy
+        self.fit_device(variant, scale_t, x_t, y_t, sky_t, radius, maxiter=maxiter, recenter=recenter, out=arena.views)
         cols = ["errmag", "chi", "sharp", "niter", "scale"]
         if xyout:
             cols += ["x", "y"]
         if returnchi2:
             cols += ["chi2"]
-        # one device->host transfer for the fp64 columns
-        f64cols = [c for c in cols if c != "niter"]
         with torch.cuda.device(dev):
-            packed, niter = _lib.to_host([torch.stack([o[c] for c in f64cols]), o["niter"]])
+            h = arena.to_host()
         res = []
         for c in cols:
-            a = niter if c == "niter" else packed[f64cols.index(c)]
+            a = h[c]
             if scalar:
                 a = int(a[0]) if c == "niter" else float(a[0])
             res.append(a)

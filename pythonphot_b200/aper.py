@@ -125,16 +125,20 @@ def aper(image, xc, yc, phpadu=1, apr=5, zeropoint=25,
     img_t = dimg.tensor
     xc_t = _lib.to_device_f64(xc, dev)
     yc_t = _lib.to_device_f64(yc, dev)
+    # the kernels write into one byte arena, which comes back in ONE device->host copy
+    from .shard import APER_SPEC, ResultArena
+    naper = _lib.host_f64(apr).size
+    arena = ResultArena(APER_SPEC(torch, naper) + [('badflag_f', torch.float64, (naper,))], nstars, dev)
     o = aper_device(img_t, xc_t, yc_t, phpadu=phpadu, apr=apr, zeropoint=zeropoint, skyrad=skyrad, badpix=badpix,
                     setskyval=setskyval, minsky=_minsky_value(minsky), exact=exact, readnoise=readnoise,
-                    compat=compat, skyalgorithm=skyalgorithm, bands=(dimg.events, dimg.band_rows) if dimg.events else None)
-    o = dict(o)
-    o['badflag'] = o['badflag'].to(torch.float64)  # the reference stores 0./1. (aper.py:174); cast on the device, not on the host
+                    compat=compat, skyalgorithm=skyalgorithm, bands=(dimg.events, dimg.band_rows) if dimg.events else None,
+                    out={k: v for k, v in arena.views.items() if k != 'badflag_f'})
+    arena.views['badflag_f'].copy_(o['badflag'])  # the reference stores 0./1. (aper.py:174); cast on the device, not on the host
     with torch.cuda.device(dev):
-        h = dict(zip(o.keys(), _lib.to_host(list(o.values()))))
+        h = arena.to_host()
     mag, magerr, flux, fluxerr = h['mag'], h['magerr'], h['flux'], h['fluxerr']
     sky, skyerr = h['sky'], h['skyerr']
-    badflag = h['badflag']
+    badflag = h['badflag_f']
     xh = np.asarray(xc.cpu() if isinstance(xc, torch.Tensor) else xc, dtype=np.float64).reshape(-1)
     yh = np.asarray(yc.cpu() if isinstance(yc, torch.Tensor) else yc, dtype=np.float64).reshape(-1)
     outstr = OutStr(xh, yh, mag, magerr)

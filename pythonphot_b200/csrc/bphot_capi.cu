@@ -190,6 +190,12 @@ __global__ void tile_key_kernel(const double* x, const double* y, int n, int nro
         idx[i] = i;
     }
 }
+// device-side copy out of page-locked host memory (bphot_fetch_host): 16-byte loads over PCIe, grid-stride
+__global__ void fetch_host_kernel(uint4* __restrict__ dst, const uint4* __restrict__ src, long long n16, unsigned char* dst8,
+                                  const unsigned char* src8, long long tail0, long long nbytes) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16; i += (long long)gridDim.x * blockDim.x) dst[i] = src[i];
+    for (long long i = tail0 + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nbytes; i += (long long)gridDim.x * blockDim.x) dst8[i] = src8[i];
+}
 // largest y of the stars of each batch of the visiting order (one CTA per batch): which image rows the batch needs
 __global__ void batch_maxrow_kernel(const double* y, const int* order, int n, int batch, float* out) {
     __shared__ float s[256];
@@ -391,6 +397,26 @@ const char* bphot_build_flags(void) {
 }
 const char* bphot_last_error(void) { return g_err; }
 long long bphot_launch_count(void) { return g_launches.load(); }
+
+int bphot_fetch_host(void* d_dst, const void* h_src, long long nbytes, void* stream) {
+    if (nbytes < 0 || (nbytes > 0 && (!d_dst || !h_src))) return fail(BPHOT_ERR_ARG, "bphot_fetch_host: null pointer");
+    if (nbytes == 0) return BPHOT_OK;
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, h_src) != cudaSuccess || at.type != cudaMemoryTypeHost || !at.devicePointer) {
+        cudaGetLastError();
+        return fail(BPHOT_ERR_ARG, "bphot_fetch_host: source is not page-locked host memory");
+    }
+    const bool aligned = (((uintptr_t)d_dst | (uintptr_t)at.devicePointer) & 15) == 0;
+    const long long n16 = aligned ? nbytes / 16 : 0;
+    long long blocks = (nbytes / 16 + 255) / 256;
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    if (blocks < 1) blocks = 1;
+    fetch_host_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>((uint4*)d_dst, (const uint4*)at.devicePointer, n16, (unsigned char*)d_dst,
+                                                                    (const unsigned char*)at.devicePointer, n16 * 16, nbytes);
+    g_launches += 1;
+    CU_TRY(cudaGetLastError());
+    return BPHOT_OK;
+}
 
 int bphot_profile(int enable) {
     const int prev = g_profile.exchange(enable ? 1 : 0);

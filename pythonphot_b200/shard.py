@@ -163,6 +163,10 @@ def unpack_records(packed, layout):
     return out
 
 
+_NP_DTYPES = {"torch.float64": np.float64, "torch.float32": np.float32, "torch.int32": np.int32, "torch.uint8": np.uint8,
+              "torch.int64": np.int64}
+
+
 class ResultArena(object):
     """Per-star result columns of one shard as typed views of ONE flat byte buffer.
 
@@ -192,6 +196,20 @@ class ResultArena(object):
         first = next(iter(results.values()))
         spec = [(k, v.dtype, tuple(v.shape[1:])) for k, v in results.items()]
         return cls(spec, first.shape[0], device if device is not None else first.device)
+
+    def to_host(self):
+        """The whole arena in ONE device->host copy through a page-locked block; returns {column: numpy view of that block}.
+        (Nine separate column copies of a 1 M-star ``aper`` result took 5-9 ms on B200, one 144 MB copy 2.7 ms.)"""
+        import torch
+        h = torch.empty(self.nbytes, dtype=torch.uint8, pin_memory=True)
+        h.copy_(self.flat, non_blocking=True)
+        torch.cuda.current_stream(self.flat.device).synchronize()
+        hn = h.numpy()
+        out = {}
+        for name, dt, tail in self.spec:
+            o, nb = self.offsets[name]
+            out[name] = hn[o:o + nb].view(_NP_DTYPES[str(dt)]).reshape((self.m,) + tail)
+        return out
 
     def store(self, results):
         """Copy result tensors that are not already this arena's views into it."""

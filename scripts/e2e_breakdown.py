@@ -32,3 +32,49 @@ T("aper.aper() host API, host image", lambda: pp.aper.aper(img, f["x"], f["y"], 
 pk = T("pkfit_class(...) construct (3 uploads)", lambda: pp.pkfit_class(img, f["gauss"], f["psf"], f["ronois"], f["phpadu"], noise, mask))
 one, sky = np.ones(nst), np.full(nst, f["sky"])
 T("pk.pkfit_norecent_noise host API", lambda: pk.pkfit_norecent_noise(one, f["xfit"], f["yfit"], sky, 5.0))
+
+# ---- round 2: the bench's end-to-end order (pkfit_class first, aper on its device image), piece by piece
+print("--- round 2 path")
+def e2e():
+    pkh = pp.pkfit_class(img, f["gauss"], f["psf"], f["ronois"], f["phpadu"], noise, mask)
+    a = pp.aper.aper(pkh.image_device(), f["x"], f["y"], verbose=False, **kw)
+    b = pkh.pkfit_norecent_noise(one, f["xfit"], f["yfit"], sky, 5.0)
+    return a, b
+T("e2e: pkfit_class + aper(image_device) + fit", e2e)
+hx = torch.from_numpy(f["x"]).pin_memory().numpy(); hy = torch.from_numpy(f["y"]).pin_memory().numpy()
+T("star columns x, y -> device (pinned)", lambda: (_lib.to_device_f64(hx, dev), _lib.to_device_f64(hy, dev)))
+T("star columns x, y -> device (pageable)", lambda: (_lib.to_device_f64(f["x"], dev), _lib.to_device_f64(f["y"], dev)))
+o2 = dict(o); o2["badflag"] = o["badflag"].to(torch.float64)
+T("_lib.to_host(aper results, 144 MB)", lambda: _lib.to_host(list(o2.values())))
+big = torch.empty(256 << 20, dtype=torch.uint8, device=dev); hb = torch.empty(256 << 20, dtype=torch.uint8).pin_memory()
+T("D2H 256 MiB pinned", lambda: hb.copy_(big, non_blocking=True))
+T("H2D 256 MiB pinned", lambda: big.copy_(hb, non_blocking=True))
+def banded_only():
+    d = _lib.upload_image_banded(img, dev); d.ready(); return d
+T("banded upload of the image alone", banded_only)
+def aper_banded():
+    d = _lib.upload_image_banded(img, dev)
+    return aper_device(d.tensor, x_t, y_t, bands=(d.events, d.band_rows), **kw)
+T("banded upload + aper_device (no result copy)", aper_banded)
+fo = T("fit_device (kernels only)", lambda: pk.fit_device(_lib.PKFIT_NORECENT, _lib.to_device_f64(one, dev), _lib.to_device_f64(f["xfit"], dev), _lib.to_device_f64(f["yfit"], dev), _lib.to_device_f64(sky, dev), 5.0))
+print("--- host-side timeline of one end-to-end step (no extra synchronisation)")
+for rep_ in range(3):
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    pkh = pp.pkfit_class(img, f["gauss"], f["psf"], f["ronois"], f["phpadu"], noise, mask)
+    t1 = time.perf_counter()
+    a = pp.aper.aper(pkh.image_device(), hx, hy, verbose=False, **kw)
+    t2 = time.perf_counter()
+    b = pkh.pkfit_norecent_noise(one, f["xfit"], f["yfit"], sky, 5.0)
+    t3 = time.perf_counter()
+    torch.cuda.synchronize()
+    t4 = time.perf_counter()
+    print("construct %.2f ms | aper.aper %.2f ms | fit %.2f ms | tail sync %.2f ms | total %.2f ms" % (
+        1e3 * (t1 - t0), 1e3 * (t2 - t1), 1e3 * (t3 - t2), 1e3 * (t4 - t3), 1e3 * (t4 - t0)))
+import cProfile, pstats
+pr = cProfile.Profile(); pr.enable()
+pkh = pp.pkfit_class(img, f["gauss"], f["psf"], f["ronois"], f["phpadu"], noise, mask)
+a = pp.aper.aper(pkh.image_device(), hx, hy, verbose=False, **kw)
+b = pkh.pkfit_norecent_noise(one, f["xfit"], f["yfit"], sky, 5.0)
+pr.disable()
+pstats.Stats(pr).sort_stats("cumulative").print_stats(18)
