@@ -827,8 +827,9 @@ __global__ void __launch_bounds__(AP_THREADS, AP_S2_MINB) aper_stage2_kernel(con
 // (IndexedView).  32 stars per warp: ~1.5 k warp-instructions per star instead of the warp-per-star kernel's 14 k.
 // Range sums come from prefix differences, so their last bits differ from a direct sum (1e-13 relative); counts and
 // iteration numbers are decided by the same comparisons on the same keys.
+constexpr int AP_MMM_THREADS = 64;  // 64 threads x <= 64 registers = the 4 096 registers per SM that stage 1's 8 CTAs leave free
 template <typename T>
-__global__ void __launch_bounds__(AP_THREADS) aper_mmm_kernel(const AperParams P) {
+__global__ void __launch_bounds__(AP_MMM_THREADS, 16) aper_mmm_kernel(const AperParams P) {
     const T* __restrict__ skeys = reinterpret_cast<const T*>(P.skeys);
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < P.scount; j += gridDim.x * blockDim.x) {
         const int i = P.s0 + j;

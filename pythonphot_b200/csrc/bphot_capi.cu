@@ -87,6 +87,9 @@ int next_pow2(long long v) {
 #ifndef AP_MMM_INDEXED
 #define AP_MMM_INDEXED 1  // 1 = mmm by one thread per star on the indexed sorted row; 0 = one warp per star on the plain row
 #endif
+#ifndef AP_MMM_OVERLAP
+#define AP_MMM_OVERLAP 1  // 1 = the thread-per-star mmm of batch b runs on a side stream under stage 1 of batch b+1 (two scratch buffers)
+#endif
 #ifndef AP_SIDE_STREAM
 #define AP_SIDE_STREAM 0  // measured: co-running aper_sums with stage 1/2 does not pay; kept as a build knob
 #endif
@@ -391,7 +394,7 @@ int bphot_version(void) { return BPHOT_VERSION; }
 #define BP_STR2(x) #x
 #define BP_STR(x) BP_STR2(x)
 const char* bphot_build_flags(void) {
-    return "AP_ASM_SELECT=" BP_STR(AP_ASM_SELECT) " AP_BATCH=" BP_STR(AP_BATCH) " AP_S1_CTAS=" BP_STR(AP_S1_CTAS) " AP_MMM_INDEXED=" BP_STR(AP_MMM_INDEXED)
+    return "AP_ASM_SELECT=" BP_STR(AP_ASM_SELECT) " AP_BATCH=" BP_STR(AP_BATCH) " AP_S1_CTAS=" BP_STR(AP_S1_CTAS) " AP_MMM_INDEXED=" BP_STR(AP_MMM_INDEXED) " AP_MMM_OVERLAP=" BP_STR(AP_MMM_OVERLAP)
            " AP_S2_MINB=" BP_STR(AP_S2_MINB) " AP_SUMS_CTAS=" BP_STR(AP_SUMS_CTAS) " AP_DYNAMIC=" BP_STR(AP_DYNAMIC)
            " PK_MINB_FORCED=" BP_STR(PK_MINB_FORCED) " PK_U=" BP_STR(PK_U) " PK_MINB_FIT=" BP_STR(PK_MINB_FIT) " PK_HOIST=" BP_STR(PK_HOIST) " PK_PSF_GLOBAL=" BP_STR(PK_PSF_GLOBAL) " AP_IDX_SKIP=" BP_STR(AP_IDX_SKIP);
 }
@@ -520,11 +523,18 @@ int bphot_aper_device_banded(const void* d_image, int image_dtype, int nrow, int
     const bool indexed = AP_MMM_INDEXED && K > 0 && !use_setsky && !P.sky_sigclip;
     const size_t keys_bytes = ((size_t)batch * P.sstride * es + 255) & ~(size_t)255;
     P.idx_stride = indexed ? (long long)sort_index_bytes(es) : 0;
-    if (!use_setsky) CU_TRY(cudaMallocAsync(&scratch, keys_bytes + (size_t)batch * (size_t)P.idx_stride, st));
+    const int nbatch = (nstars + batch - 1) / batch;
+    // The thread-per-star mmm waits for memory and leaves the issue slots idle; stage 1 is bound by issue slots and leaves
+    // exactly 4 096 registers per SM free (8 CTAs x 96 threads x 80 registers).  So mmm runs in 64-thread blocks of <= 64
+    // registers on a side stream, batch b under stage 1 of batch b+1, on a second scratch buffer.  Per-kernel timing
+    // (bphot_profile) keeps everything on one stream.
+    const bool overlap = AP_MMM_OVERLAP && indexed && nbatch > 1 && g_profile.load() == 0;
+    const int nbuf = overlap ? 2 : 1;
+    const size_t buf_bytes = (keys_bytes + (size_t)batch * (size_t)P.idx_stride + 255) & ~(size_t)255;
+    if (!use_setsky) CU_TRY(cudaMallocAsync(&scratch, (size_t)nbuf * buf_bytes, st));
     P.skeys = scratch;
     P.sidx = indexed ? (void*)(reinterpret_cast<char*>(scratch) + keys_bytes) : nullptr;
     // one zeroed work counter per stage-1 / retry / stage-2 launch
-    const int nbatch = (nstars + batch - 1) / batch;
     int* counters = nullptr;
     CU_TRY(cudaMallocAsync((void**)&counters, (size_t)(3 * nbatch + 2) * sizeof(int), st));
     CU_TRY(cudaMemsetAsync(counters, 0, (size_t)(3 * nbatch + 2) * sizeof(int), st));
@@ -589,7 +599,7 @@ int bphot_aper_device_banded(const void* d_image, int image_dtype, int nrow, int
 #define BP_STAGE2(T)                                                                                              \
     do {                                                                                                          \
         if (indexed) {                                                                                            \
-            aper_mmm_kernel<T><<<(P.scount + AP_THREADS - 1) / AP_THREADS, AP_THREADS, 0, st>>>(P);               \
+            aper_mmm_kernel<T><<<(P.scount + AP_MMM_THREADS - 1) / AP_MMM_THREADS, AP_MMM_THREADS, 0, overlap ? s2 : st>>>(P); \
             break;                                                                                                \
         }                                                                                                         \
         rc = persistent_grid(aper_stage2_kernel<T>, AP_THREADS, 0, (P.scount + AP_WARPS - 1) / AP_WARPS, &grid2); \
@@ -631,20 +641,47 @@ int bphot_aper_device_banded(const void* d_image, int image_dtype, int nrow, int
         if (side) cudaEventRecord(ev_join, side);
     };
     if (nbands == 0) launch_sums();  // otherwise after the batches: by then the whole image is resident
+    cudaStream_t s2 = nullptr;
+    std::vector<cudaEvent_t> ev_s1, ev_m;
+    if (overlap) {
+        rc = side_stream(&s2);
+        if (rc) { if (scratch) cudaFreeAsync(scratch, st); cudaFreeAsync(counters, st); ord.release(st); return rc; }
+        ev_s1.resize(nbatch); ev_m.resize(nbatch);
+        for (int b = 0; b < nbatch; b++) {
+            cudaEventCreateWithFlags(&ev_s1[b], cudaEventDisableTiming);
+            cudaEventCreateWithFlags(&ev_m[b], cudaEventDisableTiming);
+        }
+    }
     for (int s0 = 0; s0 < nstars && !rc; s0 += batch) {
+        const int b = s0 / batch;
         P.s0 = s0;
         P.scount = (nstars - s0) < batch ? (nstars - s0) : batch;
-        if (nbands > 0) wait_band(batch_band[s0 / batch]);
+        if (scratch) {
+            char* buf = reinterpret_cast<char*>(scratch) + (size_t)(b % nbuf) * buf_bytes;
+            P.skeys = buf;
+            P.sidx = indexed ? (void*)(buf + keys_bytes) : nullptr;
+        }
+        if (nbands > 0) wait_band(batch_band[b]);
+        if (overlap && b >= nbuf) cudaStreamWaitEvent(st, ev_m[b - nbuf], 0);  // the buffer's previous reader is done
         lt.begin(KT_APER_STAGE1);
         if (image_dtype == BPHOT_F32) BP_STAGE1_K(float);
         else BP_STAGE1_K(double);
         lt.end();
         if (rc) break;
+        if (overlap) {
+            cudaEventRecord(ev_s1[b], st);
+            cudaStreamWaitEvent(s2, ev_s1[b], 0);
+        }
         lt.begin(KT_APER_STAGE2);
         if (image_dtype == BPHOT_F32) BP_STAGE2(float);
         else BP_STAGE2(double);
         lt.end();
+        if (overlap) cudaEventRecord(ev_m[b], s2);
         g_launches += 2;
+    }
+    if (overlap) {
+        for (int b = 0; b < nbatch; b++) cudaStreamWaitEvent(st, ev_m[b], 0);  // unrecorded events (error path) are no-ops
+        for (int b = 0; b < nbatch; b++) { cudaEventDestroy(ev_s1[b]); cudaEventDestroy(ev_m[b]); }
     }
 #undef BP_STAGE2
 #undef BP_STAGE1_K

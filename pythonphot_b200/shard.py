@@ -132,11 +132,12 @@ class ShardPlan(object):
         return full.index_select(0, self._index_t("inverse", 0, full.device))
 
 
-def gather_arena(plan, arena, group=None, side_stream=None):
+def gather_arena(plan, arena, group=None, side_stream=None, ncols=None):
     """All-gather a ``ResultArena`` (one NCCL ``all_gather_into_tensor`` of ``arena.nbytes`` per rank) and copy every column
     into caller order.  With ``side_stream`` (CUDA) both run on that stream, after the work already queued on the current
-    one; the returned ``GatherHandle.result()`` joins.  Works on CPU tensors under gloo (tests)."""
-    return _gather_arena(plan, arena, group=group, side_stream=side_stream)
+    one; the returned ``GatherHandle.result()`` joins.  ``ncols`` gathers only the first columns of the arena's spec (a
+    prefix of the flat buffer).  Works on CPU tensors under gloo (tests)."""
+    return _gather_arena(plan, arena, group=group, side_stream=side_stream, ncols=ncols)
 
 
 def pack_records(columns):
@@ -234,7 +235,7 @@ class GatherHandle(object):
         return self._outs
 
 
-def _gather_arena(plan, arena, group=None, side_stream=None):
+def _gather_arena(plan, arena, group=None, side_stream=None, ncols=None):
     import torch
     dist = _dist()
     rank, world = world_info(group)
@@ -243,19 +244,23 @@ def _gather_arena(plan, arena, group=None, side_stream=None):
     dev = arena.flat.device
     use_side = side_stream is not None and dev.type == "cuda"
     # buffers are allocated on the caller's stream; the side stream only uses them between wait_stream pairs
-    full = arena.flat.reshape(1, -1) if world == 1 else torch.empty((world, arena.nbytes), dtype=torch.uint8, device=dev)
+    spec = arena.spec if ncols is None else arena.spec[:ncols]
+    last_off, last_nb = arena.offsets[spec[-1][0]]
+    nbytes = arena.nbytes if ncols is None else (last_off + last_nb + 255) // 256 * 256  # the prefix that holds `spec`
+    flat = arena.flat[:nbytes]
+    full = flat.reshape(1, -1) if world == 1 else torch.empty((world, nbytes), dtype=torch.uint8, device=dev)
     ridx, pidx = plan._index_t("rank_of", 0, dev), plan._index_t("pos_of", 0, dev)
-    outs = {name: torch.empty((plan.n,) + tail, dtype=dt, device=dev) for name, dt, tail in arena.spec}
+    outs = {name: torch.empty((plan.n,) + tail, dtype=dt, device=dev) for name, dt, tail in spec}
 
     def work():
         if world > 1:
-            dist.all_gather_into_tensor(full.reshape(-1), arena.flat, group=group)
-        for name, dt, tail in arena.spec:
+            dist.all_gather_into_tensor(full.reshape(-1), flat, group=group)
+        for name, dt, tail in spec:
             o, nb = arena.offsets[name]
             es = outs[name].element_size()
             k = int(np.prod(tail, dtype=np.int64))
             typed = full.reshape(-1).view(dt)
-            col = torch.as_strided(typed, (world, plan.m, k), (arena.nbytes // es, k, 1), o // es)  # [rank, star, component]
+            col = torch.as_strided(typed, (world, plan.m, k), (nbytes // es, k, 1), o // es)  # [rank, star, component]
             if plan.n:
                 outs[name].reshape(plan.n, k).copy_(col[ridx, pidx])  # row s <- (rank_of[s], pos_of[s])
     if use_side:
@@ -315,8 +320,9 @@ APER_SPEC = lambda torch, naper: [("mag", torch.float64, (naper,)), ("magerr", t
                                   ("flux", torch.float64, (naper,)), ("fluxerr", torch.float64, (naper,)),
                                   ("sky", torch.float64, ()), ("skyerr", torch.float64, ()),
                                   ("badflag", torch.uint8, (naper,)), ("nsky", torch.int32, ()), ("mmm_iter", torch.int32, ())]
-FIT_SPEC = lambda torch: [(k, torch.float64, ()) for k in ("errmag", "chi", "sharp", "scale", "x", "y", "chi2")] + \
-    [("niter", torch.int32, ())]  # noqa: E731
+# the reference's own five return values first: a caller that does not need x, y, chi2 gathers only that prefix of the arena
+FIT_SPEC = lambda torch: [(k, torch.float64, ()) for k in ("errmag", "chi", "sharp", "scale")] + [("niter", torch.int32, ())] + \
+    [(k, torch.float64, ()) for k in ("x", "y", "chi2")]  # noqa: E731
 
 
 def exposure_header(image_t, noise_t, mask_t):
