@@ -487,18 +487,20 @@ BP_D ApPartial aperture_warp(const AperParams& P, const T* __restrict__ stamp, c
     const int npx = (bw > 0 && bh > 0) ? bw * bh : 0;
     const unsigned lt = (1u << lane) - 1u;
     int cnt = 0;
-    for (int base = w * 32; base < npx; base += 32 * nw) {
+    // box position (row rr, column cc) of this lane's pixel, advanced by the loop stride without a division per pixel
+    const int step = 32 * nw, bwd = bw > 0 ? bw : 1, krow = step / bwd, kcol = step - krow * bwd;
+    int rr = (w * 32 + lane) / bwd, cc = (w * 32 + lane) - rr * bwd;
+    for (int base = w * 32; base < npx; base += step) {
         const int p = base + lane;
         int r = 0, c = 0, cls = 0;
         double xxp = 0., yyp = 0., wgt = 0.;
         bool full = false;
         if (p < npx) {
-            const int rr = p / bw;
             r = r0 + rr;
-            c = c0 + (p - rr * bw);
+            c = c0 + cc;
             if (P.exact) {  // aper.py:313-333
                 xxp = (double)c;
-                yyp = P.compat_py2 ? (double)r : (double)((long long)r * g.nx + c) / (double)g.nx;
+                yyp = P.compat_py2 ? (double)r : (double)(r * g.nx + c) / (double)g.nx;  // r * nx + c < 2^31 (stamp <= 20 000 px wide)
                 const double x1 = fabs(xxp - g.dx), y1 = fabs(yyp - g.dy);
                 if (!(x1 > bigrad || y1 > bigrad)) cls = (x1 < smallrad && y1 < smallrad) ? 1 : pixel_class(x1, y1, ap);
                 if (cls == 1) wgt = 1.0;
@@ -525,6 +527,8 @@ BP_D ApPartial aperture_warp(const AperParams& P, const T* __restrict__ stamp, c
             flush_cross_list<T>(P, stamp, g, ap, L, cnt, lane, A);
             cnt = 0;
         }
+        rr += krow; cc += kcol;
+        if (cc >= bwd) { cc -= bwd; rr++; }
     }
     if (cnt > 0) flush_cross_list<T>(P, stamp, g, ap, L, cnt, lane, A);
     A.sfull = warp_sum(A.sfull);
@@ -827,9 +831,13 @@ __global__ void __launch_bounds__(AP_THREADS, AP_S2_MINB) aper_stage2_kernel(con
 // (IndexedView).  32 stars per warp: ~1.5 k warp-instructions per star instead of the warp-per-star kernel's 14 k.
 // Range sums come from prefix differences, so their last bits differ from a direct sum (1e-13 relative); counts and
 // iteration numbers are decided by the same comparisons on the same keys.
-constexpr int AP_MMM_THREADS = 64;  // 64 threads x <= 64 registers = the 4 096 registers per SM that stage 1's 8 CTAs leave free
+#ifndef AP_MMM_OVERLAP
+#define AP_MMM_OVERLAP 0
+#endif
+// with AP_MMM_OVERLAP: 64 threads x <= 64 registers = the 4 096 registers per SM that stage 1's 8 CTAs leave free
+constexpr int AP_MMM_THREADS = AP_MMM_OVERLAP ? 64 : AP_THREADS;
 template <typename T>
-__global__ void __launch_bounds__(AP_MMM_THREADS, 16) aper_mmm_kernel(const AperParams P) {
+__global__ void __launch_bounds__(AP_MMM_THREADS, AP_MMM_OVERLAP ? 16 : 1) aper_mmm_kernel(const AperParams P) {
     const T* __restrict__ skeys = reinterpret_cast<const T*>(P.skeys);
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < P.scount; j += gridDim.x * blockDim.x) {
         const int i = P.s0 + j;

@@ -88,7 +88,7 @@ int next_pow2(long long v) {
 #define AP_MMM_INDEXED 1  // 1 = mmm by one thread per star on the indexed sorted row; 0 = one warp per star on the plain row
 #endif
 #ifndef AP_MMM_OVERLAP
-#define AP_MMM_OVERLAP 1  // 1 = the thread-per-star mmm of batch b runs on a side stream under stage 1 of batch b+1 (two scratch buffers)
+#define AP_MMM_OVERLAP 0  // 1 = the thread-per-star mmm of batch b runs on a side stream under stage 1 of batch b+1 (two scratch buffers); measured: no gain
 #endif
 #ifndef AP_SIDE_STREAM
 #define AP_SIDE_STREAM 0  // measured: co-running aper_sums with stage 1/2 does not pay; kept as a build knob
@@ -524,10 +524,11 @@ int bphot_aper_device_banded(const void* d_image, int image_dtype, int nrow, int
     const size_t keys_bytes = ((size_t)batch * P.sstride * es + 255) & ~(size_t)255;
     P.idx_stride = indexed ? (long long)sort_index_bytes(es) : 0;
     const int nbatch = (nstars + batch - 1) / batch;
-    // The thread-per-star mmm waits for memory and leaves the issue slots idle; stage 1 is bound by issue slots and leaves
-    // exactly 4 096 registers per SM free (8 CTAs x 96 threads x 80 registers).  So mmm runs in 64-thread blocks of <= 64
-    // registers on a side stream, batch b under stage 1 of batch b+1, on a second scratch buffer.  Per-kernel timing
-    // (bphot_profile) keeps everything on one stream.
+    // AP_MMM_OVERLAP (off): the thread-per-star mmm waits for memory and leaves the issue slots idle, stage 1 is bound by issue
+    // slots and leaves exactly 4 096 registers per SM free (8 CTAs x 96 threads x 80 registers), so mmm was run in 64-thread
+    // blocks of <= 64 registers on a side stream, batch b under stage 1 of batch b+1, on a second scratch buffer.  Measured on
+    // B200: aper 56.0 ms with, 55.7 ms without -- the side kernel's blocks do not get SM time while the persistent stage-1 grid
+    // is resident -- so the knob stays off.  Per-kernel timing (bphot_profile) always keeps everything on one stream.
     const bool overlap = AP_MMM_OVERLAP && indexed && nbatch > 1 && g_profile.load() == 0;
     const int nbuf = overlap ? 2 : 1;
     const size_t buf_bytes = (keys_bytes + (size_t)batch * (size_t)P.idx_stride + 255) & ~(size_t)255;
