@@ -26,6 +26,9 @@ constexpr int AP_WARPS = AP_THREADS / 32;
 #ifndef AP_S1_CTAS
 #define AP_S1_CTAS 6  // resident stage-1 CTAs per SM the register budget is compiled for (K = 32, fp32 keys)
 #endif
+#ifndef AP_S1_CTAS_F64
+#define AP_S1_CTAS_F64 4  // the same for fp64 keys (64 key registers per thread): 255 registers and 2 CTAs/SM when left to the compiler
+#endif
 #ifndef AP_DYNAMIC
 #define AP_DYNAMIC 1  // 1 = stage-1 CTAs / stage-2 warps draw stars from an atomic counter; 0 = static grid stride
 #endif
@@ -635,7 +638,7 @@ BP_D void sort_index(const AperParams& P, const T (&r)[K], const T* __restrict__
 
 // K > 0: register sort of 128*K keys (P.sort_cap == 128*K).  K == 0: shared-memory sort of P.sort_cap keys.
 template <typename T, int K>
-__global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S1_CTAS : 1) aper_stage1_kernel(const AperParams P) {
+__global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S1_CTAS : (K == 32 ? AP_S1_CTAS_F64 : 1)) aper_stage1_kernel(const AperParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* keys = reinterpret_cast<T*>(smem_raw);
     const size_t key_bytes = ((size_t)(K > 0 ? AP_THREADS * (K + 1) : P.sort_cap) * sizeof(T) + 15) & ~(size_t)15;

@@ -537,8 +537,15 @@ int bphot_aper_device_banded(const void* d_image, int image_dtype, int nrow, int
     P.sidx = indexed ? (void*)(reinterpret_cast<char*>(scratch) + keys_bytes) : nullptr;
     // one zeroed work counter per stage-1 / retry / stage-2 launch
     int* counters = nullptr;
-    CU_TRY(cudaMallocAsync((void**)&counters, (size_t)(3 * nbatch + 2) * sizeof(int), st));
-    CU_TRY(cudaMemsetAsync(counters, 0, (size_t)(3 * nbatch + 2) * sizeof(int), st));
+    {   // a failure here must not leak the scratch block that is already allocated
+        cudaError_t e = cudaMallocAsync((void**)&counters, (size_t)(3 * nbatch + 2) * sizeof(int), st);
+        if (e == cudaSuccess) e = cudaMemsetAsync(counters, 0, (size_t)(3 * nbatch + 2) * sizeof(int), st);
+        if (e != cudaSuccess) {
+            if (counters) cudaFreeAsync(counters, st);
+            if (scratch) cudaFreeAsync(scratch, st);
+            return fail(BPHOT_ERR_CUDA, "bphot_aper: work counters: %s", cudaGetErrorString(e));
+        }
+    }
     int* next_counter = counters;
     StarOrder ord;
     rc = make_star_order(d_xc, d_yc, nstars, nrow, ncol, st, &ord);
