@@ -578,14 +578,13 @@ def main():
                 # several GPUs: the exposure crosses PCIe once, on rank 0, and reaches the other GPUs over NVLink
                 # (shard.broadcast_exposure); every rank then calls the public API on its own shard of
                 # the star list with HOST star columns and gets HOST results back
+                # band by band: rank 0's upload of band k, its NCCL broadcast, and the kernels that only need rows up to band k
+                # overlap on every rank (shard.distribute_exposure)
+                hdr = {"shape": shape, "image_dtype": str(tdt), "noise_dtype": str(tdt) if do_fit else None, "has_mask": bool(do_fit)}
+                im_a, nz_a, mk_a = shard.distribute_exposure([np_img, np_noise if do_fit else None, np_mask if do_fit else None],
+                                                             header=hdr, src=0, device=dev)
                 if rank == 0:
-                    ex = [_lib.to_device_image(np_img, dev), _lib.to_device_image(np_noise, dev) if do_fit else None,
-                          _lib.to_device_mask(np_mask, dev) if do_fit else None]
                     h2d += np_img.nbytes + (np_noise.nbytes + np_mask.nbytes if do_fit else 0)
-                else:
-                    ex = [torch.empty_like(img_t), torch.empty_like(noise_t) if do_fit else None,
-                          torch.empty_like(mask_t) if do_fit else None]
-                im_a, nz_a, mk_a = shard.broadcast_exposure(ex, src=0)
             else:
                 im_a, nz_a, mk_a = np_img, np_noise, np_mask
                 h2d += np_img.nbytes + (np_noise.nbytes + np_mask.nbytes if do_fit else 0)
@@ -625,8 +624,9 @@ def main():
                "path": ("pk = pkfit_class(numpy image, noise, mask) [one upload of each, on a copy stream]; "
                         "aper.aper(pk.image_device(), numpy x, y) -> numpy results; pk.pkfit_norecent_noise(numpy lists) -> numpy results"
                         if world == 1 else
-                        "rank 0 uploads the exposure and NCCL-broadcasts it; every rank calls pkfit_class + aper.aper + "
-                        "pkfit_norecent_noise on its shard with numpy star columns, numpy results; byte counts are rank 0's")}
+                        "rank 0 uploads the exposure in row bands and NCCL-broadcasts each band as it lands (shard.distribute_exposure); "
+                        "every rank calls pkfit_class + aper.aper + pkfit_norecent_noise on its shard with numpy star columns, numpy "
+                        "results, its kernels starting on the bands already there; byte counts are rank 0's")}
 
     # ---- config 5 (N > 1): the multi-GPU configuration north_star names, strong scaling
     c5 = None

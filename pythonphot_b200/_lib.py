@@ -170,20 +170,9 @@ class DeviceImage(object):
 BAND_MIN_BYTES = 32 << 20  # smaller images go up in one piece
 
 
-def upload_image_banded(a, device, nbands=16):
-    """Host array -> ``DeviceImage`` uploaded in ``nbands`` row bands on the copy stream (asynchronous when ``a`` is
-    page-locked).  Small images and CUDA tensors come back as a plain, already ordered ``DeviceImage``."""
+def _upload_banded(a, device, nbands):
+    """2-D contiguous host array -> DeviceImage, ``nbands`` row bands on the copy stream, one event per band."""
     torch = torch_cuda()
-    if isinstance(a, DeviceImage):
-        return a
-    if isinstance(a, torch.Tensor) or np.asarray(a).nbytes < BAND_MIN_BYTES:
-        return DeviceImage(to_device_image(a, device))
-    a = np.asarray(a)
-    if a.dtype != np.float32:
-        a = a.astype(np.float64, copy=False)
-    a = np.ascontiguousarray(a)
-    if a.ndim != 2:
-        raise BphotError("image must be 2-D, got shape %s" % (a.shape,))
     host = torch.from_numpy(a)
     cur, up = torch.cuda.current_stream(device), copy_stream(device)
     t = torch.empty(a.shape, dtype=host.dtype, device=device)
@@ -198,6 +187,37 @@ def upload_image_banded(a, device, nbands=16):
             events.append(ev)
     t.record_stream(up)
     return DeviceImage(t, events, rows)
+
+
+def upload_image_banded(a, device, nbands=16, min_bytes=BAND_MIN_BYTES):
+    """Host array -> ``DeviceImage`` uploaded in ``nbands`` row bands on the copy stream (asynchronous when ``a`` is
+    page-locked).  Small images and CUDA tensors come back as a plain, already ordered ``DeviceImage``."""
+    torch = torch_cuda()
+    if isinstance(a, DeviceImage):
+        return a
+    if isinstance(a, torch.Tensor) or np.asarray(a).nbytes < max(min_bytes, 1):
+        return DeviceImage(to_device_image(a, device))
+    a = np.asarray(a)
+    if a.dtype != np.float32:
+        a = a.astype(np.float64, copy=False)
+    a = np.ascontiguousarray(a)
+    if a.ndim != 2:
+        raise BphotError("image must be 2-D, got shape %s" % (a.shape,))
+    return _upload_banded(a, device, nbands)
+
+
+def upload_mask_banded(a, device, nbands=16, min_bytes=BAND_MIN_BYTES):
+    """The same for a mask image: uint8 / bool host masks go up in bands as they are, anything else through
+    ``to_device_mask`` (reduced to 0/1 on the device)."""
+    torch = torch_cuda()
+    if isinstance(a, DeviceImage):
+        return a
+    if isinstance(a, torch.Tensor) or np.asarray(a).dtype not in (np.uint8, np.bool_) or np.asarray(a).nbytes < max(min_bytes, 1):
+        return DeviceImage(to_device_mask(a, device))
+    a = np.ascontiguousarray(np.asarray(a).view(np.uint8))
+    if a.ndim != 2:
+        raise BphotError("mask must be 2-D, got shape %s" % (a.shape,))
+    return _upload_banded(a, device, nbands)
 
 
 def dtype_code(t):

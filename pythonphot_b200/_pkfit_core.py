@@ -12,6 +12,8 @@ class PkfitEngine(object):
 
     def __init__(self, image, gauss, psf, ronois, phpadu, noiseim=None, maskim=None, device=None):
         torch = _lib.torch_cuda()
+        if device is None and isinstance(image, _lib.DeviceImage):
+            device = image.device
         if device is None and isinstance(image, torch.Tensor) and image.is_cuda:
             device = image.device
         self.device = _lib.device_of(device)
@@ -22,27 +24,16 @@ class PkfitEngine(object):
         self.fmask = maskim
         self.ronois = ronois
         self.phpadu = phpadu
-        # Host arrays go up on a copy stream of their own, image first: the constructor returns while the copies run
-        # (when the arrays are page-locked), ``image_device()`` waits for the image only, the fits for all three -- so
-        # work queued in between, e.g. ``aper.aper(pk.image_device(), ...)``, overlaps the noise and mask uploads.
-        host_in = any(a is not None and not isinstance(a, (torch.Tensor, _lib.DeviceImage)) for a in (image, noiseim, maskim))
-        self._ev_all = None
-        self._dimg = _lib.upload_image_banded(image, self.device)  # banded, on the copy stream, when it is a large host array
+        # Large host arrays go up in row bands on a copy stream of their own, image first: the constructor returns while
+        # the copies run (when the arrays are page-locked), ``image_device()`` hands out the image with its band events,
+        # the fits wait for all three -- so work queued in between, e.g. ``aper.aper(pk.image_device(), ...)``, overlaps the
+        # noise and mask uploads.  ``DeviceImage`` arguments (e.g. from ``shard.distribute_exposure``) are taken as they are.
+        self._dimg = _lib.upload_image_banded(image, self.device)
+        self._dnoise = _lib.upload_image_banded(noiseim, self.device) if noiseim is not None else None
+        self._dmask = _lib.upload_mask_banded(maskim, self.device) if maskim is not None else None
         self._img_t = self._dimg.tensor
-        if host_in:
-            cur, up = torch.cuda.current_stream(self.device), _lib.copy_stream(self.device)
-            up.wait_stream(cur)
-            with torch.cuda.stream(up):
-                self._noise_t = _lib.to_device_image(noiseim, self.device) if noiseim is not None else None
-                self._mask_t = _lib.to_device_mask(maskim, self.device) if maskim is not None else None
-                self._ev_all = torch.cuda.Event()
-                self._ev_all.record(up)
-            for t in (self._noise_t, self._mask_t):
-                if t is not None:
-                    t.record_stream(cur)
-        else:
-            self._noise_t = _lib.to_device_image(noiseim, self.device) if noiseim is not None else None
-            self._mask_t = _lib.to_device_mask(maskim, self.device) if maskim is not None else None
+        self._noise_t = self._dnoise.tensor if self._dnoise is not None else None
+        self._mask_t = self._dmask.tensor if self._dmask is not None else None
         for name, t in (("noise", self._noise_t), ("mask", self._mask_t)):
             if t is not None and tuple(t.shape) != tuple(self._img_t.shape):
                 raise ValueError("%s image shape %s differs from image shape %s" % (name, tuple(t.shape), tuple(self._img_t.shape)))
@@ -63,10 +54,9 @@ class PkfitEngine(object):
         return self._dimg
 
     def _uploads_done(self):
-        self._dimg.ready()
-        if self._ev_all is not None:
-            torch = _lib.torch_cuda()
-            torch.cuda.current_stream(self.device).wait_event(self._ev_all)
+        for d in (self._dimg, self._dnoise, self._dmask):
+            if d is not None:
+                d.ready()
 
     def fit_device(self, variant, scale_t, x_t, y_t, sky_t, radius, maxiter=25, recenter=True, out=None):
         """All star columns are fp64 CUDA vectors of equal length; returns a dict of CUDA tensors

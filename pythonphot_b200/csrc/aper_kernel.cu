@@ -27,7 +27,7 @@ constexpr int AP_WARPS = AP_THREADS / 32;
 #define AP_S1_CTAS 6  // resident stage-1 CTAs per SM the register budget is compiled for (K = 32, fp32 keys)
 #endif
 #ifndef AP_S1_CTAS_F64
-#define AP_S1_CTAS_F64 4  // the same for fp64 keys (64 key registers per thread): 255 registers and 2 CTAs/SM when left to the compiler
+#define AP_S1_CTAS_F64 1  // fp64 keys: measured 220 ms per 1 M stars at 255 registers (1), 250 at 3 CTAs, 260 at 4 -- not occupancy-bound
 #endif
 #ifndef AP_DYNAMIC
 #define AP_DYNAMIC 1  // 1 = stage-1 CTAs / stage-2 warps draw stars from an atomic counter; 0 = static grid stride

@@ -85,8 +85,19 @@ BP_D FitBox fit_box(const PkfitParams& P, double x, double y) {
 
 // Column and row factors of the integrated Gaussian for the whole box (daoerf.py:49-72): lanes
 // 0..ixx-1 take the columns, the next iyy lanes the rows.  AX = [FX | EX | FY | EY], each `acap` long.
-BP_D void fill_axes(const FitBox& b, double x, double y, const double* gauss, double* AX, int acap, int lane) {
+// Returns, for lane i < ixx + iyy <= 32, the lane's term of rho = dx^2/sigx^2 + dy^2/sigy^2 (pkfit.py:292): column i's
+// dx^2/sigx^2 or row (i - ixx)'s dy^2/sigy^2 -- the same operations on the same operands as the per-pixel expression, taken once per
+// column and row; pixels fetch the two terms by shuffle.
+BP_D double fill_axes(const FitBox& b, double x, double y, const double* gauss, double* AX, int acap, int lane) {
     const int nitem = b.ixx + b.iyy;
+    double qv = 0.;
+    if (lane < nitem && nitem <= 32) {
+        const bool col = lane < b.ixx;
+        const int k = col ? lane : lane - b.ixx;
+        const double d = col ? (double)(k + b.ixlo) - x : (double)(k + b.iylo) - y;
+        const double s = col ? gauss[3] : gauss[4];
+        qv = d * d / (s * s);
+    }
     for (int i = lane; i < nitem; i += 32) {
         const bool col = i < b.ixx;
         const int k = col ? i : i - b.ixx;
@@ -98,6 +109,7 @@ BP_D void fill_axes(const FitBox& b, double x, double y, const double* gauss, do
         dst[k] = f;
         dst[acap + k] = e;
     }
+    return qv;
 }
 
 // dao_value.py:95-107 for the pixel in column c, row r of the box (offsets dxv, dyv from the star).
@@ -432,33 +444,41 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
         if (!isfinite(S.x) || !isfinite(S.y)) return fit_nan(S, false, false);
         const double scl = S.scale, chiold = S.chiold;
         const FitBox b = fit_box(P, S.x, S.y);
-        fill_axes(b, S.x, S.y, gauss, AX, acap, lane);
+        const double qaxis = fill_axes(b, S.x, S.y, gauss, AX, acap, lane);
+        const bool qsep = b.ixx + b.iyy <= 32;  // warp-uniform: the rho terms of every column and row sit in one lane each
 
         // ---- pass A: ordered list of good pixels (pkfit.py:184-219, pkfit_noise.py:206-208)
         int ngood = 0;
         double xmin = KeyTraits<double>::inf(), xmax = -KeyTraits<double>::inf(), ymin = xmin, ymax = xmax;
+        // box position of this lane's pixel, advanced by 32 per pass without a division
+        const int ixd = b.ixx > 0 ? b.ixx : 1, krow = 32 / ixd, kcol = 32 - krow * ixd;
+        int r = lane / ixd, c = lane - r * ixd;
         for (int base = 0; base < b.npix; base += 32) {
             const int p = base + lane;
+            const bool in = p < b.npix;
             bool ok = false;
-            int r = 0, c = 0;
             double dxv = 0., dyv = 0., rsq = 0., rho = 0., fv = 0., nz = 0.;
-            if (p < b.npix) {
-                r = p / b.ixx;
-                c = p - r * b.ixx;
+            // rho's two terms come from the lanes that own column c and row r (all lanes take part in the shuffles)
+            const double qx = __shfl_sync(FULL, qaxis, (in && qsep) ? c : 0), qy = __shfl_sync(FULL, qaxis, (in && qsep) ? b.ixx + r : 0);
+            if (in) {
                 dyv = (double)(r + b.iylo) - S.y;
                 dxv = (double)(c + b.ixlo) - S.x;
                 const double dysq = dyv * dyv, dxsq = dxv * dxv;
                 rsq = (dxsq + dysq) / radsq;
                 ok = rsq < 1.;
                 if (ok) {
+                    // the three loads are independent: one memory round trip, not three
                     const size_t row = (size_t)(b.iylo + r), col = (size_t)(b.ixlo + c);
+                    const TI fraw = img[row * P.pitch + col];
                     if (!ANALYTIC) {
-                        nz = (double)noise[row * P.npitch + col];
-                        ok = (nz > 0) && (mask[row * P.mpitch + col] == 0);
+                        const TN nraw = noise[row * P.npitch + col];
+                        const uint8_t mraw = mask[row * P.mpitch + col];
+                        nz = (double)nraw;
+                        ok = (nz > 0) && (mraw == 0);
                     }
                     if (ok) {
-                        fv = (double)img[row * P.pitch + col];
-                        rho = dxsq / gx2 + dysq / gy2;  // pkfit.py:292
+                        fv = (double)fraw;
+                        rho = qsep ? qx + qy : dxsq / gx2 + dysq / gy2;  // pkfit.py:292
                     }
                 }
             }
@@ -474,6 +494,8 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
                 }
             }
             ngood += __popc(mk);
+            r += krow; c += kcol;
+            if (c >= ixd) { c -= ixd; r++; }
         }
         if (ngood > cap) ngood = cap;
         if (ngood == 0) return fit_nan(S, false, false);  // pkfit.py:211-219
@@ -483,7 +505,9 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
         ymin = 2. * pk_min(ymin) + half; ymax = 2. * pk_max(ymax) + half;
         const bool guard = (xmin < 1.) || (xmax > npsf - 2.) || (ymin < 1.) || (ymax > npsf - 2.);
 
-        // ---- pass B: model, residuals (pkfit.py:224-283)
+        // ---- pass B: model, residuals (pkfit.py:224-283); the 10-sigma test of pkfit.py:296-300 is taken here, where the
+        // residual is at hand: the flag travels in bit 30 of GIDX (box rows stay below 2^14: radius < 64)
+        int nbad = 0;
         for (int q = lane; q < ngood; q += 32) {
             double mval = 0., dvx = 0., dvy = 0.;
             if (!guard) {
@@ -504,7 +528,9 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
                 SIG[q] = sqrt(s2);
             }
             DF[q] = df;
-            REL[q] = df / SIG[q];
+            const double rel = df / SIG[q];
+            REL[q] = rel;
+            if (S.niter >= 2 && fabs(rel / chiold) >= 10.) { nbad++; GIDX[q] |= 0x40000000; }
         }
         __syncwarp();
 
@@ -512,9 +538,6 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
         int m = ngood;
         bool compacted = false;
         if (S.niter >= 2) {
-            int nbad = 0;
-            for (int q = lane; q < ngood; q += 32)
-                if (fabs(REL[q] / chiold) >= 10.) nbad++;
             nbad = warp_sum_int(nbad);
             // pkfit.py:303-309; pkfit_norecenter.py:509 takes this return only when more than one pixel is rejected
             if (nbad == ngood && !(V == 3 && nbad <= 1)) return fit_nan(S, true, true);
@@ -527,7 +550,7 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
                     double a0 = 0., a1 = 0., a2 = 0., a3 = 0., a4 = 0., a5 = 0., a6 = 0.;
                     if (q < ngood) {
                         a0 = REL[q];
-                        keep = !(fabs(a0 / chiold) >= 10.);
+                        keep = !(GIDX[q] & 0x40000000);
                         a1 = DF[q]; a2 = RSQ[q]; a3 = RHO[q]; a4 = FSUB[q]; a5 = SIG[q]; a6 = SIGSQ[q];
                     }
                     const unsigned mk = __ballot_sync(FULL, keep);

@@ -285,6 +285,71 @@ def broadcast_exposure(tensors, src=0, group=None):
     return tensors
 
 
+def distribute_exposure(arrays, header=None, src=0, group=None, device=None, nbands=16):
+    """Host exposure on ``src`` -> one ``_lib.DeviceImage`` per array on EVERY rank, pipelined band by band: ``src`` uploads
+    band k on its copy stream, the NCCL broadcast of band k follows on a communication stream as soon as that band is
+    resident, and the event of band k fires on each rank when ITS copy of rows [0, (k+1)*band_rows) is complete -- so
+    ``aper.aper(DeviceImage, ...)`` starts on every GPU while the rest of the exposure is still crossing PCIe and NVLink.
+
+    ``arrays`` = [image, noise, mask] (host arrays or CUDA tensors; entries may be None) on ``src``, anything elsewhere;
+    ``header`` = ``exposure_header``-style dict known on every rank (else ``src`` broadcasts it first: a host-synchronous
+    object broadcast).  The arrays are sent one after the other, so a later one's events imply the earlier ones.
+    Returns [image, noise, mask] as ``DeviceImage`` (None where the source has none)."""
+    from . import _lib
+    torch = _lib.torch_cuda()
+    dist = _dist()
+    rank, world = world_info(group)
+    dev = _lib.device_of(device)
+    ups = [None, None, None]
+    if rank == src:
+        ups[0] = _lib.upload_image_banded(arrays[0], dev, nbands=nbands, min_bytes=0)
+        ups[1] = _lib.upload_image_banded(arrays[1], dev, nbands=nbands, min_bytes=0) if arrays[1] is not None else None
+        ups[2] = _lib.upload_mask_banded(arrays[2], dev, nbands=nbands, min_bytes=0) if arrays[2] is not None else None
+    if header is None:
+        header = broadcast_header(exposure_header(*[u.tensor if u is not None else None for u in ups]) if rank == src else None,
+                                  src=src, group=group)
+    if world == 1:
+        return ups
+    dts = {"torch.float32": torch.float32, "torch.float64": torch.float64}
+    shape = tuple(header["shape"])
+    kinds = [dts[header["image_dtype"]], dts[header["noise_dtype"]] if header["noise_dtype"] else None,
+             torch.uint8 if header["has_mask"] else None]
+    rows = (shape[0] + nbands - 1) // nbands
+    cur, comm = torch.cuda.current_stream(dev), _comm_stream(dev)
+    comm.wait_stream(cur)
+    out = []
+    for up, dt in zip(ups, kinds):
+        if dt is None:
+            out.append(None)
+            continue
+        t = up.tensor if up is not None else torch.empty(shape, dtype=dt, device=dev)
+        events = []
+        with torch.cuda.stream(comm):
+            for k, r0 in enumerate(range(0, shape[0], rows)):
+                if up is not None and up.events:
+                    comm.wait_event(up.events[min(k, len(up.events) - 1)])
+                elif up is not None and k == 0:
+                    comm.wait_stream(cur)  # a source tensor that was produced on the caller's stream
+                dist.broadcast(t[r0:r0 + rows], src=src, group=group)
+                ev = torch.cuda.Event()
+                ev.record(comm)
+                events.append(ev)
+        t.record_stream(comm)
+        out.append(_lib.DeviceImage(t, events, rows))
+    return out
+
+
+_comm_streams = {}
+
+
+def _comm_stream(device):
+    import torch
+    key = str(device)
+    if key not in _comm_streams:
+        _comm_streams[key] = torch.cuda.Stream(device=device)
+    return _comm_streams[key]
+
+
 def broadcast_columns(columns, n, device, src=0, group=None):
     """Star-list columns (fp64) known on ``src`` -> a ``[ncol, n]`` fp64 tensor on every rank."""
     import torch

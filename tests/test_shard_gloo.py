@@ -179,3 +179,51 @@ def test_sharded_two_gpus_bit_identical_to_one(tmp_path):
     want = _single_gpu_reference()
     for r in range(2):
         _assert_bitwise(torch.load(os.path.join(str(tmp_path), "g%d.pt" % r)), want)
+
+
+def _gpu_worker_banded(rank, world, port, out_dir):
+    """Exposure distributed band by band (upload on rank 0 + NCCL broadcast per band), consumed through DeviceImage."""
+    import torch.distributed as dist
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world,
+                            device_id=torch.device("cuda", rank))
+    try:
+        import pythonphot_b200 as pp
+        from pythonphot_b200 import synth
+        f = synth.make_field(768, 768, 3000, seed=11, dtype=np.float32)
+        n = f["x"].size
+        arrays = [f["image"], f["noise"], f["mask"]] if rank == 0 else [None, None, None]
+        dimg, dnz, dmk = shard.distribute_exposure(arrays, src=0, nbands=7)
+        assert len(dimg.events) == 7 and dmk.tensor.dtype == torch.uint8
+        pk = pp.pkfit_class(dimg, f["gauss"], f["psf"], f["ronois"], f["phpadu"], dnz, dmk)
+        a = pp.aper.aper(pk.image_device(), f["x"], f["y"], phpadu=f["phpadu"], apr=np.array([3., 5., 8.]), skyrad=[40, 50],
+                         badpix=[-12000, 60000], exact=True, verbose=False)
+        p = pk.pkfit_noise(np.ones(n), f["xfit"], f["yfit"], a[4], 5.0, xyout=True)
+        torch.save({"aper": [np.asarray(v) for v in a[:7]], "fit": [np.asarray(v) for v in p]}, os.path.join(out_dir, "b%d.pt" % rank))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_banded_exposure_distribution_two_gpus(tmp_path):
+    """Every rank computes the full star list on ITS copy of the exposure, received band by band: all copies must give what
+    the plain single-GPU call on host arrays gives, bit for bit."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run under gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+    import pythonphot_b200 as pp
+    from pythonphot_b200 import synth
+    port = _free_port()
+    mp.spawn(_gpu_worker_banded, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    f = synth.make_field(768, 768, 3000, seed=11, dtype=np.float32)
+    n = f["x"].size
+    a = pp.aper.aper(f["image"], f["x"], f["y"], phpadu=f["phpadu"], apr=np.array([3., 5., 8.]), skyrad=[40, 50],
+                     badpix=[-12000, 60000], exact=True, verbose=False)
+    pk = pp.pkfit_class(f["image"], f["gauss"], f["psf"], f["ronois"], f["phpadu"], f["noise"], f["mask"])
+    p = pk.pkfit_noise(np.ones(n), f["xfit"], f["yfit"], a[4], 5.0, xyout=True)
+    for r in range(2):
+        got = torch.load(os.path.join(str(tmp_path), "b%d.pt" % r), weights_only=False)
+        for u, v in zip(got["aper"], a[:7]):
+            assert np.array_equal(np.nan_to_num(u, nan=-1.0), np.nan_to_num(np.asarray(v), nan=-1.0))
+        for u, v in zip(got["fit"], p):
+            assert np.array_equal(np.nan_to_num(u, nan=-1.0), np.nan_to_num(np.asarray(v), nan=-1.0))
