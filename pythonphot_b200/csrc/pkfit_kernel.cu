@@ -452,23 +452,23 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
         double xmin = KeyTraits<double>::inf(), xmax = -KeyTraits<double>::inf(), ymin = xmin, ymax = xmax;
         // box position of this lane's pixel, advanced by 32 per pass without a division
         const int ixd = b.ixx > 0 ? b.ixx : 1, krow = 32 / ixd, kcol = 32 - krow * ixd;
-        int r = lane / ixd, c = lane - r * ixd;
+        int pr = lane / ixd, pc = lane - pr * ixd;
         for (int base = 0; base < b.npix; base += 32) {
             const int p = base + lane;
             const bool in = p < b.npix;
             bool ok = false;
             double dxv = 0., dyv = 0., rsq = 0., rho = 0., fv = 0., nz = 0.;
             // rho's two terms come from the lanes that own column c and row r (all lanes take part in the shuffles)
-            const double qx = __shfl_sync(FULL, qaxis, (in && qsep) ? c : 0), qy = __shfl_sync(FULL, qaxis, (in && qsep) ? b.ixx + r : 0);
+            const double qx = __shfl_sync(FULL, qaxis, (in && qsep) ? pc : 0), qy = __shfl_sync(FULL, qaxis, (in && qsep) ? b.ixx + pr : 0);
             if (in) {
-                dyv = (double)(r + b.iylo) - S.y;
-                dxv = (double)(c + b.ixlo) - S.x;
+                dyv = (double)(pr + b.iylo) - S.y;
+                dxv = (double)(pc + b.ixlo) - S.x;
                 const double dysq = dyv * dyv, dxsq = dxv * dxv;
                 rsq = (dxsq + dysq) / radsq;
                 ok = rsq < 1.;
                 if (ok) {
                     // the three loads are independent: one memory round trip, not three
-                    const size_t row = (size_t)(b.iylo + r), col = (size_t)(b.ixlo + c);
+                    const size_t row = (size_t)(b.iylo + pr), col = (size_t)(b.ixlo + pc);
                     const TI fraw = img[row * P.pitch + col];
                     if (!ANALYTIC) {
                         const TN nraw = noise[row * P.npitch + col];
@@ -487,15 +487,15 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
                 const int q = ngood + __popc(mk & lt);
                 if (q < cap) {
                     DX[q] = dxv; DY[q] = dyv; RSQ[q] = rsq; RHO[q] = rho; FSUB[q] = fv;
-                    GIDX[q] = r * 65536 + c;
+                    GIDX[q] = pr * 65536 + pc;
                     if (!ANALYTIC) { SIG[q] = nz; SIGSQ[q] = nz * nz; }
                     xmin = fmin(xmin, dxv); xmax = fmax(xmax, dxv);
                     ymin = fmin(ymin, dyv); ymax = fmax(ymax, dyv);
                 }
             }
             ngood += __popc(mk);
-            r += krow; c += kcol;
-            if (c >= ixd) { c -= ixd; r++; }
+            pr += krow; pc += kcol;
+            if (pc >= ixd) { pc -= ixd; pr++; }
         }
         if (ngood > cap) ngood = cap;
         if (ngood == 0) return fit_nan(S, false, false);  // pkfit.py:211-219
