@@ -29,6 +29,9 @@ constexpr int AP_WARPS = AP_THREADS / 32;
 #ifndef AP_S1_CTAS_F64
 #define AP_S1_CTAS_F64 1  // fp64 keys: measured 220 ms per 1 M stars at 255 registers (1), 250 at 3 CTAs, 260 at 4 -- not occupancy-bound
 #endif
+#ifndef AP_GATHER_U
+#define AP_GATHER_U 4
+#endif
 #ifndef AP_DYNAMIC
 #define AP_DYNAMIC 1  // 1 = stage-1 CTAs / stage-2 warps draw stars from an atomic counter; 0 = static grid stride
 #endif
@@ -384,7 +387,7 @@ BP_D int2 gather_rows(const AperParams& P, const T* __restrict__ stamp, const St
     int nrej = 0, nnan = 0;
     const bool window = P.badlo != P.badhi;
     const int nw = (int)(blockDim.x >> 5);  // 4 warps, or 3 when the annulus fits 96 threads x K keys
-    constexpr int U = 4;  // rows in flight per warp: U independent loads per lane before the first use
+    constexpr int U = AP_GATHER_U;  // rows in flight per warp: U independent loads per lane before the first use
     for (int r0 = warp; r0 < g.ny; r0 += U * nw) {
         int a0[U], nl[U], skip[U], tot[U], off[U];
         const T* __restrict__ row[U];
