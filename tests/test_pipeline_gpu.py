@@ -54,3 +54,29 @@ def test_aper_banded_upload_equals_resident_image(pinned):
     b = pk2.pkfit_norecent_noise(np.ones(n), f["xfit"][:n], f["yfit"][:n], np.full(n, f["sky"]), 5.0)
     for u, v in zip(a, b):
         assert np.array_equal(np.nan_to_num(u, nan=-1.0), np.nan_to_num(v, nan=-1.0))
+
+
+@pytest.mark.gpu
+def test_fetch_host_reads_page_locked_memory_and_refuses_pageable():
+    """bphot_fetch_host: a kernel copies a page-locked host buffer (any length, any alignment of the tail) into device memory
+    without using the copy engine; pageable memory is refused so that the caller falls back to cudaMemcpyAsync."""
+    import ctypes as C
+    import torch
+    from pythonphot_b200 import _lib
+    lib = _lib.lib()
+    for n in (1, 17, 4096, 1000003):
+        h = torch.arange(n, dtype=torch.float64).pin_memory()
+        d = torch.empty(n, dtype=torch.float64, device="cuda")
+        rc = lib.bphot_fetch_host(_lib.ptr(d), C.c_void_p(h.data_ptr()), n * 8, _lib.stream_ptr(d.device))
+        assert rc == 0 and torch.equal(d.cpu(), h)
+    hb = torch.arange(1003, dtype=torch.uint8).pin_memory()
+    db = torch.zeros(1003, dtype=torch.uint8, device="cuda")
+    assert lib.bphot_fetch_host(C.c_void_p(db.data_ptr() + 1), C.c_void_p(hb.data_ptr() + 1), 1001, _lib.stream_ptr(db.device)) == 0
+    assert torch.equal(db.cpu()[1:1002], hb[1:1002]) and int(db[0]) == 0 and int(db[1002]) == 0
+    pageable = np.arange(5000, dtype=np.float64)
+    d = torch.empty(5000, dtype=torch.float64, device="cuda")
+    assert lib.bphot_fetch_host(_lib.ptr(d), pageable.ctypes.data_as(C.c_void_p), 40000, _lib.stream_ptr(d.device)) == -1
+    # the column helper takes either kind
+    assert torch.equal(_lib.to_device_f64(pageable, d.device).cpu(), torch.from_numpy(pageable))
+    pinned = torch.from_numpy(pageable).pin_memory().numpy()
+    assert torch.equal(_lib.to_device_f64(pinned, d.device).cpu(), torch.from_numpy(pageable))
