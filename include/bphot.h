@@ -69,6 +69,9 @@ long long bphot_launch_count(void);
  * not page-locked (the caller falls back to cudaMemcpyAsync).
  */
 int bphot_fetch_host(void* d_dst, const void* h_src, long long nbytes, void* stream);
+/* slots of the per-star pixel list the fit kernels allocate for this fitting radius: a rigorous upper bound on the number
+ * of pixel centres strictly inside a disc of that radius, for any centre (tests/test_abi_cpu.py checks it against brute force) */
+int bphot_pkfit_capacity(double radius);
 int bphot_profile(int enable);
 int bphot_kernel_times(double* ms, long long* launches);
 

@@ -30,6 +30,7 @@ _SIGNATURES = {
     "bphot_device_count": (C.c_int, []),
     "bphot_launch_count": (C.c_longlong, []),
     "bphot_fetch_host": (C.c_int, [_vp, _vp, _ll, _vp]),
+    "bphot_pkfit_capacity": (C.c_int, [_d]),
     "bphot_profile": (C.c_int, [_i]),
     "bphot_kernel_times": (C.c_int, [_vp, _vp]),
     "bphot_aper_device": (C.c_int, [_vp, _i, _i, _i, _ll, _vp, _vp, _i, _d, _vp, _i, _d, _d, _d, _d, _d, _i, _vp, _i, _i,

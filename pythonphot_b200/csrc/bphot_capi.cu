@@ -421,6 +421,11 @@ int bphot_fetch_host(void* d_dst, const void* h_src, long long nbytes, void* str
     return BPHOT_OK;
 }
 
+int bphot_pkfit_capacity(double radius) {
+    if (!(radius > 0.) || !(radius < 64.)) return fail(BPHOT_ERR_ARG, "bphot_pkfit_capacity: radius %g outside (0, 64)", radius);
+    return (disc_lattice_bound(radius) + 7) / 8 * 8;
+}
+
 int bphot_profile(int enable) {
     const int prev = g_profile.exchange(enable ? 1 : 0);
     if (enable) for (int k = 0; k < KT_N; k++) { g_kt_ms[k] = 0.; g_kt_n[k] = 0; }

@@ -67,3 +67,21 @@ def test_product_package_does_not_import_oracle():
             if fn.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, fn)).read()
                 assert "oracle" not in src.replace("# oracle", ""), "%s mentions the oracle" % fn
+
+
+def test_pixel_list_capacity_bounds_every_disc(lib):
+    """The fit kernels size their per-warp pixel lists from bphot_pkfit_capacity(radius); a list that is too short would
+    silently drop pixels.  Brute force over 40 000 random disc centres per radius: never more pixels than the bound, and
+    the bound is tight (within 12 of the observed maximum, 8 of which is rounding to a multiple of 8)."""
+    h = lib.lib()
+    rng = np.random.default_rng(0)
+    for radius in (0.7, 1.0, 2.2, 3.0, 4.0, 5.0, 7.5, 11.0):
+        cap = h.bphot_pkfit_capacity(float(radius))
+        R = int(np.ceil(radius)) + 1
+        g = np.arange(-R, R + 2, dtype=np.float64)
+        fx, fy = rng.uniform(0, 1, 40000), rng.uniform(0, 1, 40000)
+        fx[:4], fy[:4] = [0.0, 0.5, 0.0, 0.5], [0.0, 0.0, 0.5, 0.5]
+        d2 = (g[None, :, None] - fx[:, None, None]) ** 2 + (g[None, None, :] - fy[:, None, None]) ** 2
+        worst = int((d2 < radius * radius).sum(axis=(1, 2)).max())
+        assert worst <= cap <= worst + 12, (radius, worst, cap)
+    assert h.bphot_pkfit_capacity(0.0) == -1 and h.bphot_pkfit_capacity(64.0) == -1
