@@ -108,14 +108,14 @@ struct DevInfo {
 int dev_info(DevInfo* d) {
     int dev = 0;
     CU_TRY(cudaGetDevice(&dev));
-    {   // keep up to 2 GiB of freed stream-ordered scratch (sorted-annulus rows, find's h image) in the device's default
+    {   // keep up to 8 GiB of freed stream-ordered scratch (sorted-annulus rows, find's h image) in the device's default
         // pool across synchronisations: with the default threshold of 0 every call re-maps ~0.7 GB from the driver (~15 ms)
         static std::atomic<unsigned long long> tuned{0};
         const unsigned long long bit = 1ull << (dev & 63);
         if (!(tuned.load() & bit)) {
             cudaMemPool_t pool;
             if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
-                unsigned long long keep = 2ull << 30;
+                unsigned long long keep = 8ull << 30;
                 cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
             }
             cudaGetLastError();
