@@ -92,6 +92,17 @@ class ShardPlan(object):
             self._dev[key] = torch.from_numpy(np.ascontiguousarray(idx)).to(device)
         return self._dev[key]
 
+    def _flat_index(self, es, k, nbytes, device):
+        """int64 [n * k]: where component j of star s sits in the gathered [world, nbytes] buffer viewed as elements of
+        ``es`` bytes, relative to the start of its column (cached per element size, width and arena size)."""
+        import torch
+        key = ("flat", es, k, nbytes, str(device))
+        if key not in self._dev:
+            base = (self.inverse // max(self.m, 1)) * (nbytes // es) + (self.inverse % max(self.m, 1)) * k
+            idx = base if k == 1 else (base[:, None] + np.arange(k, dtype=np.int64)[None, :]).reshape(-1)
+            self._dev[key] = torch.from_numpy(np.ascontiguousarray(idx)).to(device)
+        return self._dev[key]
+
     @classmethod
     def for_stars(cls, x, y, nrow, ncol, world, chunk=4096):
         """Tile-ordered stars dealt to the ranks in chunks of ``chunk`` consecutive stars (chunk c -> rank c mod world):
@@ -249,7 +260,6 @@ def _gather_arena(plan, arena, group=None, side_stream=None, ncols=None):
     nbytes = arena.nbytes if ncols is None else (last_off + last_nb + 255) // 256 * 256  # the prefix that holds `spec`
     flat = arena.flat[:nbytes]
     full = flat.reshape(1, -1) if world == 1 else torch.empty((world, nbytes), dtype=torch.uint8, device=dev)
-    ridx, pidx = plan._index_t("rank_of", 0, dev), plan._index_t("pos_of", 0, dev)
     outs = {name: torch.empty((plan.n,) + tail, dtype=dt, device=dev) for name, dt, tail in spec}
 
     def work():
@@ -260,9 +270,8 @@ def _gather_arena(plan, arena, group=None, side_stream=None, ncols=None):
             es = outs[name].element_size()
             k = int(np.prod(tail, dtype=np.int64))
             typed = full.reshape(-1).view(dt)
-            col = torch.as_strided(typed, (world, plan.m, k), (nbytes // es, k, 1), o // es)  # [rank, star, component]
-            if plan.n:
-                outs[name].reshape(plan.n, k).copy_(col[ridx, pidx])  # row s <- (rank_of[s], pos_of[s])
+            if plan.n:  # element (s, j) <- flat element rank_of[s] * (nbytes / es) + pos_of[s] * k + j of the column: one gather
+                torch.take(typed[o // es:], plan._flat_index(es, k, nbytes, dev), out=outs[name].reshape(-1))
     if use_side:
         cur = torch.cuda.current_stream(dev)
         side_stream.wait_stream(cur)
