@@ -81,6 +81,9 @@ int next_pow2(long long v) {
     return m;
 }
 
+#ifndef BP_POOL_KEEP_GIB
+#define BP_POOL_KEEP_GIB 8  // freed stream-ordered scratch the device pool keeps across synchronisations
+#endif
 #ifndef AP_BATCH
 #define AP_BATCH 65536
 #endif
@@ -115,7 +118,7 @@ int dev_info(DevInfo* d) {
         if (!(tuned.load() & bit)) {
             cudaMemPool_t pool;
             if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
-                unsigned long long keep = 8ull << 30;
+                unsigned long long keep = (unsigned long long)BP_POOL_KEEP_GIB << 30;
                 cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
             }
             cudaGetLastError();
