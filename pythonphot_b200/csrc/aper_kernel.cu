@@ -713,7 +713,7 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S
                 continue;
             }
             // ---- P2: sort (mmm.py:119); the tail is padded with +inf; sorted keys go to the scratch row
-            T* __restrict__ dst = skeys + (size_t)(i - P.s0) * P.sstride;
+            T* __restrict__ dst = skeys + (size_t)(i - P.s0 + P.row0) * P.sstride;
             if constexpr (K > 0) {
                 T r[K];
                 const int nwarps = ((nslots + K - 1) / K + 31) >> 5, nthr = nwarps * 32;  // warps / threads that get real keys
@@ -733,7 +733,7 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S
                         else *reinterpret_cast<double2*>(dst + e) = make_double2(r[q], r[q + 1]);
                     }
                 }
-                if (P.sidx) sort_index<T, K>(P, r, dst, nvalid, (size_t)(i - P.s0), tid, s_wsum);
+                if (P.sidx) sort_index<T, K>(P, r, dst, nvalid, (size_t)(i - P.s0 + P.row0), tid, s_wsum);
             } else {
                 int m = 2;
                 while (m < nslots) m <<= 1;

@@ -102,7 +102,10 @@ int next_pow2(long long v) {
 #ifndef AP_S2_CTAS
 #define AP_S2_CTAS 0  // 0 = as many stage-2 CTAs per SM as fit
 #endif
-constexpr int APER_BATCH = AP_BATCH;  // stars per stage-1 / stage-2 launch pair (scratch = batch * ~13 KB)
+#ifndef AP_GROUP
+#define AP_GROUP 4  // stage-1 launches per stage-2 (mmm) launch: the thread-per-star mmm wants many stars in flight
+#endif
+constexpr int APER_BATCH = AP_BATCH;  // stars per stage-1 launch (also the granularity of the banded-upload waits)
 
 struct DevInfo {
     int sms;
@@ -397,7 +400,7 @@ int bphot_version(void) { return BPHOT_VERSION; }
 #define BP_STR2(x) #x
 #define BP_STR(x) BP_STR2(x)
 const char* bphot_build_flags(void) {
-    return "AP_ASM_SELECT=" BP_STR(AP_ASM_SELECT) " AP_BATCH=" BP_STR(AP_BATCH) " AP_S1_CTAS=" BP_STR(AP_S1_CTAS) " AP_MMM_INDEXED=" BP_STR(AP_MMM_INDEXED) " AP_MMM_OVERLAP=" BP_STR(AP_MMM_OVERLAP)
+    return "AP_ASM_SELECT=" BP_STR(AP_ASM_SELECT) " AP_BATCH=" BP_STR(AP_BATCH) " AP_GROUP=" BP_STR(AP_GROUP) " AP_S1_CTAS=" BP_STR(AP_S1_CTAS) " AP_MMM_INDEXED=" BP_STR(AP_MMM_INDEXED) " AP_MMM_OVERLAP=" BP_STR(AP_MMM_OVERLAP)
            " AP_S2_MINB=" BP_STR(AP_S2_MINB) " AP_SUMS_CTAS=" BP_STR(AP_SUMS_CTAS) " AP_DYNAMIC=" BP_STR(AP_DYNAMIC)
            " PK_MINB_FORCED=" BP_STR(PK_MINB_FORCED) " PK_U=" BP_STR(PK_U) " PK_MINB_FIT=" BP_STR(PK_MINB_FIT) " PK_HOIST=" BP_STR(PK_HOIST) " PK_PSF_GLOBAL=" BP_STR(PK_PSF_GLOBAL) " AP_IDX_SKIP=" BP_STR(AP_IDX_SKIP);
 }
@@ -529,7 +532,12 @@ int bphot_aper_device_banded(const void* d_image, int image_dtype, int nrow, int
     void* scratch = nullptr;
     // thread-per-star mmm on an index of the sorted row (aper_kernel.cu sort_index): register-sort variants, mmm sky
     const bool indexed = AP_MMM_INDEXED && K > 0 && !use_setsky && !P.sky_sigclip;
-    const size_t keys_bytes = ((size_t)batch * P.sstride * es + 255) & ~(size_t)255;
+    // scratch for `group` stage-1 launches: one mmm launch then works on up to 262 144 stars (5.7 -> 4.5 ms per 1 M stars: it
+    // waits for memory and needs the warps); stage 1 keeps its 65 536-star launches
+    const int group_max = (AP_MMM_OVERLAP ? 1 : AP_GROUP);
+    const int group = (nstars + batch - 1) / batch < group_max ? (nstars + batch - 1) / batch : group_max;
+    const long long gstars = (long long)batch * group < nstars ? (long long)batch * group : nstars;
+    const size_t keys_bytes = ((size_t)gstars * P.sstride * es + 255) & ~(size_t)255;
     P.idx_stride = indexed ? (long long)sort_index_bytes(es) : 0;
     const int nbatch = (nstars + batch - 1) / batch;
     // AP_MMM_OVERLAP (off): the thread-per-star mmm waits for memory and leaves the issue slots idle, stage 1 is bound by issue
@@ -539,7 +547,7 @@ int bphot_aper_device_banded(const void* d_image, int image_dtype, int nrow, int
     // is resident -- so the knob stays off.  Per-kernel timing (bphot_profile) always keeps everything on one stream.
     const bool overlap = AP_MMM_OVERLAP && indexed && nbatch > 1 && g_profile.load() == 0;
     const int nbuf = overlap ? 2 : 1;
-    const size_t buf_bytes = (keys_bytes + (size_t)batch * (size_t)P.idx_stride + 255) & ~(size_t)255;
+    const size_t buf_bytes = (keys_bytes + (size_t)gstars * (size_t)P.idx_stride + 255) & ~(size_t)255;
     if (!use_setsky) CU_TRY(cudaMallocAsync(&scratch, (size_t)nbuf * buf_bytes, st));
     P.skeys = scratch;
     P.sidx = indexed ? (void*)(reinterpret_cast<char*>(scratch) + keys_bytes) : nullptr;
@@ -669,11 +677,12 @@ int bphot_aper_device_banded(const void* d_image, int image_dtype, int nrow, int
         }
     }
     for (int s0 = 0; s0 < nstars && !rc; s0 += batch) {
-        const int b = s0 / batch;
+        const int b = s0 / batch, gb = b % group;
         P.s0 = s0;
         P.scount = (nstars - s0) < batch ? (nstars - s0) : batch;
+        P.row0 = gb * batch;
         if (scratch) {
-            char* buf = reinterpret_cast<char*>(scratch) + (size_t)(b % nbuf) * buf_bytes;
+            char* buf = reinterpret_cast<char*>(scratch) + (size_t)((b / group) % nbuf) * buf_bytes;
             P.skeys = buf;
             P.sidx = indexed ? (void*)(buf + keys_bytes) : nullptr;
         }
@@ -688,6 +697,10 @@ int bphot_aper_device_banded(const void* d_image, int image_dtype, int nrow, int
             cudaEventRecord(ev_s1[b], st);
             cudaStreamWaitEvent(s2, ev_s1[b], 0);
         }
+        if (gb != group - 1 && s0 + batch < nstars) { g_launches += 1; continue; }  // stage 2 after the group's last stage-1 launch
+        P.s0 = (b - gb) * batch;
+        P.scount = s0 + P.scount - P.s0;
+        P.row0 = 0;
         lt.begin(KT_APER_STAGE2);
         if (image_dtype == BPHOT_F32) BP_STAGE2(float);
         else BP_STAGE2(double);

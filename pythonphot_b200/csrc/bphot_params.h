@@ -34,6 +34,7 @@ struct AperParams {
     void* skeys;
     long long sstride;
     int s0, scount;
+    int row0;  // stage 1: scratch row of star s0 (a stage-2 launch covers several stage-1 launches)
     // index of each sorted row for the thread-per-star mmm (aper_kernel.cu sort_index): null = not built
     void* sidx;
     long long idx_stride;  // bytes per star
