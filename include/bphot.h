@@ -123,6 +123,30 @@ int bphot_aper_device_banded(const void* d_image, int image_dtype, int nrow, int
                              double* d_sky, double* d_skyerr, unsigned char* d_badflag,
                              int* d_nsky, int* d_mmm_iter,
                              const void* const* band_events, int nbands, int band_rows, void* stream);
+/*
+ * bphot_aper_device for callers that may not allocate.  NO counterpart in the reference: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.  Same arguments,
+ * same outputs; the call makes no cudaMalloc / cudaMallocAsync / cudaFree and uses no allocating library routine.  Its
+ * scratch (work counters, sorted sky-annulus rows, row indexes) lives in ONE static device array of
+ * BPHOT_NOALLOC_SCRATCH_BYTES that every GPU loading libbphot.so holds until the process exits.
+ *   limit   nstars <= 65536 and 256 + nstars * (row + index bytes) <= BPHOT_NOALLOC_SCRATCH_BYTES; for fp32 pixels and
+ *           skyrad=[40,50] that is 18 240 B per star = 3 679 stars per call (setsky: no rows, 65 536 stars).  Beyond it the
+ *           call returns BPHOT_ERR_CAPACITY and bphot_last_error() names the largest star count that fits.
+ *   sharing every call on a device uses the same array, which keeps the last call's contents (the call clears the counters
+ *           it needs at zero itself): two calls that OVERLAP on the GPU (different streams, or concurrent host threads) race.
+ *   order   stars are processed in caller order on the caller's stream (no visiting-order sort, no side stream), so results
+ *           are those of bphot_aper_device; large star lists are faster through bphot_aper_device.
+ */
+#define BPHOT_NOALLOC_SCRATCH_BYTES (64u << 20)
+int bphot_aper_device_noalloc(const void* d_image, int image_dtype, int nrow, int ncol, long long pitch,
+                              const double* d_xc, const double* d_yc, int nstars,
+                              double phpadu, const double* apr, int naper, double zeropoint,
+                              double skyrad_in, double skyrad_out, double badlo, double badhi,
+                              int use_setsky, const double* setsky, int minsky, int exact,
+                              double readnoise, int flags,
+                              double* d_mag, double* d_magerr, double* d_flux, double* d_fluxerr,
+                              double* d_sky, double* d_skyerr, unsigned char* d_badflag,
+                              int* d_nsky, int* d_mmm_iter, void* stream);
 
 int bphot_aper_host(const void* image, int image_dtype, int nrow, int ncol,
                     const double* xc, const double* yc, int nstars,

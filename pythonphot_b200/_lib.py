@@ -37,6 +37,8 @@ _SIGNATURES = {
                                     _d, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "bphot_aper_device_banded": (C.c_int, [_vp, _i, _i, _i, _ll, _vp, _vp, _i, _d, _vp, _i, _d, _d, _d, _d, _d, _i, _vp, _i, _i,
                                            _d, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
+    "bphot_aper_device_noalloc": (C.c_int, [_vp, _i, _i, _i, _ll, _vp, _vp, _i, _d, _vp, _i, _d, _d, _d, _d, _d, _i, _vp, _i, _i,
+                                            _d, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "bphot_aper_host": (C.c_int, [_vp, _i, _i, _i, _vp, _vp, _i, _d, _vp, _i, _d, _d, _d, _d, _d, _i, _vp, _i, _i,
                                   _d, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i]),
     "bphot_pkfit_device": (C.c_int, [_i, _vp, _i, _vp, _i, _vp, _i, _i, _ll, _ll, _ll, _vp, _vp, _i, _d, _d,

@@ -17,6 +17,11 @@
 #include "pkfit_kernel.cu"
 #include "find_kernel.cu"
 
+// Scratch of bphot_aper_device_noalloc, the one entry point that allocates nothing: BPHOT_NOALLOC_SCRATCH_BYTES of device memory
+// that every GPU loading this library holds until exit.  In host code this NAME is a host-side stand-in, not a device address:
+// noalloc_scratch() below asks the runtime for the address, once per device.  All calls share it (overlapping calls race).
+static __device__ __align__(256) unsigned char g_noalloc_scratch[BPHOT_NOALLOC_SCRATCH_BYTES];
+
 namespace {
 
 thread_local char g_err[512] = "";
@@ -385,6 +390,25 @@ int ensure_log10_table(cudaStream_t st) {
     return 0;
 }
 
+// device address of g_noalloc_scratch on the current device (cudaGetSymbolAddress once per device, that device current)
+constexpr size_t NOALLOC_HEAD = 256;  // the first 256 bytes are the work counters, zeroed by every call
+int noalloc_scratch(unsigned char** out) {
+    static std::atomic<unsigned char*> ptrs[64];
+    int dev = 0;
+    CU_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(BPHOT_ERR_ARG, "bphot_aper_noalloc: device ordinal %d outside 0..63", dev);
+    unsigned char* p = ptrs[dev].load();
+    if (!p) {
+        void* sym = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&sym, g_noalloc_scratch);
+        if (e != cudaSuccess || !sym) return fail(BPHOT_ERR_CUDA, "bphot_aper_noalloc: cudaGetSymbolAddress(scratch) on device %d: %s", dev, cudaGetErrorString(e));
+        p = reinterpret_cast<unsigned char*>(sym);
+        ptrs[dev].store(p);
+    }
+    *out = p;
+    return 0;
+}
+
 struct DevBuf {  // frees on scope exit
     void* p = nullptr;
     ~DevBuf() { if (p) cudaFree(p); }
@@ -738,6 +762,146 @@ int bphot_aper_device_banded(const void* d_image, int image_dtype, int nrow, int
     cudaFreeAsync(counters, st);
     ord.release(st);
     if (rc) return rc;
+    CU_TRY(cudaGetLastError());
+    return BPHOT_OK;
+}
+
+// ---- bphot_aper_device_noalloc: bphot_aper_device for callers that may not allocate (include/bphot.h).
+// Its scratch (work counters | sorted annulus rows | row indexes) is g_noalloc_scratch, a file-scope device array that every GPU
+// loading the library holds until exit.  One stage-1 launch (+ the wide retry), one stage-2 launch, the aperture sums and the
+// finalize kernel, all on the caller's stream, stars in caller order: no visiting-order sort, no side stream, no events.
+int bphot_aper_device_noalloc(const void* d_image, int image_dtype, int nrow, int ncol, long long pitch,
+                              const double* d_xc, const double* d_yc, int nstars,
+                              double phpadu, const double* apr, int naper, double zeropoint,
+                              double skyrad_in, double skyrad_out, double badlo, double badhi,
+                              int use_setsky, const double* setsky, int minsky, int exact,
+                              double readnoise, int flags,
+                              double* d_mag, double* d_magerr, double* d_flux, double* d_fluxerr,
+                              double* d_sky, double* d_skyerr, unsigned char* d_badflag,
+                              int* d_nsky, int* d_mmm_iter, void* stream) {
+    using namespace bphot;
+    if (!d_image || !apr || nstars < 0 || nrow <= 0 || ncol <= 0) return fail(BPHOT_ERR_ARG, "bphot_aper_noalloc: null image/apr or bad shape");
+    if (naper < 1 || naper > BPHOT_MAX_APER) return fail(BPHOT_ERR_ARG, "bphot_aper_noalloc: naper=%d outside 1..%d", naper, BPHOT_MAX_APER);
+    if (image_dtype != BPHOT_F32 && image_dtype != BPHOT_F64) return fail(BPHOT_ERR_ARG, "bphot_aper_noalloc: image dtype %d", image_dtype);
+    if (use_setsky && !setsky) return fail(BPHOT_ERR_ARG, "bphot_aper_noalloc: use_setsky without setsky[3]");
+    if (nstars == 0) return BPHOT_OK;
+    if (!d_xc || !d_yc || !d_mag || !d_magerr || !d_flux || !d_fluxerr || !d_sky || !d_skyerr || !d_badflag || !d_nsky || !d_mmm_iter)
+        return fail(BPHOT_ERR_ARG, "bphot_aper_noalloc: null star list or output pointer");
+    AperParams P;
+    memset(&P, 0, sizeof(P));
+    P.img = d_image; P.nrow = nrow; P.ncol = ncol; P.pitch = pitch > 0 ? pitch : ncol;
+    P.xc = d_xc; P.yc = d_yc; P.nstars = nstars;
+    P.phpadu = phpadu; P.zeropoint = zeropoint; P.naper = naper;
+    double amax = apr[0];
+    for (int k = 0; k < naper; k++) { P.apr[k] = apr[k]; if (apr[k] > amax) amax = apr[k]; }
+    P.use_setsky = use_setsky ? 1 : 0;
+    if (use_setsky) {  // aper.py:156-160
+        skyrad_in = 0.; skyrad_out = amax + 1.;
+        P.setsky[0] = setsky[0]; P.setsky[1] = setsky[1]; P.setsky[2] = setsky[2];
+    }
+    if (!(skyrad_out >= 0.) || !(skyrad_in >= 0.) || !(skyrad_out < 1e4)) return fail(BPHOT_ERR_ARG, "bphot_aper_noalloc: skyrad out of range");
+    P.skyrad_in = skyrad_in; P.skyrad_out = skyrad_out; P.badlo = badlo; P.badhi = badhi;
+    {   // the fp32 form of the bad-pixel window, as in bphot_aper_device_banded
+        float lo = (float)badlo, hi = (float)badhi;
+        if ((double)lo < badlo) lo = nextafterf(lo, INFINITY);
+        if ((double)hi > badhi) hi = nextafterf(hi, -INFINITY);
+        P.badlo_t = lo; P.badhi_t = hi;
+    }
+    P.minsky = minsky; P.exact = exact ? 1 : 0; P.compat_py2 = (flags & BPHOT_APER_PY2) ? 1 : 0; P.mxiter = 50;
+    P.sky_sigclip = (flags & BPHOT_APER_SIGMACLIP) ? 1 : 0;
+    P.readnoise = readnoise;
+    const long long bound = use_setsky ? 4 : annulus_bound(skyrad_in, skyrad_out);
+    const int need = next_pow2(bound);
+    const int K = need <= 1024 ? 8 : need <= 2048 ? 16 : need <= 4096 ? 32 : 0;
+    P.sort_cap = K ? AP_THREADS * K : need;
+    P.mag = d_mag; P.magerr = d_magerr; P.flux = d_flux; P.fluxerr = d_fluxerr;
+    P.sky = d_sky; P.skyerr = d_skyerr; P.badflag = d_badflag; P.nsky = d_nsky; P.mmm_iter = d_mmm_iter;
+    P.span_rows = (int)(2. * skyrad_out) + 4;
+    const size_t es = esize(image_dtype);
+    const size_t key_bytes = ((size_t)(K ? AP_THREADS * (K + 1) : need) * es + 15) & ~(size_t)15;
+    const size_t smem = key_bytes + (size_t)P.span_rows * 20;
+    int dev = 0, sms = 0, smem_optin = 0;
+    CU_TRY(cudaGetDevice(&dev));
+    CU_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    CU_TRY(cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    if (smem + 16384 > (size_t)smem_optin)
+        return fail(BPHOT_ERR_CAPACITY, "bphot_aper_noalloc: sky annulus [%g,%g] needs %zu B of shared memory per star (limit %d)",
+                    skyrad_in, skyrad_out, smem, smem_optin);
+    P.sstride = (bound + 15) / 16 * 16;
+    const bool indexed = AP_MMM_INDEXED && K > 0 && !use_setsky && !P.sky_sigclip;
+    P.idx_stride = indexed ? (long long)sort_index_bytes(es) : 0;
+    // the limit: one stage-1 launch, and counters + rows + indexes inside the static array
+    const size_t per_star = use_setsky ? 0 : (size_t)P.sstride * es + (size_t)P.idx_stride;
+    const size_t keys_bytes = use_setsky ? 0 : (((size_t)nstars * P.sstride * es + 255) & ~(size_t)255);
+    const size_t total = NOALLOC_HEAD + keys_bytes + (size_t)nstars * (size_t)P.idx_stride;
+    if (nstars > APER_BATCH || total > (size_t)BPHOT_NOALLOC_SCRATCH_BYTES) {
+        long long most = per_star ? (long long)(((size_t)BPHOT_NOALLOC_SCRATCH_BYTES - NOALLOC_HEAD - 256) / per_star) : APER_BATCH;
+        if (most > APER_BATCH) most = APER_BATCH;
+        return fail(BPHOT_ERR_CAPACITY, "bphot_aper_noalloc: %d stars need %zu B of scratch, the static array holds %llu B (%zu B per star "
+                    "for sky annulus [%g,%g]: at most %lld stars per call); use bphot_aper_device for more",
+                    nstars, total, (unsigned long long)BPHOT_NOALLOC_SCRATCH_BYTES, per_star, skyrad_in, skyrad_out, most);
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc = ensure_log10_table(st);
+    if (rc) return rc;
+    unsigned char* base = nullptr;
+    rc = noalloc_scratch(&base);
+    if (rc) return rc;
+    // the array keeps the previous call's contents: the work counters must start at zero, rows and indexes are written before read
+    CU_TRY(cudaMemsetAsync(base, 0, NOALLOC_HEAD, st));
+    int* next_counter = reinterpret_cast<int*>(base);
+    P.skeys = use_setsky ? nullptr : (void*)(base + NOALLOC_HEAD);
+    P.sidx = indexed ? (void*)(base + NOALLOC_HEAD + keys_bytes) : nullptr;
+    P.order = nullptr;
+    P.s0 = 0; P.scount = nstars; P.row0 = 0;
+    const double expect = M_PI * (skyrad_out * skyrad_out - skyrad_in * skyrad_in) * 1.03;
+    const int nt1 = (K > 0 && !use_setsky && (expect <= 96.0 * K || (flags & BPHOT_APER_NARROW_CTAS))) ? 96 : AP_THREADS;
+    int grid = 0;
+#define BP_NA_STAGE1(T, KK)                                                                      \
+    do {                                                                                         \
+        rc = persistent_grid(aper_stage1_kernel<T, KK>, nt1, smem, P.scount, &grid);             \
+        P.work_counter = next_counter++;                                                         \
+        if (!rc) aper_stage1_kernel<T, KK><<<grid, nt1, smem, st>>>(P);                          \
+        if (!rc && nt1 != AP_THREADS) {                                                          \
+            P.retry_wide = 1;                                                                    \
+            P.work_counter = next_counter++;                                                     \
+            rc = persistent_grid(aper_stage1_kernel<T, KK>, AP_THREADS, smem, P.scount, &grid);  \
+            if (!rc) aper_stage1_kernel<T, KK><<<grid, AP_THREADS, smem, st>>>(P);               \
+            P.retry_wide = 0;                                                                    \
+            g_launches += 1;                                                                     \
+        }                                                                                        \
+    } while (0)
+#define BP_NA_STAGE1_K(T)                       \
+    do {                                        \
+        if (K == 8) BP_NA_STAGE1(T, 8);         \
+        else if (K == 16) BP_NA_STAGE1(T, 16);  \
+        else if (K == 32) BP_NA_STAGE1(T, 32);  \
+        else BP_NA_STAGE1(T, 0);                \
+    } while (0)
+#define BP_NA_REST(T)                                                                                                \
+    do {                                                                                                             \
+        if (indexed) {                                                                                               \
+            aper_mmm_kernel<T><<<(P.scount + AP_MMM_THREADS - 1) / AP_MMM_THREADS, AP_MMM_THREADS, 0, st>>>(P);      \
+        } else {                                                                                                     \
+            rc = persistent_grid(aper_stage2_kernel<T>, AP_THREADS, 0, (P.scount + AP_WARPS - 1) / AP_WARPS, &grid); \
+            P.work_counter = next_counter++;                                                                         \
+            if (!rc) aper_stage2_kernel<T><<<grid, AP_THREADS, 0, st>>>(P);                                          \
+        }                                                                                                            \
+        if (rc) break;                                                                                               \
+        rc = persistent_grid(aper_sums_kernel<T>, AP_THREADS, 0, ((long long)nstars + AP_WARPS - 1) / AP_WARPS, &grid); \
+        P.work_counter = next_counter++;                                                                             \
+        if (!rc) aper_sums_kernel<T><<<grid, AP_THREADS, 0, st>>>(P);                                                \
+    } while (0)
+    if (image_dtype == BPHOT_F32) { BP_NA_STAGE1_K(float); if (!rc) BP_NA_REST(float); }
+    else { BP_NA_STAGE1_K(double); if (!rc) BP_NA_REST(double); }
+#undef BP_NA_REST
+#undef BP_NA_STAGE1_K
+#undef BP_NA_STAGE1
+    if (rc) return rc;
+    int gf = (nstars + 255) / 256;
+    if (gf > sms * 8) gf = sms * 8;
+    aper_finalize_kernel<<<gf, 256, 0, st>>>(P);
+    g_launches += 4;
     CU_TRY(cudaGetLastError());
     return BPHOT_OK;
 }
