@@ -46,7 +46,7 @@ extern "C" {
 #define BPHOT_OK 0
 #define BPHOT_ERR_ARG (-1)      /* bad argument (NULL pointer, naper out of range, ...) */
 #define BPHOT_ERR_CUDA (-2)     /* CUDA runtime error, see bphot_last_error() */
-#define BPHOT_ERR_CAPACITY (-3) /* sky annulus / fitting box larger than one CTA's shared memory */
+#define BPHOT_ERR_CAPACITY (-3) /* fitting box larger than one CTA's shared memory, output columns too short, no-alloc scratch too small */
 #define BPHOT_ERR_NODEVICE (-4) /* no CUDA device: there is no CPU fallback */
 
 int bphot_version(void);
@@ -198,6 +198,8 @@ int bphot_pkfit_host(int variant, const void* image, int image_dtype,
  * mmm.mmm(sky_vector, readnoise, minsky, mxiter) for nvec vectors packed back to back
  * (PythonPhot/mmm.py:7-314).  offs[nvec+1] = element offsets; max_len = longest vector.
  * out3[nvec*3] = (skymod, sigma, skew) per vector; iters[nvec] = clipping iterations.
+ * Vectors longer than one CTA sorts (32 768 fp32 / 16 384 fp64 elements) are sorted in global memory (the call then reads
+ * offs[nvec] back and synchronises the stream once).
  */
 int bphot_mmm_device(const void* d_vec, int dtype, const long long* d_offs, int nvec, int max_len,
                      double readnoise, int minsky, int mxiter,

@@ -749,6 +749,62 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S
     }
 }
 
+// Stage 1 for annuli that do not fit one CTA's shared memory (more than 32 768 fp32 / 16 384 fp64 pixels, e.g.
+// skyrad=[100,400]; aper.py:257-288 has no size limit): the same exact spans and slot-addressed gather, but the keys go
+// UNSORTED into the star's row of the global scratch (P.skeys, P.sstride = P.sort_cap slots) and seg_count[i - s0] gets the
+// number of slots in use; a segmented device sort (bphot_capi.cu) orders every row, aper_stage2_kernel runs mmm on it.
+// Only the span tables are in shared memory (20 bytes per stamp row).
+constexpr int AP_BIG_THREADS = 256;
+template <typename T>
+__global__ void __launch_bounds__(AP_BIG_THREADS) aper_gather_global_kernel(const AperParams P, int* __restrict__ seg_count) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    int* span = reinterpret_cast<int*>(smem_raw);
+    int* rowoff = span + 4 * P.span_rows;
+    __shared__ int s_ntot, s_star;
+    __shared__ int s_nrej[AP_BIG_THREADS / 32], s_nnan[AP_BIG_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = (int)(blockDim.x >> 5);
+    const T* __restrict__ img = reinterpret_cast<const T*>(P.img);
+    T* __restrict__ skeys = reinterpret_cast<T*>(P.skeys);
+    const double rinsq = P.skyrad_in * P.skyrad_in, routsq = P.skyrad_out * P.skyrad_out;
+    for (;;) {
+        __syncthreads();  // the previous star's tables and counters are no longer read
+        if (tid == 0) s_star = atomicAdd(P.work_counter, 1);
+        __syncthreads();
+        const int i = P.s0 + s_star;
+        if (i >= P.s0 + P.scount) break;
+        const int s = P.order ? P.order[i] : i;
+        const double x = P.xc[s], y = P.yc[s];
+        if (tid == 0) seg_count[i - P.s0] = 0;
+        if (!(x >= 0.5) || !(x <= P.ncol - 1.5) || !(y >= 0.5) || !(y <= P.nrow - 1.5)) {  // aper.py:209-210
+            if (tid == 0) { P.nsky[s] = 0; P.mmm_iter[s] = -1; }
+            continue;
+        }
+        const StarGeom g = star_geom(P, x, y);
+        row_spans(g, rinsq, routsq, span, rowoff, tid);
+        __syncthreads();
+        if (warp == 0) {
+            const int tot = row_offsets(rowoff, g.ny, lane);
+            if (lane == 0) s_ntot = tot;
+        }
+        __syncthreads();
+        T* __restrict__ dst = skeys + (size_t)(i - P.s0) * P.sstride;
+        const int2 cnt = gather_rows<T>(P, img + g.origin, g, span, rowoff, dst, warp, lane);
+        const int wrej = warp_sum_int(cnt.x), wnan = warp_sum_int(cnt.y);
+        if (lane == 0) { s_nrej[warp] = wrej; s_nnan[warp] = wnan; }
+        __syncthreads();
+        if (tid == 0) {
+            int nrej = 0, nnan = 0;
+            for (int w = 0; w < nw; w++) { nrej += s_nrej[w]; nnan += s_nnan[w]; }
+            const int nslots = s_ntot < P.sort_cap ? s_ntot : P.sort_cap;  // the bound is rigorous: always s_ntot
+            const int nsky_all = s_ntot - nrej;                              // aper.py:267 counts NaNs
+            int nvalid = nsky_all - nnan;                                    // mmm.py:106 drops them (they hold +inf here)
+            if (nvalid > nslots) nvalid = nslots;
+            if (nsky_all < P.minsky) { P.nsky[s] = nsky_all; P.mmm_iter[s] = -2; }  // aper.py:269-272
+            else { P.nsky[s] = nsky_all; P.mmm_iter[s] = nvalid; seg_count[i - P.s0] = nslots; }
+        }
+    }
+}
+
 // Aperture sums, one WARP per star (aper.py:310-380): no CTA-wide barrier, a small code footprint of its own, and
 // ~40 stars in flight per SM.  Leaves flux[s,k] = sum of weight*pixel and badflag[s,k] = raw flag bits for stage 2.
 template <typename T>
@@ -996,6 +1052,50 @@ __global__ void __launch_bounds__(AP_THREADS) mmm_kernel(const T* vec, const lon
 }
 
 // Pixwt(xc, yc, r, x[], y[]) -- pixwt.py:8 (row a5).
+// mmm over vectors that do not fit one CTA's shared memory (mmm.py has no size limit): mmm_prep_global_kernel copies every
+// vector into scratch with NaNs replaced by +inf (mmm.py:106 drops them) and counts the rest, a segmented device sort orders
+// the copies (bphot_capi.cu), mmm_global_kernel runs the clipping loop with one warp per vector on the sorted copy.
+template <typename T>
+__global__ void __launch_bounds__(256) mmm_prep_global_kernel(const T* __restrict__ vec, const long long* __restrict__ offs, int nvec,
+                                                              T* __restrict__ out, int* __restrict__ nvalid) {
+    __shared__ int s_cnt[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int v = blockIdx.x; v < nvec; v += gridDim.x) {
+        const long long b = offs[v], e = offs[v + 1];
+        int cnt = 0;
+        for (long long i = b + threadIdx.x; i < e; i += blockDim.x) {
+            const T val = vec[i];
+            const bool ok = (val == val);
+            cnt += ok;
+            out[i] = ok ? val : KeyTraits<T>::inf();
+        }
+        cnt = warp_sum_int(cnt);
+        __syncthreads();
+        if (lane == 0) s_cnt[warp] = cnt;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int t = 0;
+            for (int w = 0; w < (int)(blockDim.x >> 5); w++) t += s_cnt[w];
+            nvalid[v] = t;
+        }
+    }
+}
+template <typename T>
+__global__ void __launch_bounds__(AP_THREADS) mmm_global_kernel(const T* __restrict__ sorted, const long long* __restrict__ offs,
+                                                                const int* __restrict__ nvalid, int nvec, double readnoise, int minsky,
+                                                                int mxiter, double* out3, int* iters) {
+    const int lane = threadIdx.x & 31;
+    for (int v = blockIdx.x * AP_WARPS + (threadIdx.x >> 5); v < nvec; v += gridDim.x * AP_WARPS) {
+        GlobalView<T> view;
+        view.p = sorted + offs[v];
+        const MmmResult R = mmm_warp(view, nvalid[v], readnoise, minsky, mxiter, lane);
+        if (lane == 0) {
+            out3[3 * (size_t)v + 0] = R.skymod; out3[3 * (size_t)v + 1] = R.sigma; out3[3 * (size_t)v + 2] = R.skew;
+            iters[v] = R.iters;
+        }
+    }
+}
+
 __global__ void pixwt_kernel(double xc, double yc, double r, const double* x, const double* y, long long n, double* out) {
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
         out[i] = pixwt(xc, yc, r, x[i], y[i]);

@@ -10,6 +10,8 @@
 #include <vector>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_select.cuh>
+#include <cub/device/device_segmented_sort.cuh>
+#include <thrust/iterator/transform_iterator.h>
 #include <thrust/iterator/counting_iterator.h>
 
 #include "../../include/bphot.h"
@@ -409,6 +411,139 @@ int noalloc_scratch(unsigned char** out) {
     return 0;
 }
 
+// ---- sky annuli above one CTA's shared memory (aper_gather_global_kernel): rows of unsorted keys in global scratch, one
+// segmented device sort per batch of stars (CUB, one segment per star: [row start, row start + slots in use)), then the
+// warp-per-star mmm / sigma-clipping kernel on the sorted rows, the aperture sums and the finalize kernel, all on `st`.
+struct SegBegin {
+    long long stride;
+    __host__ __device__ int operator()(int i) const { return (int)(i * stride); }
+};
+struct SegEnd {
+    const int* count;
+    long long stride;
+    __host__ __device__ int operator()(int i) const { return (int)(i * stride) + count[i]; }
+};
+constexpr long long BIG_BATCH_KEYS = 1ll << 27;  // keys per batch of stars: 0.5 GiB (fp32) per buffer, three buffers
+
+template <typename T>
+int aper_big_annulus_run(bphot::AperParams P, int nstars, int batch, T* buf_in, T* buf_out, void* tmp, size_t tmp_bytes,
+                         int* seg_count, int* counters, size_t smem, cudaStream_t st) {
+    using namespace bphot;
+    int* next_counter = counters;
+    for (int s0 = 0; s0 < nstars; s0 += batch) {
+        int grid = 0;
+        P.s0 = s0;
+        P.scount = (nstars - s0) < batch ? (nstars - s0) : batch;
+        P.row0 = 0;
+        P.skeys = buf_in;
+        int rc = persistent_grid(aper_gather_global_kernel<T>, AP_BIG_THREADS, smem, P.scount, &grid);
+        if (rc) return rc;
+        P.work_counter = next_counter++;
+        aper_gather_global_kernel<T><<<grid, AP_BIG_THREADS, smem, st>>>(P, seg_count);
+        auto begins = thrust::make_transform_iterator(thrust::counting_iterator<int>(0), SegBegin{P.sstride});
+        auto ends = thrust::make_transform_iterator(thrust::counting_iterator<int>(0), SegEnd{seg_count, P.sstride});
+        size_t need = 0;
+        CU_TRY(cub::DeviceSegmentedSort::SortKeys(nullptr, need, buf_in, buf_out, (int)((long long)P.scount * P.sstride), P.scount, begins, ends, st));
+        if (need > tmp_bytes) return fail(BPHOT_ERR_CUDA, "bphot_aper: segmented sort wants %zu B of temporary storage, %zu B reserved", need, tmp_bytes);
+        CU_TRY(cub::DeviceSegmentedSort::SortKeys(tmp, need, buf_in, buf_out, (int)((long long)P.scount * P.sstride), P.scount, begins, ends, st));
+        P.skeys = buf_out;
+        rc = persistent_grid(aper_stage2_kernel<T>, AP_THREADS, 0, (P.scount + AP_WARPS - 1) / AP_WARPS, &grid);
+        if (rc) return rc;
+        P.work_counter = next_counter++;
+        aper_stage2_kernel<T><<<grid, AP_THREADS, 0, st>>>(P);
+        g_launches += 2;  // ours; the sort passes are CUB's
+    }
+    int grid = 0;
+    P.s0 = 0; P.scount = nstars;
+    int rc = persistent_grid(aper_sums_kernel<T>, AP_THREADS, 0, ((long long)nstars + AP_WARPS - 1) / AP_WARPS, &grid);
+    if (rc) return rc;
+    P.work_counter = next_counter++;
+    aper_sums_kernel<T><<<grid, AP_THREADS, 0, st>>>(P);
+    int gf = (nstars + 255) / 256;
+    if (gf > 148 * 8) gf = 148 * 8;
+    aper_finalize_kernel<<<gf, 256, 0, st>>>(P);
+    g_launches += 2;
+    CU_TRY(cudaGetLastError());
+    return 0;
+}
+
+// P: everything but the scratch fields filled in by bphot_aper_device_banded; `pixels` = upper bound on annulus pixels per star
+int aper_big_annulus(bphot::AperParams P, int image_dtype, long long pixels, int nstars, int smem_optin, cudaStream_t st) {
+    using namespace bphot;
+    if (P.span_rows > P.nrow) P.span_rows = P.nrow;  // a stamp never has more rows than the image
+    if (pixels > (long long)P.nrow * P.ncol) pixels = (long long)P.nrow * P.ncol;
+    const size_t smem = (size_t)P.span_rows * 20;
+    P.sstride = (pixels + 15) / 16 * 16;
+    if (smem + 2048 > (size_t)smem_optin || P.sstride > BIG_BATCH_KEYS)
+        return fail(BPHOT_ERR_CAPACITY, "bphot_aper: sky annulus [%g,%g] on a %d x %d image: %lld pixels per star / %zu B of span tables "
+                    "(limits %lld pixels, %d B)", P.skyrad_in, P.skyrad_out, P.nrow, P.ncol, P.sstride, smem, BIG_BATCH_KEYS, smem_optin - 2048);
+    P.sort_cap = (int)P.sstride;
+    P.idx_stride = 0; P.sidx = nullptr; P.order = nullptr;
+    long long batch = BIG_BATCH_KEYS / P.sstride;
+    if (batch > nstars) batch = nstars;
+    if (batch > APER_BATCH) batch = APER_BATCH;
+    const int nbatch = (int)((nstars + batch - 1) / batch);
+    const size_t es = esize(image_dtype);
+    const size_t row_bytes = ((size_t)batch * P.sstride * es + 255) & ~(size_t)255;
+    size_t tmp_bytes = 0;
+    {
+        auto begins = thrust::make_transform_iterator(thrust::counting_iterator<int>(0), SegBegin{P.sstride});
+        auto ends = thrust::make_transform_iterator(thrust::counting_iterator<int>(0), SegEnd{nullptr, P.sstride});
+        if (image_dtype == BPHOT_F32)
+            CU_TRY(cub::DeviceSegmentedSort::SortKeys(nullptr, tmp_bytes, (const float*)nullptr, (float*)nullptr, (int)(batch * P.sstride), (int)batch, begins, ends, st));
+        else
+            CU_TRY(cub::DeviceSegmentedSort::SortKeys(nullptr, tmp_bytes, (const double*)nullptr, (double*)nullptr, (int)(batch * P.sstride), (int)batch, begins, ends, st));
+    }
+    tmp_bytes = (tmp_bytes + 255) & ~(size_t)255;
+    const size_t cnt_bytes = ((size_t)batch * sizeof(int) + 255) & ~(size_t)255;
+    const size_t ctr_bytes = ((size_t)(2 * nbatch + 1) * sizeof(int) + 255) & ~(size_t)255;
+    char* block = nullptr;
+    CU_TRY(cudaMallocAsync((void**)&block, 2 * row_bytes + tmp_bytes + cnt_bytes + ctr_bytes, st));
+    int* seg_count = reinterpret_cast<int*>(block + 2 * row_bytes + tmp_bytes);
+    int* counters = reinterpret_cast<int*>(block + 2 * row_bytes + tmp_bytes + cnt_bytes);
+    int rc = 0;
+    if (cudaMemsetAsync(counters, 0, ctr_bytes, st) != cudaSuccess) rc = fail(BPHOT_ERR_CUDA, "bphot_aper: work counters: %s", cudaGetErrorString(cudaGetLastError()));
+    if (!rc) rc = ensure_log10_table(st);
+    if (!rc) {
+        if (image_dtype == BPHOT_F32)
+            rc = aper_big_annulus_run<float>(P, nstars, (int)batch, (float*)block, (float*)(block + row_bytes), block + 2 * row_bytes, tmp_bytes, seg_count, counters, smem, st);
+        else
+            rc = aper_big_annulus_run<double>(P, nstars, (int)batch, (double*)block, (double*)(block + row_bytes), block + 2 * row_bytes, tmp_bytes, seg_count, counters, smem, st);
+    }
+    cudaFreeAsync(block, st);
+    return rc;
+}
+
+// bphot_mmm_device for vectors above one CTA's shared memory (mmm_prep_global_kernel / mmm_global_kernel)
+template <typename T>
+int mmm_big(const T* d_vec, const long long* d_offs, int nvec, double readnoise, int minsky, int mxiter, double* d_out3, int* d_iters,
+            int sms, cudaStream_t st) {
+    using namespace bphot;
+    long long total = 0;
+    CU_TRY(cudaMemcpyAsync(&total, d_offs + nvec, sizeof(long long), cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    if (total < 0 || total > 0x7fffffffll) return fail(BPHOT_ERR_CAPACITY, "bphot_mmm: %lld elements in one call (limit 2^31 - 1 on the large-vector path)", total);
+    size_t tmp_bytes = 0;
+    CU_TRY(cub::DeviceSegmentedSort::SortKeys(nullptr, tmp_bytes, (const T*)nullptr, (T*)nullptr, (int)total, nvec, d_offs, d_offs + 1, st));
+    tmp_bytes = (tmp_bytes + 255) & ~(size_t)255;
+    const size_t col = ((size_t)total * sizeof(T) + 255) & ~(size_t)255;
+    char* block = nullptr;
+    CU_TRY(cudaMallocAsync((void**)&block, 2 * col + tmp_bytes + (size_t)nvec * sizeof(int), st));
+    T* copy = reinterpret_cast<T*>(block), *sorted = reinterpret_cast<T*>(block + col);
+    int* nvalid = reinterpret_cast<int*>(block + 2 * col + tmp_bytes);
+    mmm_prep_global_kernel<T><<<nvec < sms * 8 ? nvec : sms * 8, 256, 0, st>>>(d_vec, d_offs, nvec, copy, nvalid);
+    cudaError_t e = cub::DeviceSegmentedSort::SortKeys(block + 2 * col, tmp_bytes, (const T*)copy, sorted, (int)total, nvec, d_offs, d_offs + 1, st);
+    if (e == cudaSuccess) {
+        const int blocks = (nvec + AP_WARPS - 1) / AP_WARPS;
+        mmm_global_kernel<T><<<blocks < sms * 8 ? blocks : sms * 8, AP_THREADS, 0, st>>>(sorted, d_offs, nvalid, nvec, readnoise, minsky, mxiter, d_out3, d_iters);
+        e = cudaGetLastError();
+    }
+    cudaFreeAsync(block, st);
+    g_launches += 2;
+    if (e != cudaSuccess) return fail(BPHOT_ERR_CUDA, "bphot_mmm (large vectors): %s", cudaGetErrorString(e));
+    return BPHOT_OK;
+}
+
 struct DevBuf {  // frees on scope exit
     void* p = nullptr;
     ~DevBuf() { if (p) cudaFree(p); }
@@ -544,9 +679,10 @@ int bphot_aper_device_banded(const void* d_image, int image_dtype, int nrow, int
     DevInfo d;
     int rc = dev_info(&d);
     if (rc) return rc;
-    if (smem + 16384 > (size_t)d.smem_optin)
-        return fail(BPHOT_ERR_CAPACITY, "bphot_aper: sky annulus [%g,%g] needs %zu B of shared memory per star (limit %d)",
-                    skyrad_in, skyrad_out, smem, d.smem_optin);
+    if (smem + 16384 > (size_t)d.smem_optin) {  // the annulus does not fit a CTA: rows in global memory, segmented device sort
+        if (nbands > 0) cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)band_events[nbands - 1], 0);  // needs the whole image
+        return aper_big_annulus(P, image_dtype, bound, nstars, d.smem_optin, (cudaStream_t)stream);
+    }
     // scratch rows of sorted annulus keys (stage 1 -> stage 2), one batch of stars at a time
     P.sstride = (bound + 15) / 16 * 16;  // rows are 64-byte aligned: the indexed mmm reads aligned groups of 16 keys
     const int batch = nstars < APER_BATCH ? nstars : APER_BATCH;
@@ -1009,11 +1145,14 @@ int bphot_mmm_device(const void* d_vec, int dtype, const long long* d_offs, int 
     DevInfo d;
     int rc = dev_info(&d);
     if (rc) return rc;
-    if (smem + 1024 > (size_t)d.smem_optin) return fail(BPHOT_ERR_CAPACITY, "bphot_mmm: vector of %d elements exceeds shared memory", max_len);
     int grid = 0;
     cudaStream_t st = (cudaStream_t)stream;
     rc = ensure_log10_table(st);
     if (rc) return rc;
+    if (smem + 1024 > (size_t)d.smem_optin) {  // longer than one CTA can sort: copy, segmented device sort, warp per vector
+        if (dtype == BPHOT_F32) return mmm_big<float>((const float*)d_vec, d_offs, nvec, readnoise, minsky, mxiter, d_out3, d_iters, d.sms, st);
+        return mmm_big<double>((const double*)d_vec, d_offs, nvec, readnoise, minsky, mxiter, d_out3, d_iters, d.sms, st);
+    }
 #define BP_LAUNCH_MMM(T, KK)                                                                                         \
     do {                                                                                                             \
         rc = persistent_grid(mmm_kernel<T, KK>, AP_THREADS, smem, nvec, &grid);                                      \

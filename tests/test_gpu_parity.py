@@ -379,8 +379,75 @@ def test_c_abi_errors_are_reported(pp):
     rc = lib.bphot_aper_device(None, 0, 10, 10, 10, None, None, 1, 1.0, None, 1, 25.0, 40.0, 50.0, 0.0, 0.0, 0, None,
                                20, 1, 0.0, 0, None, None, None, None, None, None, None, None, None, None)
     assert rc == -1 and b"null" in lib.bphot_last_error()
-    with pytest.raises(_lib.BphotError):  # annulus too large for one CTA's shared memory
-        pp.aper.aper(np.zeros((64, 64), np.float32), [30.0], [30.0], skyrad=[100, 400], verbose=False)
+    # an annulus too large for one CTA's shared memory is not an error (global-memory sort path): here it lies off the frame
+    r = pp.aper.aper(np.zeros((64, 64), np.float32), [30.0], [30.0], skyrad=[100, 400], verbose=False)
+    assert float(np.asarray(r[4]).reshape(-1)[0]) == 0.0 and float(np.asarray(r[5]).reshape(-1)[0]) == 0.0  # aper.py:269-272
+
+
+# ------------------------------------------------------------------ annuli above one CTA's shared memory
+@pytest.mark.parametrize("mode,cname", [("py3", "r100_180"), ("py3", "r60_260"), ("py2", "r100_180")])
+def test_aper_big_annulus_golden(pp, oracle, mode, cname):
+    """skyrad=[100,180] / [60,260] (70 000 - 180 000 annulus pixels per star; one CTA sorts at most 32 768): rows in global
+    memory + segmented device sort + warp-per-star mmm, against the UNMODIFIED reference (tests/golden/gen_golden_bigannulus.py),
+    nsky / mmm iterations against the oracle.  fp32 image, then the same pixels as fp64."""
+    import hashlib
+    from tests.golden import gen_golden_bigannulus as G
+    g = load_golden("golden_aper_bigannulus.npz")
+    f = G.field()
+    assert hashlib.sha256(np.ascontiguousarray(f["image"]).tobytes()).hexdigest() == str(g["image_sha256"]), "generator drift"
+    kw = G.CASES[cname]
+    n = g["x"].size
+    want = {nm: g["%s__%s__%s" % (mode, cname, nm)] for nm in NAMES}
+    o = oracle.aper(f["image"], g["x"], g["y"], phpadu=float(g["phpadu"]), zeropoint=25.0, compat=mode, return_extra=True, **kw)
+    for img in (f["image"], f["image"].astype(np.float64)):
+        r = pp.aper.aper(img, g["x"], g["y"], phpadu=float(g["phpadu"]), zeropoint=25.0, verbose=False, compat=mode,
+                         return_info=True, **kw)
+        got = dict(zip(NAMES, r[:7]))
+        for k in ("mag", "magerr", "flux", "fluxerr", "badflag"):
+            got[k] = np.asarray(got[k]).reshape(n, -1)
+        _check_aper(got, want, o, "%s/%s/%s" % (mode, cname, img.dtype), r[8]["nsky"], o[7], r[8]["mmm_iter"])
+    assert int(np.max(o[7])) > 32768
+
+
+def test_mmm_big_vectors_golden(pp, oracle):
+    """mmm.mmm on vectors longer than one CTA sorts (40 000 - 262 144 elements, NaNs inside) against the reference's own
+    outputs; as one batch together with short vectors (the longest decides the path), fp64 and fp32, iterations against the oracle."""
+    from tests.golden import gen_golden_bigannulus as G
+    g = load_golden("golden_aper_bigannulus.npz")
+    vecs = G.big_vectors()
+    for v, want in zip(vecs, g["mmm_big"]):
+        assert_close(pp.mmm.mmm(v), want, rtol=1e-9, atol=1e-12, what="mmm n=%d" % v.size)
+    rng = np.random.default_rng(9)
+    mixed = [vecs[0], rng.normal(300, 5, 500), vecs[2], rng.normal(10, 1, 19), np.full(100, np.nan)]
+    for batch in (mixed, [v.astype(np.float32) for v in mixed]):
+        got, iters = pp.mmm.mmm_batch(batch, return_iters=True)
+        for i, v in enumerate(batch):
+            want = oracle.mmm(v.astype(np.float64), return_info=True)
+            assert iters[i] == want[3], "mmm iterations differ for vector %d" % i
+            assert_close(got[i], want[:3], rtol=1e-9, atol=1e-12, what="mmm vec %d" % i)
+
+
+def test_aper_big_annulus_many_stars_and_sigclip(pp, oracle):
+    """The same path with more stars than one batch of rows holds (2^27 keys per batch / ~96 000 slots per star = 1 390
+    stars), and with skyalgorithm='sigmaclipping' (aper.py:275-282) on a subset against oracle/sigclip_oracle.py."""
+    from oracle import sigclip_oracle
+    from pythonphot_b200 import synth
+    f = synth.make_field(700, 700, 1500, seed=515, dtype=np.float32, with_noise=False)
+    kw = dict(apr=np.array([5.0]), skyrad=[100, 200], badpix=[-12000, 60000], exact=False)
+    n = f["x"].size
+    r = pp.aper.aper(f["image"], f["x"], f["y"], phpadu=f["phpadu"], zeropoint=25.0, verbose=False, return_info=True, **kw)
+    o = oracle.aper(f["image"], f["x"], f["y"], phpadu=f["phpadu"], zeropoint=25.0, return_extra=True, nthreads=0, **kw)
+    got = dict(zip(NAMES, r[:7]))
+    for k in ("mag", "magerr", "flux", "fluxerr", "badflag"):
+        got[k] = np.asarray(got[k]).reshape(n, -1)
+    _check_aper(got, dict(zip(NAMES, o[:7])), o, "big annulus, two batches", r[8]["nsky"], o[7], r[8]["mmm_iter"])
+    sub = slice(0, 60)
+    r = pp.aper.aper(f["image"], f["x"][sub], f["y"][sub], phpadu=f["phpadu"], zeropoint=25.0, verbose=False,
+                     skyalgorithm="sigmaclipping", return_info=True, **kw)
+    sky, sig, nsky = sigclip_oracle.sky(f["image"], f["x"][sub], f["y"][sub], kw["skyrad"], kw["badpix"])
+    assert np.array_equal(np.asarray(r[8]["nsky"]).reshape(-1), nsky)
+    assert_close(np.asarray(r[4]).reshape(-1), sky, rtol=1e-9, atol=1e-9, what="sigclip sky")
+    assert_close(np.asarray(r[5]).reshape(-1), sig, rtol=1e-9, atol=1e-9, what="sigclip skyerr")
 
 
 # ------------------------------------------------------------------ fourth fit variant

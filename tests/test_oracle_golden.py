@@ -164,3 +164,28 @@ def test_pkfit_norecenter_golden(radius):
     p = oracle.pkfit(oracle.PKFIT, g["image"], g["gauss"], g["psf"], float(g["ronois"]), float(g["phpadu"]), None, None,
                      g["scale0"], g["x"], g["y"], g["sky"], radius, recenter=False)
     assert (p["niter"] != o["niter"]).any()
+
+
+# ----------------------------------------------------------------------------- large annuli / long sky vectors
+@pytest.mark.parametrize("mode,cname", [("py3", "r100_180"), ("py3", "r60_260"), ("py2", "r100_180")])
+def test_oracle_big_annulus_matches_reference(mode, cname):
+    """tests/golden/gen_golden_bigannulus.py: aper with 50 000 - 180 000 annulus pixels per star, reference vs oracle."""
+    import hashlib
+    from oracle import compare, oracle
+    from tests.golden import gen_golden_bigannulus as G
+    g = load_golden("golden_aper_bigannulus.npz")
+    f = G.field()
+    assert hashlib.sha256(np.ascontiguousarray(f["image"]).tobytes()).hexdigest() == str(g["image_sha256"]), "generator drift"
+    o = oracle.aper(f["image"], g["x"], g["y"], phpadu=float(g["phpadu"]), zeropoint=25.0, compat=mode, return_extra=True, **G.CASES[cname])
+    want = {nm: g["%s__%s__%s" % (mode, cname, nm)] for nm in G.NAMES}
+    rep = compare.compare_aper(dict(zip(G.NAMES, o[:7])), want, o[9], alt=o[10])
+    assert rep["mismatches"] == 0 and rep["fragile_checked"] == rep["fragile"], rep
+    assert int(np.max(o[7])) > 32768
+
+
+def test_oracle_mmm_long_vectors_match_reference():
+    from oracle import oracle
+    from tests.golden import gen_golden_bigannulus as G
+    g = load_golden("golden_aper_bigannulus.npz")
+    for v, want in zip(G.big_vectors(), g["mmm_big"]):
+        assert_close(oracle.mmm(v), want, rtol=1e-12, what="mmm n=%d" % v.size)
