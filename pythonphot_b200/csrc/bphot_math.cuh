@@ -17,6 +17,10 @@
 #include <math.h>
 #include <stdint.h>
 
+#ifndef PK_RECIP
+#define PK_RECIP 1  // fits: divisions whose divisor is fixed for a pixel / an iteration become multiplications by one reciprocal
+#endif
+
 #if defined(__CUDACC__)
 #define BP_HD __host__ __device__ __forceinline__
 #define BP_D __device__ __forceinline__
@@ -279,23 +283,45 @@ BP_HD int inv3(double c[3][3]) {
         double s = c[0][0];
         if (s > 0.0) {
             l00 = sqrt(s);
+#if PK_RECIP
+            // three reciprocals instead of nine divisions (every quotient below has l00, l11 or l22 as its divisor); the
+            // results move by an ulp or two, far inside the 1e-9 the fits are held to
+            const double m00 = 1.0 / l00;
+            l10 = c[1][0] * m00;
+            l20 = c[2][0] * m00;
+#else
             l10 = c[1][0] / l00;
             l20 = c[2][0] / l00;
+#endif
             s = c[1][1] - l10 * l10;
             if (s > 0.0) {
                 l11 = sqrt(s);
+#if PK_RECIP
+                const double m11 = 1.0 / l11;
+                l21 = (c[2][1] - l20 * l10) * m11;
+#else
                 l21 = (c[2][1] - l20 * l10) / l11;
+#endif
                 s = c[2][2] - l20 * l20;
                 s = s - l21 * l21;
                 if (s > 0.0) {
                     l22 = sqrt(s);
                     // M = inv(L), lower triangular; inv(A) = M^T M
+#if PK_RECIP
+                    const double m22 = 1.0 / l22;
+                    const double m10 = -(l10 * m00) * m11;
+                    const double m21 = -(l21 * m11) * m22;
+                    double t = 0.0 + l20 * m00;
+                    t = t + l21 * m10;
+                    const double m20 = -t * m22;
+#else
                     const double m00 = 1.0 / l00, m11 = 1.0 / l11, m22 = 1.0 / l22;
                     const double m10 = -(l10 * m00) / l11;
                     const double m21 = -(l21 * m11) / l22;
                     double t = 0.0 + l20 * m00;
                     t = t + l21 * m10;
                     const double m20 = -t / l22;
+#endif
                     double a00 = 0.0 + m00 * m00; a00 = a00 + m10 * m10; a00 = a00 + m20 * m20;
                     double a01 = 0.0 + m10 * m11; a01 = a01 + m20 * m21;
                     const double a02 = 0.0 + m20 * m22;

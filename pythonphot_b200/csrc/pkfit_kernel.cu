@@ -266,7 +266,7 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
             if (q < cap) {
                 const size_t row = (size_t)(b.iylo + r), col = (size_t)(b.ixlo + c);
                 FSUB[q] = (double)img[row * P.pitch + col];
-                SIG[q] = nz;
+                SIG[q] = PK_RECIP ? 1. / nz : nz;
                 W0[q] = 5. / (5. + rsq / (1. - rsq));
                 const double rho = dxv * dxv / gx2 + dyv * dyv / gy2;  // :338
                 const double rh = 0.5 * rho;
@@ -307,6 +307,7 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
     while (loop) {
         S.niter++;
         const double chiold = S.chiold;
+        const double inv_chi = 1. / chiold;  // PK_RECIP
         const bool later = S.niter >= 2;
         double numer = 0., denom = 0., s3 = 0., schi = 0., sumwt = 0.;
         double v0 = 0., v1 = 0., v2 = 0., c00 = 0., c01 = 0., c02 = 0., c11 = 0., c12 = 0., c22 = 0.;
@@ -327,9 +328,14 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
                     t0[u] = MV[q];
                     const double sg = SIG[q];
                     df[u] = FSUB[q] - S.scale * t0[u] - sky;  // :278
+#if PK_RECIP
+                    rel[u] = df[u] * sg;                       // :327, sg = 1 / sigma
+                    keep[u] = !(later && fabs(rel[u] * inv_chi) >= 10.);
+#else
                     rel[u] = df[u] / sg;                       // :327
                     keep[u] = !(later && fabs(rel[u] / chiold) >= 10.);  // :341-373 (rejection restarts from the full list)
-                    sigsq[u] = sg * sg;
+#endif
+                    sigsq[u] = sg * sg;                        // PK_RECIP: 1 / sigma^2
                     dfs[u] = DFS[q];
                     lil[u] = keep[u] && (dfs[u] == dfs[u]);
 #if PK_HOIST
@@ -352,13 +358,13 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
                 if (base0 + 32 * u >= ngood) break;  // warp-uniform
                 const unsigned mk = __ballot_sync(FULL, keep[u]);
                 if (lil[u]) {  // :377-410
-                    numer = numer + dfs[u] * df[u] / sigsq[u];
+                    numer = PK_RECIP ? numer + dfs[u] * df[u] * sigsq[u] : numer + dfs[u] * df[u] / sigsq[u];
 #if PK_HOIST
                     denom = denom + dds[u];
 #else
                     denom = denom + dfs[u] * dfs[u] / sigsq[u];
 #endif
-                    s3 = s3 + df[u] * df[u] / sigsq[u];
+                    s3 = PK_RECIP ? s3 + df[u] * df[u] * sigsq[u] : s3 + df[u] * df[u] / sigsq[u];
                     nl++;
                 }
                 if (keep[u]) {
@@ -368,7 +374,7 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
                     wmin = fmin(wmin, w);
                     if (!seen && (mk & lt) == 0u) wfirst_nan = (w != w);
                     if (later) {                   // :426-427
-                        const double e = 0.4 * rel[u] / chiold;
+                        const double e = PK_RECIP ? 0.4 * rel[u] * inv_chi : 0.4 * rel[u] / chiold;
                         const double e2 = e * e, e4 = e2 * e2;
                         w = w / (1. + e4 * e4);
                     }
