@@ -36,7 +36,18 @@ namespace bphot {
 
 // ------------------------------------------------------------------ pixwt
 // pixwt.py:50-62.  Plain division: x == 0 gives +-inf and atan(+-inf) = +-pi/2 (IEEE), as numpy.
+// PW_ONE_ATAN: atan(a) - atan(b) = atan((a - b) / (1 + a b)) while a b > -1, i.e. x^2 + y0 y1 > 0 -- every arc of a pixel
+// the circle crosses (its end points lie on one side of the axis) and every pixel beyond a circle of radius > 1/2: one
+// atan and one division instead of two of each (they were 28 % of aper_sums' instructions).  The value moves by a few
+// 1e-16 (the difference of two rounded atans is no more exact than this form); x == 0 gives atan(0) = 0 = pi/2 - pi/2.
+#ifndef PW_ONE_ATAN
+#define PW_ONE_ATAN 1
+#endif
 BP_HD double pw_arc(double x, double y0, double y1, double r) {
+#if PW_ONE_ATAN
+    const double den = x * x + y0 * y1;
+    if (den > 0.0) return 0.5 * r * r * atan((y1 - y0) * x / den);
+#endif
     return 0.5 * r * r * (atan(y1 / x) - atan(y0 / x));
 }
 // pixwt.py:64-72

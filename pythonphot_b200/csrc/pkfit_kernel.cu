@@ -449,6 +449,8 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
         // pkfit.py:158-166.  A non-finite position cannot be truncated to a pixel index (the reference raises); treated as NaN.
         if (!isfinite(S.x) || !isfinite(S.y)) return fit_nan(S, false, false);
         const double scl = S.scale, chiold = S.chiold;
+        const double inv_chi = 1. / chiold;  // PK_RECIP
+        (void)inv_chi;
         const FitBox b = fit_box(P, S.x, S.y);
         const double qaxis = fill_axes(b, S.x, S.y, gauss, AX, acap, lane);
         const bool qsep = b.ixx + b.iyy <= 32;  // warp-uniform: the rho terms of every column and row sit in one lane each
@@ -494,7 +496,14 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
                 if (q < cap) {
                     DX[q] = dxv; DY[q] = dyv; RSQ[q] = rsq; RHO[q] = rho; FSUB[q] = fv;
                     GIDX[q] = pr * 65536 + pc;
-                    if (!ANALYTIC) { SIG[q] = nz; SIGSQ[q] = nz * nz; }
+                    if (!ANALYTIC) {
+#if PK_RECIP
+                        const double isg = 1. / nz;  // SIG / SIGSQ hold 1/sigma and 1/sigma^2: one division per pixel, the rest multiply
+                        SIG[q] = isg; SIGSQ[q] = isg * isg;
+#else
+                        SIG[q] = nz; SIGSQ[q] = nz * nz;
+#endif
+                    }
                     xmin = fmin(xmin, dxv); xmax = fmax(xmax, dxv);
                     ymin = fmin(ymin, dyv); ymax = fmax(ymax, dyv);
                 }
@@ -530,13 +539,25 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
                 if (fpos < 0.) fpos = 0.;
                 const double s2 = fpos / P.phpadu + P.ronois + (0.0075 * fpos) * (0.0075 * fpos) +
                                   (pkerr * (fpos - sky)) * (pkerr * (fpos - sky));
+#if PK_RECIP
+                const double isg = 1. / sqrt(s2);
+                SIG[q] = isg;
+                SIGSQ[q] = isg * isg;
+#else
                 SIGSQ[q] = s2;
                 SIG[q] = sqrt(s2);
+#endif
             }
             DF[q] = df;
+#if PK_RECIP
+            const double rel = df * SIG[q];
+            REL[q] = rel;
+            if (S.niter >= 2 && fabs(rel * inv_chi) >= 10.) { nbad++; GIDX[q] |= 0x40000000; }
+#else
             const double rel = df / SIG[q];
             REL[q] = rel;
             if (S.niter >= 2 && fabs(rel / chiold) >= 10.) { nbad++; GIDX[q] |= 0x40000000; }
+#endif
         }
         __syncwarp();
 
@@ -596,22 +617,32 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
                         (pkerr * (fpos - sky)) * (pkerr * (fpos - sky));
                 } else {
                     const double sg = SIG[q];
-                    s = sg * sg;  // pkfit_noise.py:361
+                    s = sg * sg;  // pkfit_noise.py:361 (PK_RECIP: this is 1 / sigma^2)
                 }
                 // pkfit.py:350 pairs dfdsig with df[0:len(lilrho)] (the FIRST nl residuals)
                 const double dfv = ANALYTIC ? DF[nl + __popc(mk & lt)] : DF[q];
+#if PK_RECIP
+                const double is = ANALYTIC ? 1. / s : s;
+                numer = numer + dfdsig * dfv * is;
+                denom = denom + dfdsig * dfdsig * is;
+#else
                 numer = numer + dfdsig * dfv / s;
                 denom = denom + dfdsig * dfdsig / s;
+#endif
             }
             nl += __popc(mk);
             if (in) {
                 const double rsq = RSQ[q], rel = REL[q], df = DF[q];
+#if PK_RECIP
+                double wt = 5. * (1. - rsq) / (5. - 4. * rsq);  // pkfit.py:323, 5 / (5 + rsq / (1 - rsq)) with one division
+#else
                 double wt = 5. / (5. + rsq / (1. - rsq));  // pkfit.py:323
+#endif
                 schi = schi + wt * fabs(rel);               // pkfit.py:359
                 sumwt = sumwt + wt;
-                wt = wt / SIGSQ[q];                          // pkfit.py:362
+                wt = PK_RECIP ? wt * SIGSQ[q] : wt / SIGSQ[q];  // pkfit.py:362
                 if (S.niter >= 2) {  // pkfit.py:364
-                    const double e = 0.4 * rel / chiold;
+                    const double e = PK_RECIP ? 0.4 * rel * inv_chi : 0.4 * rel / chiold;
                     const double e2 = e * e, e4 = e2 * e2;
                     wt = wt / (1. + e4 * e4);
                 }

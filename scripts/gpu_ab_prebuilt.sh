@@ -14,6 +14,9 @@ for TAG in "$@"; do
         timeout 600 python -m pytest tests -m gpu -x -q -p no:cacheprovider > gpurun_out/abp_tests_$TAG.log 2>&1; echo "[$TAG] pytest rc=$?"; tail -3 gpurun_out/abp_tests_$TAG.log
     fi
     timeout 300 python bench.py --steps 5 --warmup 3 --no-e2e --no-cpu-baseline ${BENCH_ARGS:-} > gpurun_out/abp_bench_$TAG.log 2>&1 || { echo "[$TAG] bench failed"; tail -5 gpurun_out/abp_bench_$TAG.log; }
+    if [ "${C5:-0}" = "1" ]; then  # the config5 pipeline at a quarter of its size (aper apr=5 -> recentring pkfit_noise), with its parity block
+        timeout 600 python bench.py --workload config5 --c5-size ${C5_SIZE:-8192} --c5-stars ${C5_STARS:-2500000} --steps 2 --warmup 2 > gpurun_out/abp_c5_$TAG.log 2>&1 || { echo "[$TAG] config5 bench failed"; tail -5 gpurun_out/abp_c5_$TAG.log; }
+    fi
     i=$((i+1))
 done
 cp gpurun_out/.libbphot_keep.so pythonphot_b200/csrc/libbphot.so
@@ -29,4 +32,15 @@ for tag in sys.argv[1:]:
                       "parity mismatches", d.get("parity", {}).get("mismatches"), "c5", (d.get("config5") or {}).get("ms_per_pass"))
     except Exception as e:
         print(tag, "no bench line:", e)
+    try:
+        for l in open("gpurun_out/abp_c5_%s.log" % tag):
+            if l.startswith("{"):
+                c = json.loads(l)["config5"]
+                print("[%s] config5 %.2f M stars/s, step %.1f ms, aper %s fit %s, mean niter %.2f, parity %s" % (
+                    tag, c["value"] / 1e6, c["ms_per_step"], c["per_rank"]["aper_ms"], c["per_rank"]["pkfit_ms"], c["mean_niter"],
+                    (c.get("parity") or {}).get("mismatches")))
+    except FileNotFoundError:
+        pass
+    except Exception as e:
+        print(tag, "no config5 line:", e)
 PY

@@ -11,16 +11,33 @@ _SO = os.path.join(_HERE, "libhostcheck.so")
 _lib = None
 
 
+_SO_EXACT = os.path.join(_HERE, "libhostcheck_exact.so")
+_lib_exact = None
+
+
+def _build(so, defines=()):
+    src = os.path.join(_HERE, "hostcheck.cpp")
+    hdr = os.path.join(_HERE, "..", "..", "pythonphot_b200", "csrc", "bphot_math.cuh")
+    if (not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(src), os.path.getmtime(hdr))):
+        subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-x", "c++"] + list(defines) +
+                              ["-shared", "-o", so, src])
+    return C.CDLL(so)
+
+
 def lib():
+    """The header as the product compiles it (default knobs)."""
     global _lib
     if _lib is None:
-        src = os.path.join(_HERE, "hostcheck.cpp")
-        hdr = os.path.join(_HERE, "..", "..", "pythonphot_b200", "csrc", "bphot_math.cuh")
-        if (not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(src), os.path.getmtime(hdr))):
-            subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-x", "c++",
-                                   "-shared", "-o", _SO, src])
-        _lib = C.CDLL(_SO)
+        _lib = _build(_SO)
     return _lib
+
+
+def lib_exact():
+    """The header with the reference-order arithmetic everywhere (PK_RECIP=0, PW_ONE_ATAN=0): what the bit-for-bit checks use."""
+    global _lib_exact
+    if _lib_exact is None:
+        _lib_exact = _build(_SO_EXACT, ("-DPK_RECIP=0", "-DPW_ONE_ATAN=0"))
+    return _lib_exact
 
 
 def _p(a):
@@ -42,9 +59,9 @@ def psfmodel(xx, yy, gauss, psf):
     return out
 
 
-def inv3(c):
+def inv3(c, exact=False):
     c = np.array(c, dtype=np.float64, order="C")
-    st = lib().hc_inv3(_p(c))
+    st = (lib_exact() if exact else lib()).hc_inv3(_p(c))
     return c, st
 
 
