@@ -55,6 +55,9 @@ constexpr int PK_NARR_FIT = 10;     // per-warp scratch arrays of `cap` doubles,
 #ifndef PK_PSF_GLOBAL
 #define PK_PSF_GLOBAL 0  // 1 = the residual look-up table is read from global memory (L1-resident, 13 KB) instead of a per-CTA shared copy
 #endif
+#ifndef PK_TSUM
+#define PK_TSUM 1  // the 13-14 warp sums of an iteration through warp_sum16 (one transposing reduction) instead of one butterfly each
+#endif
 #ifndef PK_HOIST
 #define PK_HOIST 1  // forced fit: W0/sigsq and dfs*dfs/sigsq (operands fixed at set-up) are divided once per star, not per iteration
 #endif
@@ -125,12 +128,14 @@ BP_D double model_at(const double* AX, int acap, int c, int r, double dxv, doubl
 
 struct FitState {
     double clamp0, clamp1, clamp2, dtold0, dtold1, dtold2;
+    double iclamp0, iclamp1, iclamp2;  // 1 / clamp: the clamps are powers of two, so multiplying by these is dividing by those, bit for bit
     double chiold, chi, sharp, errmag, chi2, scale, x, y;
     int niter;
 };
 BP_D FitState fit_init(double scale, double x, double y, bool norecenter = false) {
     FitState S;
     S.clamp0 = S.clamp1 = S.clamp2 = 1.;
+    S.iclamp0 = S.iclamp1 = S.iclamp2 = 1.;
     S.dtold0 = S.dtold1 = S.dtold2 = 0.;
     S.chiold = 1.;
     S.chi = S.sharp = S.errmag = S.chi2 = nan64();
@@ -176,11 +181,21 @@ BP_D bool fit_tail(const PkfitParams& P, const double* gauss, FitState& S, doubl
     const double dt1 = v[0] * c[0][1] + v[1] * c[1][1] + v[2] * c[2][1];
     const double dt2 = v[0] * c[0][2] + v[1] * c[1][2] + v[2] * c[2][2];
     if (V == 2 && isinf(c[0][0])) return false;  // pkfit_norecent_noise.py:474-483
-    if (S.dtold0 * dt0 < -1.e-38) S.clamp0 = S.clamp0 / 2.;  // pkfit.py:421-423
-    if (S.dtold1 * dt1 < -1.e-38) S.clamp1 = S.clamp1 / 2.;
-    if (S.dtold2 * dt2 < -1.e-38) S.clamp2 = S.clamp2 / 2.;
+    if (S.dtold0 * dt0 < -1.e-38) { S.clamp0 = S.clamp0 / 2.; S.iclamp0 = S.iclamp0 * 2.; }  // pkfit.py:421-423
+    if (S.dtold1 * dt1 < -1.e-38) { S.clamp1 = S.clamp1 / 2.; S.iclamp1 = S.iclamp1 * 2.; }
+    if (S.dtold2 * dt2 < -1.e-38) { S.clamp2 = S.clamp2 / 2.; S.iclamp2 = S.iclamp2 * 2.; }
     S.dtold0 = dt0; S.dtold1 = dt1; S.dtold2 = dt2;
     const double adt0 = fabs(dt0), adt1 = fabs(dt1), adt2 = fabs(dt2);
+#if PK_RECIP
+    const double rs = dt0 / S.scale;  // pkfit.py:427-429 with one division for both candidates
+    double denom2 = rs * (1. / 5.25);
+    if (denom2 < -rs * (1. / 0.84)) denom2 = -rs * (1. / 0.84);
+    S.scale = S.scale + dt0 / (1 + denom2 * S.iclamp0);
+    if (V == 1 || (V == 0 && P.recenter)) {  // pkfit.py:430-432
+        S.x = S.x + dt1 / (1. + adt1 * (2. * S.iclamp1));
+        S.y = S.y + dt2 / (1. + adt2 * (2. * S.iclamp2));
+    }
+#else
     double denom2 = dt0 / (5.25 * S.scale);  // pkfit.py:427-429
     if (denom2 < (-1 * dt0 / (0.84 * S.scale))) denom2 = (-1 * dt0 / (0.84 * S.scale));
     S.scale = S.scale + dt0 / (1 + denom2 / S.clamp0);
@@ -188,6 +203,7 @@ BP_D bool fit_tail(const PkfitParams& P, const double* gauss, FitState& S, doubl
         S.x = S.x + dt1 / (1. + adt1 / (0.5 * S.clamp1));
         S.y = S.y + dt2 / (1. + adt2 / (0.5 * S.clamp2));
     }
+#endif
     bool redo = false;
     S.sharp = 2. * gauss[3] * gauss[4] * numer / (gauss[0] * S.scale * denom);  // pkfit.py:440
     S.errmag = S.chiold * sqrt(c[0][0]);
@@ -381,31 +397,49 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
                     v0 = v0 + df[u] * t0[u] * w; v1 = v1 + df[u] * t1[u] * w; v2 = v2 + df[u] * t2[u] * w;
                     c00 = c00 + t0[u] * t0[u] * w; c01 = c01 + t0[u] * t1[u] * w; c02 = c02 + t0[u] * t2[u] * w;
                     c11 = c11 + t1[u] * t1[u] * w; c12 = c12 + t1[u] * t2[u] * w; c22 = c22 + t2[u] * t2[u] * w;
-                    nkept++;
                 }
+                nkept += __popc(mk);  // warp-uniform count
                 if (mk) seen = true;
             }
         }
-        nkept = warp_sum_int(nkept);
         if (nkept == 0) return fit_nan(S, false, true);  // :347-356 (every pixel rejected)
         nl = warp_sum_int(nl);
         if (nl == 0) return fit_nan(S, false, false);    // :391-401
+#if PK_TSUM
+        {   // the fourteen sums of the iteration in one pass (warp_sum16: same additions, same bits as fourteen butterflies)
+            double t[16] = {numer, denom, s3, schi, sumwt, v0, v1, v2, c00, c01, c02, c11, c12, c22, 0., 0.};
+            warp_sum16(t, lane);
+            numer = t[0]; denom = t[1]; s3 = t[2]; schi = t[3]; sumwt = t[4]; v0 = t[5]; v1 = t[6]; v2 = t[7];
+            c00 = t[8]; c01 = t[9]; c02 = t[10]; c11 = t[11]; c12 = t[12]; c22 = t[13];
+        }
+        S.chi2 = s3 / (double)(nl - 1);          // :409-410
+        S.chi = schi;
+#else
         numer = pk_sum(numer); denom = pk_sum(denom);
         S.chi2 = pk_sum(s3) / (double)(nl - 1);          // :409-410
         schi = pk_sum(schi);
         S.chi = schi;
         sumwt = pk_sum(sumwt);
+#endif
         {   // :416-424; python min(): a NaN first element wins
             wmin = pk_min(wmin);
             const bool fn = __any_sync(FULL, wfirst_nan);
             if (!fn && wmin > 100000) return fit_nan(S, false, false);
         }
         double v[3], c[3][3];
+#if PK_TSUM
+        v[0] = v0; v[1] = v1; v[2] = v2;
+        c[0][0] = c00; c[1][1] = c11; c[2][2] = c22;
+        c[0][1] = c[1][0] = c01;
+        c[0][2] = c[2][0] = c02;
+        c[1][2] = c[2][1] = c12;
+#else
         v[0] = pk_sum(v0); v[1] = pk_sum(v1); v[2] = pk_sum(v2);
         c[0][0] = pk_sum(c00); c[1][1] = pk_sum(c11); c[2][2] = pk_sum(c22);
         c[0][1] = c[1][0] = pk_sum(c01);
         c[0][2] = c[2][0] = pk_sum(c02);
         c[1][2] = c[2][1] = pk_sum(c12);
+#endif
         if (!fit_tail<2>(P, gauss, S, v, c, numer, denom, schi, sumwt, &loop)) return fit_nan(S, false, false);
     }
     return fit_out(S);
@@ -657,16 +691,30 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
         // pkfit_norecenter.py:537,570-573 multiplies df[lilrho] (nl long) with wt (m long): numpy raises unless every pixel
         // lies within 6 sigma; reported as a failed fit
         if (V == 3 && nl != m) return fit_nan(S, false, false);
+        double v[3], c[3][3];
+#if PK_TSUM
+        {
+            double t[16] = {numer, denom, schi, sumwt, v0, v1, v2, c00, c01, c02, c11, c12, c22, 0., 0., 0.};
+            warp_sum16(t, lane);
+            numer = t[0]; denom = t[1]; schi = t[2]; sumwt = t[3];
+            v[0] = t[4]; v[1] = t[5]; v[2] = t[6];
+            c[0][0] = t[7]; c[1][1] = t[10]; c[2][2] = t[12];
+            c[0][1] = c[1][0] = t[8];
+            c[0][2] = c[2][0] = t[9];
+            c[1][2] = c[2][1] = t[11];
+        }
+        S.chi = schi;
+#else
         numer = pk_sum(numer); denom = pk_sum(denom);
         schi = pk_sum(schi);
         S.chi = schi;
         sumwt = pk_sum(sumwt);
-        double v[3], c[3][3];
         v[0] = pk_sum(v0); v[1] = pk_sum(v1); v[2] = pk_sum(v2);
         c[0][0] = pk_sum(c00); c[1][1] = pk_sum(c11); c[2][2] = pk_sum(c22);
         c[0][1] = c[1][0] = pk_sum(c01);
         c[0][2] = c[2][0] = pk_sum(c02);
         c[1][2] = c[2][1] = pk_sum(c12);
+#endif
         if (!fit_tail<V>(P, gauss, S, v, c, numer, denom, schi, sumwt, &loop)) return fit_nan(S, false, false);
         __syncwarp();
     }
