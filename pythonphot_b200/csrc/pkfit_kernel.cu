@@ -327,7 +327,7 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
         const bool later = S.niter >= 2;
         double numer = 0., denom = 0., s3 = 0., schi = 0., sumwt = 0.;
         double v0 = 0., v1 = 0., v2 = 0., c00 = 0., c01 = 0., c02 = 0., c11 = 0., c12 = 0., c22 = 0.;
-        double wmin = KeyTraits<double>::inf();
+        bool wle = false;  // some kept pixel has weight <= 100000: min(wt) > 100000 (:416-424) is "no lane saw one"
         bool wfirst_nan = false, seen = false;
         int nkept = 0, nl = 0;
         // PK_U chunks of 32 pixels per pass: the divisions of the chunks are independent and overlap; the sums still
@@ -387,16 +387,25 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
                     schi = schi + wt[u] * fabs(rel[u]);  // :411
                     sumwt = sumwt + wt[u];
                     double w = wtr[u];
-                    wmin = fmin(wmin, w);
+                    wle = wle || (w <= 100000.);
                     if (!seen && (mk & lt) == 0u) wfirst_nan = (w != w);
                     if (later) {                   // :426-427
                         const double e = PK_RECIP ? 0.4 * rel[u] * inv_chi : 0.4 * rel[u] / chiold;
                         const double e2 = e * e, e4 = e2 * e2;
                         w = w / (1. + e4 * e4);
                     }
+#if PK_RECIP
+                    {   // weighted model terms once, then one fused multiply-add per normal-equation sum (12 fp64 operations, not 27)
+                        const double a0 = t0[u] * w, a1 = t1[u] * w, a2 = t2[u] * w;
+                        v0 = fma(df[u], a0, v0); v1 = fma(df[u], a1, v1); v2 = fma(df[u], a2, v2);
+                        c00 = fma(t0[u], a0, c00); c01 = fma(t0[u], a1, c01); c02 = fma(t0[u], a2, c02);
+                        c11 = fma(t1[u], a1, c11); c12 = fma(t1[u], a2, c12); c22 = fma(t2[u], a2, c22);
+                    }
+#else
                     v0 = v0 + df[u] * t0[u] * w; v1 = v1 + df[u] * t1[u] * w; v2 = v2 + df[u] * t2[u] * w;
                     c00 = c00 + t0[u] * t0[u] * w; c01 = c01 + t0[u] * t1[u] * w; c02 = c02 + t0[u] * t2[u] * w;
                     c11 = c11 + t1[u] * t1[u] * w; c12 = c12 + t1[u] * t2[u] * w; c22 = c22 + t2[u] * t2[u] * w;
+#endif
                 }
                 nkept += __popc(mk);  // warp-uniform count
                 if (mk) seen = true;
@@ -422,9 +431,9 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
         sumwt = pk_sum(sumwt);
 #endif
         {   // :416-424; python min(): a NaN first element wins
-            wmin = pk_min(wmin);
+            // (NaN weights never win a later comparison in python's min(), so they count for nothing unless first)
             const bool fn = __any_sync(FULL, wfirst_nan);
-            if (!fn && wmin > 100000) return fit_nan(S, false, false);
+            if (!fn && !__any_sync(FULL, wle)) return fit_nan(S, false, false);
         }
         double v[3], c[3][3];
 #if PK_TSUM
@@ -682,9 +691,18 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
                 }
                 const int g = direct ? q : GIDX[q];
                 const double t0 = T0[g], t1 = T1[g], t2 = T2[g];
+#if PK_RECIP
+                {
+                    const double a0 = t0 * wt, a1 = t1 * wt, a2 = t2 * wt;
+                    v0 = fma(df, a0, v0); v1 = fma(df, a1, v1); v2 = fma(df, a2, v2);
+                    c00 = fma(t0, a0, c00); c01 = fma(t0, a1, c01); c02 = fma(t0, a2, c02);
+                    c11 = fma(t1, a1, c11); c12 = fma(t1, a2, c12); c22 = fma(t2, a2, c22);
+                }
+#else
                 v0 = v0 + df * t0 * wt; v1 = v1 + df * t1 * wt; v2 = v2 + df * t2 * wt;
                 c00 = c00 + t0 * t0 * wt; c01 = c01 + t0 * t1 * wt; c02 = c02 + t0 * t2 * wt;
                 c11 = c11 + t1 * t1 * wt; c12 = c12 + t1 * t2 * wt; c22 = c22 + t2 * t2 * wt;
+#endif
             }
         }
         if (nl == 0) return fit_nan(S, false, false);  // pkfit.py:325-333
