@@ -55,6 +55,12 @@ constexpr int PK_NARR_FIT = 10;     // per-warp scratch arrays of `cap` doubles,
 #ifndef PK_PSF_GLOBAL
 #define PK_PSF_GLOBAL 0  // 1 = the residual look-up table is read from global memory (L1-resident, 13 KB) instead of a per-CTA shared copy
 #endif
+#ifndef PK_FMA_MODEL
+#define PK_FMA_MODEL PK_RECIP  // the look-up table's cubics in fused multiply-adds (rinter_f)
+#endif
+#ifndef PK_FMA_LOOP
+#define PK_FMA_LOOP 0  // forced fit, bit mask: 1 = sky taken off the pixel at set-up and the residual as one fma, 2 = dfs / sigma^2 stored, 4 = s3 / schi / e^8 as fmas
+#endif
 #ifndef PK_TSUM
 #define PK_TSUM 1  // the 13-14 warp sums of an iteration through warp_sum16 (one transposing reduction) instead of one butterfly each
 #endif
@@ -115,14 +121,54 @@ BP_D double fill_axes(const FitBox& b, double x, double y, const double* gauss, 
     return qv;
 }
 
+// rinter.py:98-195 as bphot_math.cuh's rinter(), with the cubics in fused multiply-adds (PK_RECIP: the fits are held to
+// 1e-9, the look-up table's unit kernel to its goldens' last bits, so only the fits use this form).
+BP_D void rinter_row_f(const double* p, long plen, long k, double xd, double* val, double* der) {
+    const double pm = rinter_at(p, plen, k - 1, 0), p0 = rinter_at(p, plen, k, 0);
+    const double p1 = rinter_at(p, plen, k + 1, 0), p2 = rinter_at(p, plen, k + 2, 0);
+    const double c1 = 0.5 * (p1 - pm);
+    const double c2 = fma(2., p1, pm) - 0.5 * fma(5., p0, p2);
+    const double c3 = 0.5 * (fma(3., p0 - p1, p2) - pm);
+    *val = fma(xd, fma(xd, fma(xd, c3, c2), c1), p0);
+    *der = fma(xd, fma(xd * 3., c3, 2. * c2), c1);
+}
+BP_D double rinter_f(const double* p, int nr, int nc, double x, double y, double* dfdx, double* dfdy) {
+    const long plen = (long)nr * nc;
+    const long i = (long)x, j = (long)y;
+    const double xd = x - (double)i, yd = y - (double)j;
+    const long km = (long)nc * (j - 1) + i;
+    double ym, y0, y1, y2, gm, g0, g1, g2;
+    rinter_row_f(p, plen, km, xd, &ym, &gm);
+    rinter_row_f(p, plen, km + nc, xd, &y0, &g0);
+    rinter_row_f(p, plen, km + 2L * nc, xd, &y1, &g1);
+    rinter_row_f(p, plen, km + 3L * nc, xd, &y2, &g2);
+    {
+        const double d1 = 0.5 * (g1 - gm);
+        const double d2 = fma(2., g1, gm) - 0.5 * fma(5., g0, g2);
+        const double d3 = 0.5 * (fma(3., g0 - g1, g2) - gm);
+        *dfdx = fma(yd, fma(yd, fma(yd, d3, d2), d1), g0);
+    }
+    const double d1 = 0.5 * (y1 - ym);
+    const double d2 = fma(2., y1, ym) - 0.5 * fma(5., y0, y2);
+    const double d3 = 0.5 * (fma(3., y0 - y1, y2) - ym);
+    *dfdy = fma(yd, fma(yd * 3., d3, 2. * d2), d1);
+    return fma(yd, fma(yd, fma(yd, d3, d2), d1), y0);
+}
+
 // dao_value.py:95-107 for the pixel in column c, row r of the box (offsets dxv, dyv from the star).
 BP_D double model_at(const double* AX, int acap, int c, int r, double dxv, double dyv, const double* gauss,
                      const double* psf, int npsf, double half, double* dvx, double* dvy) {
     double p1, p2, dfdx, dfdy;
     const double e = daoerf_from_axes(gauss[0], AX[c], AX[acap + c], AX[2 * acap + r], AX[3 * acap + r], &p1, &p2);
+#if PK_FMA_MODEL
+    const double v = rinter_f(psf, npsf, npsf, fma(2., dxv, half), fma(2., dyv, half), &dfdx, &dfdy);
+    *dvx = fma(2., dfdx, -p1);
+    *dvy = fma(2., dfdy, -p2);
+#else
     const double v = rinter(psf, npsf, npsf, 2. * dxv + half, 2. * dyv + half, &dfdx, &dfdy);
     *dvx = 2. * dfdx - p1;
     *dvy = 2. * dfdy - p2;
+#endif
     return e + v;
 }
 
@@ -281,15 +327,19 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
             const int q = ngood + __popc(mk & lt);
             if (q < cap) {
                 const size_t row = (size_t)(b.iylo + r), col = (size_t)(b.ixlo + c);
-                FSUB[q] = (double)img[row * P.pitch + col];
+                FSUB[q] = (PK_FMA_LOOP & 1) ? (double)img[row * P.pitch + col] - sky : (double)img[row * P.pitch + col];  // PK_RECIP: sky taken off once
                 SIG[q] = PK_RECIP ? 1. / nz : nz;
                 W0[q] = 5. / (5. + rsq / (1. - rsq));
                 const double rho = dxv * dxv / gx2 + dyv * dyv / gy2;  // :338
                 const double rh = 0.5 * rho;
                 const double dfsv = (rho <= 36.) ? exp(-rh) * (rh - 1.) : nan64();
-                DFS[q] = dfsv;
 #if PK_HOIST
                 const double ssq = nz * nz;
+                DFS[q] = (PK_FMA_LOOP & 2) ? dfsv / ssq : dfsv;  // PK_RECIP: the sharpness numerator's per-pixel factor, NaN where dfsv is
+#else
+                DFS[q] = dfsv;
+#endif
+#if PK_HOIST
                 WTR[q] = W0[q] / ssq;
                 DDS[q] = dfsv * dfsv / ssq;
 #endif
@@ -343,11 +393,12 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
                 if (q < ngood) {
                     t0[u] = MV[q];
                     const double sg = SIG[q];
-                    df[u] = FSUB[q] - S.scale * t0[u] - sky;  // :278
 #if PK_RECIP
+                    df[u] = (PK_FMA_LOOP & 1) ? fma(-S.scale, t0[u], FSUB[q]) : FSUB[q] - S.scale * t0[u] - sky;  // :278 (PK_FMA_LOOP: FSUB = pixel - sky)
                     rel[u] = df[u] * sg;                       // :327, sg = 1 / sigma
                     keep[u] = !(later && fabs(rel[u] * inv_chi) >= 10.);
 #else
+                    df[u] = FSUB[q] - S.scale * t0[u] - sky;  // :278
                     rel[u] = df[u] / sg;                       // :327
                     keep[u] = !(later && fabs(rel[u] / chiold) >= 10.);  // :341-373 (rejection restarts from the full list)
 #endif
@@ -374,17 +425,17 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
                 if (base0 + 32 * u >= ngood) break;  // warp-uniform
                 const unsigned mk = __ballot_sync(FULL, keep[u]);
                 if (lil[u]) {  // :377-410
-                    numer = PK_RECIP ? numer + dfs[u] * df[u] * sigsq[u] : numer + dfs[u] * df[u] / sigsq[u];
+                    numer = ((PK_FMA_LOOP & 2) && PK_HOIST) ? fma(dfs[u], df[u], numer) : PK_RECIP ? numer + dfs[u] * df[u] * sigsq[u] : numer + dfs[u] * df[u] / sigsq[u];
 #if PK_HOIST
                     denom = denom + dds[u];
 #else
                     denom = denom + dfs[u] * dfs[u] / sigsq[u];
 #endif
-                    s3 = PK_RECIP ? s3 + df[u] * df[u] * sigsq[u] : s3 + df[u] * df[u] / sigsq[u];
+                    s3 = (PK_FMA_LOOP & 4) ? fma(df[u] * df[u], sigsq[u], s3) : PK_RECIP ? s3 + df[u] * df[u] * sigsq[u] : s3 + df[u] * df[u] / sigsq[u];
                     nl++;
                 }
                 if (keep[u]) {
-                    schi = schi + wt[u] * fabs(rel[u]);  // :411
+                    schi = (PK_FMA_LOOP & 4) ? fma(wt[u], fabs(rel[u]), schi) : schi + wt[u] * fabs(rel[u]);  // :411
                     sumwt = sumwt + wt[u];
                     double w = wtr[u];
                     wle = wle || (w <= 100000.);
@@ -392,7 +443,7 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
                     if (later) {                   // :426-427
                         const double e = PK_RECIP ? 0.4 * rel[u] * inv_chi : 0.4 * rel[u] / chiold;
                         const double e2 = e * e, e4 = e2 * e2;
-                        w = w / (1. + e4 * e4);
+                        w = (PK_FMA_LOOP & 4) ? w / fma(e4, e4, 1.) : w / (1. + e4 * e4);
                     }
 #if PK_RECIP
                     {   // weighted model terms once, then one fused multiply-add per normal-equation sum (12 fp64 operations, not 27)
@@ -576,7 +627,7 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
             T1[q] = -scl * dvx;
             T2[q] = -scl * dvy;
             const double fsub = FSUB[q];
-            const double df = fsub - scl * mval - sky;
+            const double df = PK_RECIP ? fma(-scl, mval, fsub) - sky : fsub - scl * mval - sky;
             if (ANALYTIC) {  // pkfit.py:277-282 (ronois enters un-squared, as in the reference)
                 double fpos = fsub - df;
                 if (fpos < 0.) fpos = 0.;
@@ -666,8 +717,8 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
                 const double dfv = ANALYTIC ? DF[nl + __popc(mk & lt)] : DF[q];
 #if PK_RECIP
                 const double is = ANALYTIC ? 1. / s : s;
-                numer = numer + dfdsig * dfv * is;
-                denom = denom + dfdsig * dfdsig * is;
+                numer = fma(dfdsig * dfv, is, numer);
+                denom = fma(dfdsig * dfdsig, is, denom);
 #else
                 numer = numer + dfdsig * dfv / s;
                 denom = denom + dfdsig * dfdsig / s;
@@ -681,7 +732,7 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
 #else
                 double wt = 5. / (5. + rsq / (1. - rsq));  // pkfit.py:323
 #endif
-                schi = schi + wt * fabs(rel);               // pkfit.py:359
+                schi = PK_RECIP ? fma(wt, fabs(rel), schi) : schi + wt * fabs(rel);  // pkfit.py:359
                 sumwt = sumwt + wt;
                 wt = PK_RECIP ? wt * SIGSQ[q] : wt / SIGSQ[q];  // pkfit.py:362
                 if (S.niter >= 2) {  // pkfit.py:364
