@@ -561,7 +561,7 @@ int bphot_version(void) { return BPHOT_VERSION; }
 const char* bphot_build_flags(void) {
     return "AP_ASM_SELECT=" BP_STR(AP_ASM_SELECT) " AP_BATCH=" BP_STR(AP_BATCH) " AP_GROUP=" BP_STR(AP_GROUP) " AP_S1_CTAS=" BP_STR(AP_S1_CTAS) " AP_MMM_INDEXED=" BP_STR(AP_MMM_INDEXED) " AP_MMM_OVERLAP=" BP_STR(AP_MMM_OVERLAP)
            " AP_S2_MINB=" BP_STR(AP_S2_MINB) " AP_SUMS_CTAS=" BP_STR(AP_SUMS_CTAS) " AP_DYNAMIC=" BP_STR(AP_DYNAMIC)
-           " PK_MINB_FORCED=" BP_STR(PK_MINB_FORCED) " PK_U=" BP_STR(PK_U) " PK_MINB_FIT=" BP_STR(PK_MINB_FIT) " PK_HOIST=" BP_STR(PK_HOIST) " PK_PSF_GLOBAL=" BP_STR(PK_PSF_GLOBAL) " AP_IDX_SKIP=" BP_STR(AP_IDX_SKIP) " AP_SIGNED_SHFL=" BP_STR(AP_SIGNED_SHFL) " AP_SMEM_UNIFORM=" BP_STR(AP_SMEM_UNIFORM) " PK_RECIP=" BP_STR(PK_RECIP) " PW_ONE_ATAN=" BP_STR(PW_ONE_ATAN) " PK_TSUM=" BP_STR(PK_TSUM);
+           " PK_MINB_FORCED=" BP_STR(PK_MINB_FORCED) " PK_U=" BP_STR(PK_U) " PK_MINB_FIT=" BP_STR(PK_MINB_FIT) " PK_HOIST=" BP_STR(PK_HOIST) " PK_PSF_GLOBAL=" BP_STR(PK_PSF_GLOBAL) " AP_IDX_SKIP=" BP_STR(AP_IDX_SKIP) " AP_SIGNED_SHFL=" BP_STR(AP_SIGNED_SHFL) " AP_SMEM_UNIFORM=" BP_STR(AP_SMEM_UNIFORM) " PK_RECIP=" BP_STR(PK_RECIP) " PW_ONE_ATAN=" BP_STR(PW_ONE_ATAN) " PK_TSUM=" BP_STR(PK_TSUM) " PK_FMA_MODEL=" BP_STR(PK_FMA_MODEL) " PK_FMA_LOOP=" BP_STR(PK_FMA_LOOP) " PK_FAST_RCP=" BP_STR(PK_FAST_RCP);
 }
 const char* bphot_last_error(void) { return g_err; }
 long long bphot_launch_count(void) { return g_launches.load(); }

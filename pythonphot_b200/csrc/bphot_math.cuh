@@ -17,6 +17,9 @@
 #include <math.h>
 #include <stdint.h>
 
+#ifndef PK_RSQRT
+#define PK_RSQRT 1  // device fits: 1 / sqrt(s) of the Cholesky pivots and of chi's normalisation by rsqrt() instead of sqrt + division
+#endif
 #ifndef PK_RECIP
 #define PK_RECIP 1  // fits: divisions whose divisor is fixed for a pixel / an iteration become multiplications by one reciprocal
 #endif
@@ -234,6 +237,15 @@ BP_HD double psf_value(double xx, double yy, const double* gauss, const double* 
     return e + v;
 }
 
+// 1 / sqrt(s) for s > 0: rsqrt() on the device (PK_RSQRT), 1.0 / sqrt(s) on the host and with the knob off
+BP_HD double bp_rsqrt(double s) {
+#if defined(__CUDA_ARCH__) && PK_RSQRT
+    return rsqrt(s);
+#else
+    return 1.0 / sqrt(s);
+#endif
+}
+
 // ------------------------------------------------------------ 3x3 inverse
 // The general case of inv3 (getrf + getri), on a flat copy of the matrix.  Normal matrices of a fit are symmetric positive
 // definite, so this is the cold path: out of line on the device, where its ~400 unrolled instructions would otherwise sit
@@ -290,42 +302,43 @@ BP_HD_COLD int inv3_lu(double* c9) {
 BP_HD int inv3(double c[3][3]) {
     bool sym = (c[0][1] == c[1][0]) && (c[0][2] == c[2][0]) && (c[1][2] == c[2][1]);
     if (sym) {
-        double l00, l10, l20, l11, l21, l22;
+        double l10, l20, l21;
         double s = c[0][0];
         if (s > 0.0) {
-            l00 = sqrt(s);
 #if PK_RECIP
             // three reciprocals instead of nine divisions (every quotient below has l00, l11 or l22 as its divisor); the
-            // results move by an ulp or two, far inside the 1e-9 the fits are held to
-            const double m00 = 1.0 / l00;
+            // results move by an ulp or two, far inside the 1e-9 the fits are held to.  On the device the reciprocal of
+            // the pivot's root is one rsqrt (the root itself is never needed).
+            const double m00 = bp_rsqrt(s);
             l10 = c[1][0] * m00;
             l20 = c[2][0] * m00;
 #else
+            const double l00 = sqrt(s);
             l10 = c[1][0] / l00;
             l20 = c[2][0] / l00;
 #endif
             s = c[1][1] - l10 * l10;
             if (s > 0.0) {
-                l11 = sqrt(s);
 #if PK_RECIP
-                const double m11 = 1.0 / l11;
+                const double m11 = bp_rsqrt(s);
                 l21 = (c[2][1] - l20 * l10) * m11;
 #else
+                const double l11 = sqrt(s);
                 l21 = (c[2][1] - l20 * l10) / l11;
 #endif
                 s = c[2][2] - l20 * l20;
                 s = s - l21 * l21;
                 if (s > 0.0) {
-                    l22 = sqrt(s);
                     // M = inv(L), lower triangular; inv(A) = M^T M
 #if PK_RECIP
-                    const double m22 = 1.0 / l22;
+                    const double m22 = bp_rsqrt(s);
                     const double m10 = -(l10 * m00) * m11;
                     const double m21 = -(l21 * m11) * m22;
                     double t = 0.0 + l20 * m00;
                     t = t + l21 * m10;
                     const double m20 = -t * m22;
 #else
+                    const double l22 = sqrt(s);
                     const double m00 = 1.0 / l00, m11 = 1.0 / l11, m22 = 1.0 / l22;
                     const double m10 = -(l10 * m00) / l11;
                     const double m21 = -(l21 * m11) / l22;

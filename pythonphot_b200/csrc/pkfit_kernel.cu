@@ -61,6 +61,9 @@ constexpr int PK_NARR_FIT = 10;     // per-warp scratch arrays of `cap` doubles,
 #ifndef PK_FMA_LOOP
 #define PK_FMA_LOOP 0  // forced fit, bit mask: 1 = sky taken off the pixel at set-up and the residual as one fma, 2 = dfs / sigma^2 stored, 4 = s3 / schi / e^8 as fmas
 #endif
+#ifndef PK_FAST_RCP
+#define PK_FAST_RCP 1  // 1 / (1 + e^8) of the residual down-weighting by rcp.approx + two Newton steps (6 instructions, ~1 ulp) instead of a division (~30)
+#endif
 #ifndef PK_TSUM
 #define PK_TSUM 1  // the 13-14 warp sums of an iteration through warp_sum16 (one transposing reduction) instead of one butterfly each
 #endif
@@ -155,6 +158,18 @@ BP_D double rinter_f(const double* p, int nr, int nc, double x, double y, double
     return fma(yd, fma(yd, fma(yd, d3, d2), d1), y0);
 }
 
+// 1 / d for 1 <= d <= 2^17 (or NaN in, NaN out): the hardware's 2^-23 reciprocal estimate and two Newton steps.  Only used
+// for pkfit.py:364's 1 + (0.4 rel/chiold)^8 of pixels that passed the 10-sigma test, i.e. d in [1, 65537]: no zero, no
+// infinity, no subnormal can reach it, which is what the ~25 extra instructions of a full IEEE division guard against.
+BP_D double rcp_bounded(double d) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+    double e = fma(-d, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-d, r, 1.0);
+    return fma(r, e, r);
+}
+
 // dao_value.py:95-107 for the pixel in column c, row r of the box (offsets dxv, dyv from the star).
 BP_D double model_at(const double* AX, int acap, int c, int r, double dxv, double dyv, const double* gauss,
                      const double* psf, int npsf, double half, double* dvx, double* dvy) {
@@ -211,8 +226,14 @@ BP_D bool fit_tail(const PkfitParams& P, const double* gauss, FitState& S, doubl
                    double denom, double schi, double sumwt, bool* loop) {
     S.chi = schi;
     if (sumwt > 3.0) {  // pkfit.py:379-381
+#if PK_RECIP
+        // sumwt is in (3, number of pixels]: the product is positive and finite, the reciprocal in rcp_bounded's range
+        S.chi = 1.2533 * S.chi * bp_rsqrt(sumwt * (sumwt - 3.));
+        S.chiold = PK_FAST_RCP ? ((sumwt - 3.) * S.chi + 3.) * rcp_bounded(sumwt) : ((sumwt - 3.) * S.chi + 3.) / sumwt;
+#else
         S.chi = 1.2533 * S.chi * sqrt(1. / (sumwt * (sumwt - 3.)));
         S.chiold = ((sumwt - 3.) * S.chi + 3.) / sumwt;
+#endif
     }
     double csum = 0.;
     for (int a = 0; a < 3; a++)
@@ -443,7 +464,7 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
                     if (later) {                   // :426-427
                         const double e = PK_RECIP ? 0.4 * rel[u] * inv_chi : 0.4 * rel[u] / chiold;
                         const double e2 = e * e, e4 = e2 * e2;
-                        w = (PK_FMA_LOOP & 4) ? w / fma(e4, e4, 1.) : w / (1. + e4 * e4);
+                        w = PK_FAST_RCP ? w * rcp_bounded(fma(e4, e4, 1.)) : (PK_FMA_LOOP & 4) ? w / fma(e4, e4, 1.) : w / (1. + e4 * e4);
                     }
 #if PK_RECIP
                     {   // weighted model terms once, then one fused multiply-add per normal-equation sum (12 fp64 operations, not 27)
@@ -738,7 +759,7 @@ BP_D FitOut pkfit_recenter_warp(const PkfitParams& P, const double* __restrict__
                 if (S.niter >= 2) {  // pkfit.py:364
                     const double e = PK_RECIP ? 0.4 * rel * inv_chi : 0.4 * rel / chiold;
                     const double e2 = e * e, e4 = e2 * e2;
-                    wt = wt / (1. + e4 * e4);
+                    wt = PK_FAST_RCP ? wt * rcp_bounded(fma(e4, e4, 1.)) : wt / (1. + e4 * e4);  // survivors of the 10-sigma test: e < 4
                 }
                 const int g = direct ? q : GIDX[q];
                 const double t0 = T0[g], t1 = T1[g], t2 = T2[g];
