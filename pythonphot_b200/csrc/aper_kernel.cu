@@ -29,6 +29,9 @@ constexpr int AP_WARPS = AP_THREADS / 32;
 #ifndef AP_S1_CTAS_F64
 #define AP_S1_CTAS_F64 1  // fp64 keys: measured 220 ms per 1 M stars at 255 registers (1), 250 at 3 CTAs, 260 at 4 -- not occupancy-bound
 #endif
+#ifndef AP_RECIP
+#define AP_RECIP 1  // aperture sums: per-pixel divisions by per-star constants as multiplications (values move by an ulp; fluxes are held to 1e-9)
+#endif
 #ifndef AP_GATHER_U
 #define AP_GATHER_U 4
 #endif
@@ -565,6 +568,7 @@ BP_D ApPartial aperture_warp(const AperParams& P, const T* __restrict__ stamp, c
     // box position (row rr, column cc) of this lane's pixel, advanced by the loop stride without a division per pixel
     const int step = 32 * nw, bwd = bw > 0 ? bw : 1, krow = step / bwd, kcol = step - krow * bwd;
     int rr = (w * 32 + lane) / bwd, cc = (w * 32 + lane) - rr * bwd;
+    const double inv_nx = 1.0 / (double)g.nx;  // AP_RECIP: the Python-3 pixel y-centre (row + col / nx) by one reciprocal per star
     for (int base = w * 32; base < npx; base += step) {
         const int p = base + lane;
         int r = 0, c = 0, cls = 0;
@@ -575,7 +579,7 @@ BP_D ApPartial aperture_warp(const AperParams& P, const T* __restrict__ stamp, c
             c = c0 + cc;
             if (P.exact) {  // aper.py:313-333
                 xxp = (double)c;
-                yyp = P.compat_py2 ? (double)r : (double)(r * g.nx + c) / (double)g.nx;  // r * nx + c < 2^31 (stamp <= 20 000 px wide)
+                yyp = P.compat_py2 ? (double)r : AP_RECIP ? (double)(r * g.nx + c) * inv_nx : (double)(r * g.nx + c) / (double)g.nx;  // r * nx + c < 2^31 (stamp <= 20 000 px wide)
                 const double x1 = fabs(xxp - g.dx), y1 = fabs(yyp - g.dy);
                 if (!(x1 > bigrad || y1 > bigrad)) cls = (x1 < smallrad && y1 < smallrad) ? 1 : pixel_class(x1, y1, ap);
                 if (cls == 1) wgt = 1.0;

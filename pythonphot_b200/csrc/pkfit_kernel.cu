@@ -257,10 +257,13 @@ BP_D bool fit_tail(const PkfitParams& P, const double* gauss, FitState& S, doubl
     const double rs = dt0 / S.scale;  // pkfit.py:427-429 with one division for both candidates
     double denom2 = rs * (1. / 5.25);
     if (denom2 < -rs * (1. / 0.84)) denom2 = -rs * (1. / 0.84);
-    S.scale = S.scale + dt0 / (1 + denom2 * S.iclamp0);
+    // the three step denominators are 1 + (something >= 0): the bounded reciprocal where they are below 2^17, a division otherwise
+    // (also for NaN); the choice is the same in every lane
+    auto step = [](double dt, double d) { return (PK_FAST_RCP && d <= 131072.) ? dt * rcp_bounded(d) : dt / d; };
+    S.scale = S.scale + step(dt0, 1 + denom2 * S.iclamp0);
     if (V == 1 || (V == 0 && P.recenter)) {  // pkfit.py:430-432
-        S.x = S.x + dt1 / (1. + adt1 * (2. * S.iclamp1));
-        S.y = S.y + dt2 / (1. + adt2 * (2. * S.iclamp2));
+        S.x = S.x + step(dt1, 1. + adt1 * (2. * S.iclamp1));
+        S.y = S.y + step(dt2, 1. + adt2 * (2. * S.iclamp2));
     }
 #else
     double denom2 = dt0 / (5.25 * S.scale);  // pkfit.py:427-429
@@ -312,6 +315,8 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
     const double gauss[5] = {P.gauss[0], P.gauss[1], P.gauss[2], P.gauss[3], P.gauss[4]};
     const double radsq = P.radius * P.radius;
     const double gx2 = gauss[3] * gauss[3], gy2 = gauss[4] * gauss[4];
+    const double igx2 = 1. / gx2, igy2 = 1. / gy2;  // PK_RECIP
+    (void)igx2; (void)igy2; (void)gx2; (void)gy2;
     const double half = (double)(npsf - 1) / 2.;
     const unsigned lt = (1u << lane) - 1u;
 
@@ -349,18 +354,29 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
             if (q < cap) {
                 const size_t row = (size_t)(b.iylo + r), col = (size_t)(b.ixlo + c);
                 FSUB[q] = (PK_FMA_LOOP & 1) ? (double)img[row * P.pitch + col] - sky : (double)img[row * P.pitch + col];  // PK_RECIP: sky taken off once
-                SIG[q] = PK_RECIP ? 1. / nz : nz;
+#if PK_RECIP
+                const double isg = 1. / nz;
+                SIG[q] = isg;
+                W0[q] = 5. * (1. - rsq) / (5. - 4. * rsq);  // :375, 5 / (5 + rsq / (1 - rsq)) with one division
+                const double rho = dxv * dxv * igx2 + dyv * dyv * igy2;  // :338
+#else
+                SIG[q] = nz;
                 W0[q] = 5. / (5. + rsq / (1. - rsq));
                 const double rho = dxv * dxv / gx2 + dyv * dyv / gy2;  // :338
+#endif
                 const double rh = 0.5 * rho;
                 const double dfsv = (rho <= 36.) ? exp(-rh) * (rh - 1.) : nan64();
 #if PK_HOIST
                 const double ssq = nz * nz;
+                (void)ssq;
                 DFS[q] = (PK_FMA_LOOP & 2) ? dfsv / ssq : dfsv;  // PK_RECIP: the sharpness numerator's per-pixel factor, NaN where dfsv is
 #else
                 DFS[q] = dfsv;
 #endif
-#if PK_HOIST
+#if PK_HOIST && PK_RECIP
+                WTR[q] = W0[q] * (isg * isg);
+                DDS[q] = dfsv * dfsv * (isg * isg);
+#elif PK_HOIST
                 WTR[q] = W0[q] / ssq;
                 DDS[q] = dfsv * dfsv / ssq;
 #endif
