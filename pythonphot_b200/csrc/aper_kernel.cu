@@ -42,7 +42,7 @@ constexpr int AP_WARPS = AP_THREADS / 32;
 #define AP_S2_MINB 9  // minimum resident stage-2 CTAs per SM the register budget is compiled for
 #endif
 #ifndef AP_SUMS_CTAS
-#define AP_SUMS_CTAS 6
+#define AP_SUMS_CTAS 8  // 6 -> 8 (64 registers): aper_sums 10.86 -> 10.32 ms per 1 M stars
 #endif
 
 BP_D float kmin(float a, float b) { return fminf(a, b); }
