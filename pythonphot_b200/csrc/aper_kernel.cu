@@ -640,21 +640,42 @@ BP_D ApPartial aperture_warp(const AperParams& P, const T* __restrict__ stamp, c
 // Index layout per star (idx_stride bytes, 64-byte aligned): T L1[16] | T L2[256] | double2 PT[257].
 constexpr size_t sort_index_bytes(size_t key_size) { return ((size_t)(16 + 256) * key_size + (size_t)257 * 16 + 63) & ~(size_t)63; }
 
+#ifndef AP_MED_SMEM
+#define AP_MED_SMEM 0  // 1 = the two median keys reach sort_index through shared memory instead of the scratch row; measured: stage 1 36.4 -> 38.0 ms (the 2 x K predicated selects and the divergent branch cost more than the L2 round trip the other CTAs hide)
+#endif
 #ifndef AP_IDX_SKIP
 #define AP_IDX_SKIP 0  // timing experiments only (wrong results): 1 = no per-key sums, 2 = no scan, 4 = no writes, 8 = no median read
 #endif
 template <typename T, int K>
-BP_D void sort_index(const AperParams& P, const T (&r)[K], const T* __restrict__ dst, int nvalid, size_t row, int tid, double (*s_wsum)[2]) {
+BP_D void sort_index(const AperParams& P, const T (&r)[K], const T* __restrict__ dst, int nvalid, size_t row, int tid, double (*s_wsum)[2], T* s_med) {
     static_assert(K == 8 || K == 16 || K == 32, "index groups are 16 keys");
     const int lane = tid & 31, warp = tid >> 5, nthr = (int)blockDim.x;
     unsigned char* base = reinterpret_cast<unsigned char*>(P.sidx) + row * (size_t)P.idx_stride;
     T* __restrict__ L1 = reinterpret_cast<T*>(base);
     T* __restrict__ L2 = L1 + 16;
     double2* __restrict__ PT = reinterpret_cast<double2*>(L2 + 256);
-    // the two median keys (ranks (n-1)/2 and n/2) were just written to the scratch row by some thread of this CTA
-    __syncthreads();
+    // the two median keys (ranks (n-1)/2 and n/2) sit in registers of one or two threads of this CTA: they go through shared
+    // memory (AP_MED_SMEM; reading them back from the scratch row just written cost an L2 round trip with every thread waiting)
     double skymid = 0.0;
+#if AP_MED_SMEM
+    (void)dst;
+    if (nvalid > 0) {
+        const int m1 = (nvalid - 1) / 2, m2 = nvalid / 2;
+        if (m1 / K == tid || m2 / K == tid) {  // at most two threads, usually one
+            const int q1 = m1 / K == tid ? m1 % K : -1, q2 = m2 / K == tid ? m2 % K : -1;
+#pragma unroll
+            for (int q = 0; q < K; q++) {
+                if (q == q1) s_med[0] = r[q];
+                if (q == q2) s_med[1] = r[q];
+            }
+        }
+    }
+    __syncthreads();
+    if (!(AP_IDX_SKIP & 8) && nvalid > 0) skymid = 0.5 * (double)s_med[0] + 0.5 * (double)s_med[1];  // mmm.py:121
+#else
+    __syncthreads();
     if (!(AP_IDX_SKIP & 8) && nvalid > 0) skymid = 0.5 * (double)__ldcg(dst + (nvalid - 1) / 2) + 0.5 * (double)__ldcg(dst + nvalid / 2);  // mmm.py:121
+#endif
     const int e0 = tid * K;
     constexpr int H = K > 16 ? 16 : K;  // keys of this thread in its first index group
     // four independent chains of K/4 keys each (the adds of one chain wait for each other), folded pairwise
@@ -731,6 +752,7 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S
     __shared__ int s_ntot;
     __shared__ int s_nrej[AP_WARPS], s_nnan[AP_WARPS];
     __shared__ double s_wsum[AP_WARPS][2];
+    __shared__ T s_med[2];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = (int)(blockDim.x >> 5);
     const T* __restrict__ img = reinterpret_cast<const T*>(P.img);
@@ -814,7 +836,7 @@ __global__ void __launch_bounds__(AP_THREADS, (K == 32 && sizeof(T) == 4) ? AP_S
                         else *reinterpret_cast<double2*>(dst + e) = make_double2(r[q], r[q + 1]);
                     }
                 }
-                if (P.sidx) sort_index<T, K>(P, r, dst, nvalid, (size_t)(i - P.s0 + P.row0), tid, s_wsum);
+                if (P.sidx) sort_index<T, K>(P, r, dst, nvalid, (size_t)(i - P.s0 + P.row0), tid, s_wsum, s_med);
             } else {
                 int m = 2;
                 while (m < nslots) m <<= 1;
