@@ -1000,9 +1000,12 @@ __global__ void __launch_bounds__(AP_THREADS, AP_S2_MINB) aper_stage2_kernel(con
 #define AP_MMM_OVERLAP 0
 #endif
 // with AP_MMM_OVERLAP: 64 threads x <= 64 registers = the 4 096 registers per SM that stage 1's 8 CTAs leave free
+#ifndef AP_MMM_MINB
+#define AP_MMM_MINB 1  // resident CTAs per SM the thread-per-star mmm is compiled for
+#endif
 constexpr int AP_MMM_THREADS = AP_MMM_OVERLAP ? 64 : AP_THREADS;
 template <typename T>
-__global__ void __launch_bounds__(AP_MMM_THREADS, AP_MMM_OVERLAP ? 16 : 1) aper_mmm_kernel(const AperParams P) {
+__global__ void __launch_bounds__(AP_MMM_THREADS, AP_MMM_OVERLAP ? 16 : AP_MMM_MINB) aper_mmm_kernel(const AperParams P) {
     const T* __restrict__ skeys = reinterpret_cast<const T*>(P.skeys);
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < P.scount; j += gridDim.x * blockDim.x) {
         const int i = P.s0 + j;
