@@ -53,6 +53,16 @@ BP_D double warp_max(double v) {
     return v;
 }
 
+// Asks L1/L2 for the 128-byte lines of rows [row0, row0 + nrows) x bytes [b0, b1) of a pitched array, one row per lane: the
+// stamp a warp is about to walk pixel by pixel (first-touch misses were its largest scoreboard stall).  No architectural effect.
+BP_D void prefetch_rows(const void* base, size_t pitch_bytes, long long row0, int nrows, size_t b0, size_t b1, int lane) {
+    for (int r = lane; r < nrows; r += 32) {
+        const char* p = reinterpret_cast<const char*>(base) + (size_t)(row0 + r) * pitch_bytes;
+        for (size_t o = b0; o < b1; o += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(p + o));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(p + b1 - 1));  // the line of the last byte (rows are not 128-byte aligned)
+    }
+}
+
 template <typename T> struct KeyTraits;
 template <> struct KeyTraits<float> {
     BP_D static float inf() { return __int_as_float(0x7f800000); }

@@ -64,6 +64,9 @@ constexpr int PK_NARR_FIT = 10;     // per-warp scratch arrays of `cap` doubles,
 #ifndef PK_FAST_RCP
 #define PK_FAST_RCP 1  // 1 / (1 + e^8) of the residual down-weighting by rcp.approx + two Newton steps (6 instructions, ~1 ulp) instead of a division (~30)
 #endif
+#ifndef PK_PREFETCH
+#define PK_PREFETCH 0  // forced fit: prefetch the fitting box of image, noise and mask at the start of a star; measured 14.7 -> 16.0 ms (the other warps already hide those misses), off
+#endif
 #ifndef PK_TSUM
 #define PK_TSUM 1  // the 13-14 warp sums of an iteration through warp_sum16 (one transposing reduction) instead of one butterfly each
 #endif
@@ -328,6 +331,12 @@ BP_D FitOut pkfit_forced_warp(const PkfitParams& P, const double* __restrict__ p
     // ---- once per star (the reference redoes this every iteration from identical inputs, :170-240)
     S.niter = 1;
     const FitBox b = fit_box(P, x, y);
+#if PK_PREFETCH
+    // the box's rows of the three images, requested before the erf / exp work of fill_axes instead of one chunk at a time
+    prefetch_rows(noise, (size_t)P.npitch * sizeof(TN), b.iylo, b.iyy, (size_t)b.ixlo * sizeof(TN), (size_t)(b.ixlo + b.ixx) * sizeof(TN), lane);
+    prefetch_rows(mask, (size_t)P.mpitch, b.iylo, b.iyy, (size_t)b.ixlo, (size_t)(b.ixlo + b.ixx), lane);
+    prefetch_rows(img, (size_t)P.pitch * sizeof(TI), b.iylo, b.iyy, (size_t)b.ixlo * sizeof(TI), (size_t)(b.ixlo + b.ixx) * sizeof(TI), lane);
+#endif
     fill_axes(b, x, y, gauss, AX, acap, lane);
     int ngood = 0;
     double xmin = KeyTraits<double>::inf(), xmax = -KeyTraits<double>::inf(), ymin = xmin, ymax = xmax;
