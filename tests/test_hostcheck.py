@@ -138,3 +138,31 @@ def test_mmm_through_index_golden():
         # north_star's bar, not 1e-10: the bimodal golden (n=85, half the keys near 300, half near 5000) has
         # mean^2 / variance = 1e6, which amplifies ANY change of summation order to ~4e-10 in sigma
         assert_close(got[:3], out[:3], rtol=1e-9, atol=1e-10, what="indexed mmm n=%d" % n)
+
+
+def test_warp_sum16_emulation_has_the_butterfly_bits():
+    """bphot_device.cuh warp_sum16 (the fits' 13-14 sums in one transposing reduction) claims the SAME additions in the same
+    order as sixteen warp_sum() butterflies.  The device code cannot run here; this is its data flow, lane by lane, in numpy
+    (fp64 addition is commutative, so a + b on one lane and b + a on its partner are the same bits)."""
+    rng = np.random.default_rng(16)
+    for trial in range(50):
+        v = rng.normal(size=(32, 16)) * 10.0 ** rng.integers(-8, 9, size=(32, 16))  # v[lane, value]
+        # reference: one butterfly per value, lane distances 16, 8, 4, 2, 1
+        b = v.copy()
+        for o in (16, 8, 4, 2, 1):
+            b = b + b[np.arange(32) ^ o]
+        assert all(np.array_equal(b[0], b[l]) for l in range(32))
+        # warp_sum16: level h = 8, 4, 2, 1 at lane distance 2h; a lane whose bit is set keeps the upper half of its slots
+        w = v.copy()
+        lanes = np.arange(32)
+        for h in (8, 4, 2, 1):
+            bit = 2 * h
+            up = (lanes & bit) != 0
+            send = np.where(up[:, None], w[:, :h], w[:, h:2 * h])
+            keep = np.where(up[:, None], w[:, h:2 * h], w[:, :h])
+            w = w.copy()
+            w[:, :h] = keep + send[lanes ^ bit]
+        tot = w[:, 0] + w[lanes ^ 1, 0]
+        got = np.array([tot[2 * k] for k in range(16)])  # value k is complete in lanes 2k and 2k + 1
+        assert np.array_equal(tot[0::2], tot[1::2])
+        assert np.array_equal(got, b[0]), "trial %d: the transposing reduction changed a sum's bits" % trial
