@@ -166,3 +166,28 @@ def test_warp_sum16_emulation_has_the_butterfly_bits():
         got = np.array([tot[2 * k] for k in range(16)])  # value k is complete in lanes 2k and 2k + 1
         assert np.array_equal(tot[0::2], tot[1::2])
         assert np.array_equal(got, b[0]), "trial %d: the transposing reduction changed a sum's bits" % trial
+
+
+def test_rcp_bounded_newton_steps_reach_one_ulp():
+    """pkfit_kernel.cu rcp_bounded: a reciprocal estimate good to 2^-23 (what rcp.approx.ftz.f64 promises) followed by two
+    Newton steps in fused multiply-adds.  Emulated with exact rational arithmetic rounded once per fma, over its stated domain
+    [1, 2^17] and with the worst seeds the estimate may return: the result is within one ulp of the correctly rounded 1/d."""
+    from fractions import Fraction
+
+    def fma(a, b, c):
+        return float(Fraction(a) * Fraction(b) + Fraction(c))  # one rounding
+
+    rng = np.random.default_rng(23)
+    worst = 0.0
+    for d in np.concatenate([rng.uniform(1.0, 2.0, 300), 2.0 ** rng.uniform(0, 17, 300), [1.0, 65537.0, 131072.0]]):
+        d = float(d)
+        for rel in (2.0 ** -23, -2.0 ** -23, 0.0, 3e-8):
+            r = float(np.float64((1.0 / d) * (1.0 + rel)))
+            e = fma(-d, r, 1.0)
+            r = fma(r, e, r)
+            e = fma(-d, r, 1.0)
+            r = fma(r, e, r)
+            exact = Fraction(1) / Fraction(d)
+            ulp = np.spacing(1.0 / d)
+            worst = max(worst, abs(float(Fraction(r) - exact)) / ulp)
+    assert worst <= 1.0, worst
