@@ -44,10 +44,10 @@ def _p(a):
     return a.ctypes.data_as(C.c_void_p)
 
 
-def pixwt(xc, yc, r, x, y):
+def pixwt(xc, yc, r, x, y, exact=False):
     x = np.ascontiguousarray(x, np.float64); y = np.ascontiguousarray(y, np.float64)
     out = np.empty_like(x)
-    lib().hc_pixwt(C.c_double(xc), C.c_double(yc), C.c_double(r), _p(x), _p(y), C.c_int(x.size), _p(out))
+    (lib_exact() if exact else lib()).hc_pixwt(C.c_double(xc), C.c_double(yc), C.c_double(r), _p(x), _p(y), C.c_int(x.size), _p(out))
     return out
 
 
